@@ -1,0 +1,336 @@
+#!/usr/bin/env python
+"""bench.py -- train samples/sec of the weather-MLP training step on N B200s (+ roofline, CPU baseline).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--rows-per-step B] [--features F] [--impl reference]
+  python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
+
+A "step" is one optimizer step of the hot path (standardise -> forward -> cross-entropy -> backward ->
+Adam) over `rows-per-step` rows PER GPU of a synthetic weather table (weak scaling).  Workload, roofline
+arithmetic and the CPU baseline are defined in DESIGN.md "Measurement".  One JSON line on stdout (rank 0).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "train samples/sec"
+UNIT = "samples/s"
+
+
+def read_peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        with open(path) as fh:
+            d = json.load(fh)
+        return float(d["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks + throttle reasons sampled every 200 ms while the timed region runs."""
+
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index = index
+        self.proc = None
+        self.lines = []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "200"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._pump, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self) -> dict:
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.25)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            parts = [p.strip() for p in ln.split(",")]
+            if len(parts) < 7:
+                continue
+            try:
+                sm.append(float(parts[0])); mx.append(float(parts[1]))
+            except ValueError:
+                continue
+            for nm, val in zip(names, parts[3:7]):
+                if val.lower().startswith("active"):
+                    reasons.add(nm)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def synth_raw_on_device(torch, n_rows: int, f: int, seed: int, device):
+    """Raw (un-standardised) fp32 columns + int64 labels, generated on the GPU (same family of distributions
+    as oracle/synth.py; generation is outside every timed region)."""
+    g = torch.Generator(device=device)
+    g.manual_seed(seed)
+    mu = [20.0, 65.0, 10.0, 50.0, 1013.0]
+    sg = [8.0, 20.0, 6.0, 30.0, 7.0]
+    raw = torch.empty(f, n_rows, dtype=torch.float32, device=device)
+    for j in range(f):
+        raw[j].normal_(mu[j % 5] + 3.0 * (j // 5), sg[j % 5] * (1.0 + 0.25 * (j // 5)), generator=g)
+    if f > 5:
+        raw[f - 1].fill_(42.5)      # constant column: exercises the std==0 guard (preprocess.py:36)
+    z0 = (raw[0] - mu[0]) / sg[0]
+    z1 = (raw[1 % f] - mu[1 % 5]) / sg[1 % 5]
+    score = -1.6 + 0.9 * z1 - 0.7 * z0 + 0.6 * torch.randn(n_rows, device=device, generator=g)
+    y = (score > 0).to(torch.int64)
+    return raw, y
+
+
+def cpu_baseline(f: int, rows_per_rank: int, steps: int, warmup: int):
+    """The oracle's restatement of the reference step under gloo DDP, world_size 2 (the reference's topology,
+    docker-compose.yml:124), on this host's cores.  Bounded sample: `steps` steps of rows_per_rank rows/rank."""
+    from oracle import train_ref
+
+    cores = os.cpu_count() or 2
+    threads = max(1, min(32, cores // 2))
+    r = train_ref.time_cpu_ddp(f=f, batch=rows_per_rank, steps=steps, warmup=warmup, world=2, threads=threads,
+                               n_rows=max(4 * rows_per_rank, 145_460), per_sample=False)
+    return r, threads
+
+
+def run_reference(args, rank: int):
+    if rank != 0:
+        return 0
+    f = args.features
+    rows = args.cpu_rows_per_step if args.cpu_rows_per_step else args.rows_per_step
+    rows_per_rank = max(1, rows // 2)
+    r, threads = cpu_baseline(f, rows_per_rank, args.steps, args.warmup)
+    val = r["samples_per_sec"]
+    line = {
+        "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * r["seconds"] / args.steps,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": workload_config(args, rows_per_gpu=rows),
+        "cpu_baseline": {"value": val, "unit": UNIT, "cores": r["cores"], "kind": "port",
+                         "sample": f"{args.steps} steps x {rows_per_rank} rows/rank x 2 ranks, gloo DDP on localhost, "
+                                   f"{threads} threads/rank, tensor-sliced batches (oracle/train_ref.py restatement of "
+                                   f"jobs/train_lightning_ddp.py; Lightning/MLflow not installable)"},
+        "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+    return 0
+
+
+def workload_config(args, rows_per_gpu: int) -> dict:
+    return {"workload": f"weather MLP F={args.features} H=64 C=2 fp32: fused standardise+forward+CE+backward+Adam "
+                        f"step (BASELINE.json configs[1]); {rows_per_gpu} rows/step/GPU streamed from a "
+                        f"{args.table_rows}-row raw fp32 columnar table resident in HBM",
+            "features": args.features, "rows_per_step_per_gpu": rows_per_gpu, "table_rows_per_gpu": args.table_rows,
+            "dropout": "philox p=0.2", "optimizer": "Adam lr=0.01",
+            "l2_policy": "inputs larger than L2: every step reads a different window of a table >> 126 MB",
+            "parallelism": f"dp{args.gpus}"}
+
+
+def main() -> int:
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="wxddp", choices=["wxddp", "reference"])
+    ap.add_argument("--features", type=int, default=20)
+    ap.add_argument("--rows-per-step", type=int, default=1 << 20)
+    ap.add_argument("--table-rows", type=int, default=1 << 24)
+    ap.add_argument("--cpu-rows-per-step", type=int, default=65536,
+                    help="CPU arms: rows per step of the bounded sample (0 = --rows-per-step)")
+    ap.add_argument("--cpu-steps", type=int, default=8)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    args = ap.parse_args()
+
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+
+    if args.impl == "reference":
+        return run_reference(args, rank)
+
+    import torch
+
+    import wxddp
+
+    if args.warmup < 3:
+        args.warmup = 3
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a B200: wxddp has no CPU path (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local_rank)
+    device = torch.device("cuda", local_rank)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=device)
+
+    f, B, T = args.features, args.rows_per_step, args.table_rows
+    if T < 2 * B:
+        T = args.table_rows = 2 * B
+    ctx = wxddp.Context(f, device=device)
+    P = ctx.P
+    raw, y = synth_raw_on_device(torch, T, f, 1234 + rank, device)
+    cols = [raw[j] for j in range(f)]
+    stats = ctx.col_stats(cols)
+    if world > 1:
+        parts = [torch.empty_like(stats) for _ in range(world)]
+        dist.all_gather(parts, stats)
+        stats = ctx.stats_merge(torch.stack(parts).contiguous())
+    torch.manual_seed(42)
+    from torch import nn
+    net = nn.Sequential(nn.Linear(f, 64), nn.ReLU(), nn.Dropout(0.2), nn.Linear(64, 2))
+    params = torch.cat([p.detach().reshape(-1) for p in net.parameters()]).to(device)
+    m = torch.zeros(P, device=device)
+    v = torch.zeros(P, device=device)
+    state = torch.zeros(2, dtype=torch.int64, device=device)
+    loss = torch.zeros(1, device=device)
+    grads = torch.zeros(P + 1, device=device)
+    feats = None
+    if world > 1:
+        feats, _ = ctx.normalize_pack(cols, stats, impute=wxddp.IMPUTE_MEAN)
+    n_windows = (T - B) // B + 1
+    step_no = [0]
+
+    def one_step():
+        s = step_no[0]
+        row0 = (s % n_windows) * B
+        if world == 1:
+            ctx.train_step_raw(params, m, v, state, cols, stats, y, loss, row0=row0, batch=B,
+                               impute=wxddp.IMPUTE_MEAN, dropout=wxddp.DROPOUT_PHILOX, seed=42)
+        else:
+            # DDP: local sums pre-scaled by 1/(W*B), SUM across ranks (what torch's reducer does, :136),
+            # loss scalar rides in the same bucket (element P), then Adam
+            ctx.mlp_grad(params, feats, y, row0=row0, batch=B, dropout=wxddp.DROPOUT_PHILOX, seed=42 + 1000 * rank,
+                         step=s, scale=1.0 / (world * B), out=grads)
+            dist.all_reduce(grads)
+            ctx.adam_step(params, grads, m, v, s + 1, n=P)
+        step_no[0] = s + 1
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        one_step()
+    barrier()
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    launches0 = ctx.launch_count
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    ev0.record()
+    for _ in range(args.steps):
+        one_step()
+    ev1.record()
+    barrier()
+    ms = ev0.elapsed_time(ev1)
+    launches = ctx.launch_count - launches0
+    clocks = sampler.stop() if rank == 0 else None
+    t = torch.tensor([ms], dtype=torch.float64, device=device)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t.item())
+    final_loss = float(loss.item()) if world == 1 else float(grads[P].item())
+
+    # ---- e2e: public API with HOST buffers; H2D of the step's raw rows + labels and D2H of the loss inside ----
+    e2e = None
+    if not args.no_e2e:
+        from wxddp.engine import StepEngine
+        eng = StepEngine(f, device=device, world=world, rank=rank, process_group=dist if world > 1 else None)
+        eng.set_stats(stats)
+        n_host = 4
+        host_cols = [torch.empty(f, B, dtype=torch.float32).pin_memory() for _ in range(n_host)]
+        host_y = [torch.empty(B, dtype=torch.int64).pin_memory() for _ in range(n_host)]
+        for i in range(n_host):
+            host_cols[i].copy_(raw[:, i * B:(i + 1) * B])
+            host_y[i].copy_(y[i * B:(i + 1) * B])
+        for i in range(3):
+            eng.step_host(host_cols[i % n_host], host_y[i % n_host])
+        barrier()
+        t0 = time.perf_counter()
+        for i in range(args.steps):
+            last = eng.step_host(host_cols[i % n_host], host_y[i % n_host])
+        barrier()
+        dt = time.perf_counter() - t0
+        tt = torch.tensor([dt], dtype=torch.float64, device=device)
+        if world > 1:
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        dt = float(tt.item())
+        e2e = {"value": args.steps * B * world / dt, "unit": UNIT, "h2d_bytes_per_step": B * (4 * f + 8),
+               "d2h_bytes_per_step": 4, "ms_per_step": 1e3 * dt / args.steps, "last_loss": last,
+               "api": "wxddp.engine.StepEngine.step_host(pinned raw columns, labels) -> loss"}
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return 0
+
+    value = args.steps * B * world / (ms / 1e3)
+    peak, peak_src = read_peaks()
+    bytes_per_row = 4 * f + 8                                   # fp32 features + int64 label
+    kernel_s = (ms / 1e3) / args.steps                          # one step-kernel launch per step on 1 GPU
+    achieved = B * bytes_per_row / kernel_s / 1e9
+    flops_per_row = 2 * (2 * f * 64 + 3 * 64 * 2)
+    roof = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+            "traffic": None, "kernel": "mlp_grid_kernel<F,TRAIN,RAW_F32> (wx_train_step_raw)" if world == 1
+            else "mlp_grid_kernel<F,TRAIN,ROWMAJOR> (wx_mlp_grad) + NCCL all-reduce + adam_kernel",
+            "peak_source": peak_src, "algorithmic_bytes_per_row": bytes_per_row,
+            "fp32_pipe": {"achieved_tflops": B * flops_per_row / kernel_s / 1e12, "peak_tflops": 74.4,
+                          "frac": B * flops_per_row / kernel_s / 1e12 / 74.4,
+                          "note": "148 SM x 128 lanes x 2 x 1.965 GHz; the step is ~67 FLOP/B, above the fp32 ridge"}}
+    line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": workload_config(args, B),
+            "roofline": roof, "clocks": clocks, "gpu_launches": int(launches), "final_loss": final_loss}
+    if e2e is not None:
+        line["e2e"] = e2e
+    if not args.no_cpu_baseline and world == 1:
+        rows_cpu = args.cpu_rows_per_step if args.cpu_rows_per_step else B
+        r, threads = cpu_baseline(f, max(1, rows_cpu // 2), args.cpu_steps, 2)
+        line["cpu_baseline"] = {"value": r["samples_per_sec"], "unit": UNIT, "cores": r["cores"], "kind": "port",
+                                "sample": f"{args.cpu_steps} steps x {max(1, rows_cpu // 2)} rows/rank x 2 ranks "
+                                          f"(gloo DDP, localhost, {threads} threads/rank, tensor-sliced batches), "
+                                          f"{r['seconds']:.1f} s of CPU work; host has {os.cpu_count()} cores"}
+        # the reference's literal configuration (batch 4 per rank, per-sample loader), for the record
+        from oracle import train_ref
+        r4 = train_ref.time_cpu_ddp(f=f, batch=4, steps=1500, warmup=50, world=2, threads=1, per_sample=True)
+        line["cpu_reference_config"] = {"value": r4["samples_per_sec"], "unit": UNIT, "cores": 2,
+                                        "sample": "1500 steps x 4 rows/rank x 2 ranks, 1 thread/rank, per-sample "
+                                                  "__getitem__+collate (train_lightning_ddp.py:49,122)"}
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -1,0 +1,283 @@
+// Host side of K2/K3/K5: argument checks, grid sizing and launches behind the C ABI (include/wxddp.h).
+#include "mlp_kernels.cuh"
+
+namespace {
+using namespace wxk;
+
+grid_kernel_t pick_grid_kernel(int f, int mode, int loader, int* smem) {
+    switch ((f - 1) / 8) {
+        case 0: return pick_grid_kernel_g0(f, mode, loader, smem);
+        case 1: return pick_grid_kernel_g1(f, mode, loader, smem);
+        case 2: return pick_grid_kernel_g2(f, mode, loader, smem);
+        case 3: return pick_grid_kernel_g3(f, mode, loader, smem);
+        default: return nullptr;
+    }
+}
+small_kernel_t pick_small_kernel(int f, int* smem) {
+    switch ((f - 1) / 8) {
+        case 0: return pick_small_kernel_g0(f, smem);
+        case 1: return pick_small_kernel_g1(f, smem);
+        case 2: return pick_small_kernel_g2(f, smem);
+        case 3: return pick_small_kernel_g3(f, smem);
+        default: return nullptr;
+    }
+}
+
+int launch_grid(wx_ctx* ctx, GridArgs& a, int mode, cudaStream_t st, const char* who) {
+    const int f = ctx->desc.n_features;
+    int smem = 0;
+    grid_kernel_t k = pick_grid_kernel(f, mode, a.loader, &smem);
+    WX_CHECK_ARG(k != nullptr, "%s: no kernel for F=%d", who, f);
+    WX_CUDA(cudaSetDevice(ctx->device));
+    WX_CUDA(cudaFuncSetAttribute(reinterpret_cast<const void*>(k), cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    int occ = 0;
+    WX_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, reinterpret_cast<const void*>(k), THREADS, smem));
+    if (occ < 1) occ = 1;
+    const int64_t nchunks = (a.batch + R - 1) / R;
+    int64_t grid = (nchunks + WARPS - 1) / WARPS;
+    const int64_t cap = int64_t(ctx->num_sms) * occ;
+    if (grid > cap) grid = cap;
+    if (grid > WX_MAX_GRID_PARTS) grid = WX_MAX_GRID_PARTS;
+    if (grid < 1) grid = 1;
+    const size_t slab = (size_t(64) * f + 64 + 128 + 2 + 1 + 3) & ~size_t(3);
+    const size_t need = mode == MODE_TRAIN ? size_t(grid) * slab * 4 : size_t(grid) * 16;
+    if (WX_SCRATCH_PART_OFF + need > ctx->scratch_bytes) {
+        wx_set_error("%s: scratch too small (%zu needed)", who, need);
+        return WX_ENOMEM;
+    }
+    a.part = reinterpret_cast<float*>(ctx->scratch + WX_SCRATCH_PART_OFF);
+    a.ticket = reinterpret_cast<unsigned int*>(ctx->scratch) + (mode == MODE_TRAIN ? 1 : 2);
+    a.desc = ctx->desc;
+    void* args[] = {&a};
+    WX_CUDA(cudaLaunchKernel(reinterpret_cast<const void*>(k), dim3((unsigned)grid), dim3(THREADS), args, smem, st));
+    WX_LAUNCH_CHECK(ctx);
+    return WX_OK;
+}
+
+int check_dropout(int mode, const uint64_t* keep_mask, const char* who) {
+    WX_CHECK_ARG(mode == WX_DROPOUT_OFF || mode == WX_DROPOUT_MASK || mode == WX_DROPOUT_PHILOX, "%s: dropout_mode=%d",
+                 who, mode);
+    WX_CHECK_ARG(mode != WX_DROPOUT_MASK || keep_mask != nullptr, "%s: WX_DROPOUT_MASK needs keep_mask", who);
+    return WX_OK;
+}
+
+void zero_args(GridArgs& a) { memset(&a, 0, sizeof(a)); }
+
+}  // namespace
+
+extern "C" {
+
+int wx_mlp_grad(wx_ctx* ctx, const float* params, const float* x, const int64_t* y, const int64_t* row_idx,
+                int64_t row0, int64_t batch, int dropout_mode, const uint64_t* keep_mask, uint64_t seed, uint64_t step,
+                float scale, float* out, void* stream) {
+    WX_CHECK_ARG(ctx != nullptr, "wx_mlp_grad: ctx is NULL");
+    WX_CHECK_ARG(params && x && y && out, "wx_mlp_grad: NULL params/x/y/out");
+    WX_CHECK_ARG(batch >= 1, "wx_mlp_grad: batch=%lld must be >= 1", (long long)batch);
+    WX_CHECK_ARG(row_idx != nullptr || row0 >= 0, "wx_mlp_grad: row0 < 0");
+    int rc = check_dropout(dropout_mode, keep_mask, "wx_mlp_grad");
+    if (rc) return rc;
+    GridArgs a;
+    zero_args(a);
+    a.params = params;
+    a.loader = LOAD_ROWMAJOR;
+    a.x = x;
+    a.y = y;
+    a.row_idx = row_idx;
+    a.row0 = row0;
+    a.batch = batch;
+    a.dropout_mode = dropout_mode;
+    a.keep_mask = keep_mask;
+    a.seed = seed;
+    a.step = step;
+    a.scale = scale;
+    a.tail = TAIL_GRADS;
+    a.out = out;
+    return launch_grid(ctx, a, MODE_TRAIN, (cudaStream_t)stream, "wx_mlp_grad");
+}
+
+int wx_adam_step(wx_ctx* ctx, float* params, const float* grads, float* m, float* v, int64_t n, int64_t step,
+                 void* stream) {
+    WX_CHECK_ARG(ctx != nullptr, "wx_adam_step: ctx is NULL");
+    WX_CHECK_ARG(params && grads && m && v, "wx_adam_step: NULL pointer");
+    WX_CHECK_ARG(n >= 0 && step >= 1, "wx_adam_step: n=%lld step=%lld", (long long)n, (long long)step);
+    if (n == 0) return WX_OK;
+    WX_CUDA(cudaSetDevice(ctx->device));
+    const wx_model_desc& d = ctx->desc;
+    AdamScalars a;
+    const double bc1 = 1.0 - pow(d.beta1, double(step));
+    const double bc2 = 1.0 - pow(d.beta2, double(step));
+    a.w_lerp = float(1.0 - d.beta1);
+    a.beta2 = float(d.beta2);
+    a.one_m_beta2 = float(1.0 - d.beta2);
+    a.neg_step = float(-(d.lr / bc1));
+    a.bc2_sqrt = float(sqrt(bc2));
+    a.eps = float(d.eps);
+    const uintptr_t al = reinterpret_cast<uintptr_t>(params) | reinterpret_cast<uintptr_t>(grads) |
+                         reinterpret_cast<uintptr_t>(m) | reinterpret_cast<uintptr_t>(v);
+    const int vec_ok = (al & 15) == 0;
+    const int64_t work = vec_ok ? ((n + 3) >> 2) : n;
+    int64_t blocks = (work + 255) / 256;
+    const int64_t cap = int64_t(ctx->num_sms) * 8;
+    if (blocks > cap) blocks = cap;
+    adam_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(params, grads, m, v, n, a, vec_ok);
+    WX_LAUNCH_CHECK(ctx);
+    return WX_OK;
+}
+
+int wx_train_step(wx_ctx* ctx, float* params, float* m, float* v, int64_t* state, const float* x, const int64_t* y,
+                  const int64_t* row_idx, int64_t row0, int64_t batch, int dropout_mode, const uint64_t* keep_mask,
+                  uint64_t seed, float* loss_out, void* stream) {
+    WX_CHECK_ARG(ctx != nullptr, "wx_train_step: ctx is NULL");
+    WX_CHECK_ARG(params && m && v && state && x && y && loss_out, "wx_train_step: NULL pointer");
+    WX_CHECK_ARG(batch >= 1, "wx_train_step: batch=%lld must be >= 1", (long long)batch);
+    WX_CHECK_ARG(row_idx != nullptr || row0 >= 0, "wx_train_step: row0 < 0");
+    int rc = check_dropout(dropout_mode, keep_mask, "wx_train_step");
+    if (rc) return rc;
+    GridArgs a;
+    zero_args(a);
+    a.params = params;
+    a.loader = LOAD_ROWMAJOR;
+    a.x = x;
+    a.y = y;
+    a.row_idx = row_idx;
+    a.row0 = row0;
+    a.batch = batch;
+    a.dropout_mode = dropout_mode;
+    a.keep_mask = keep_mask;
+    a.seed = seed;
+    a.scale = 1.0f / float(batch);
+    a.tail = TAIL_ADAM;
+    a.p_rw = params;
+    a.m = m;
+    a.v = v;
+    a.state = state;
+    a.loss_out = loss_out;
+    return launch_grid(ctx, a, MODE_TRAIN, (cudaStream_t)stream, "wx_train_step");
+}
+
+int wx_train_step_raw(wx_ctx* ctx, float* params, float* m, float* v, int64_t* state, const void* const* cols,
+                      int dtype, const double* stats, int impute_mode, const int64_t* y, int64_t row0, int64_t batch,
+                      int dropout_mode, const uint64_t* keep_mask, uint64_t seed, float* loss_out, void* stream) {
+    WX_CHECK_ARG(ctx != nullptr, "wx_train_step_raw: ctx is NULL");
+    WX_CHECK_ARG(params && m && v && state && cols && stats && y && loss_out, "wx_train_step_raw: NULL pointer");
+    WX_CHECK_ARG(batch >= 1 && row0 >= 0, "wx_train_step_raw: batch=%lld row0=%lld", (long long)batch, (long long)row0);
+    WX_CHECK_ARG(dtype == WX_F32 || dtype == WX_F64, "wx_train_step_raw: dtype=%d", dtype);
+    WX_CHECK_ARG(impute_mode == WX_IMPUTE_NONE || impute_mode == WX_IMPUTE_MEAN, "wx_train_step_raw: impute_mode=%d",
+                 impute_mode);
+    int rc = check_dropout(dropout_mode, keep_mask, "wx_train_step_raw");
+    if (rc) return rc;
+    GridArgs a;
+    zero_args(a);
+    const int f = ctx->desc.n_features;
+    const size_t esz = dtype == WX_F32 ? 4 : 8;
+    for (int j = 0; j < f; ++j) {
+        WX_CHECK_ARG(cols[j] != nullptr && (reinterpret_cast<uintptr_t>(cols[j]) % esz) == 0,
+                     "wx_train_step_raw: column %d is NULL or misaligned", j);
+        a.cols.col[j] = cols[j];
+    }
+    a.params = params;
+    a.loader = dtype == WX_F32 ? LOAD_RAW_F32 : LOAD_RAW_F64;
+    a.stats = stats;
+    a.impute = impute_mode;
+    a.y = y;
+    a.row0 = row0;
+    a.batch = batch;
+    a.dropout_mode = dropout_mode;
+    a.keep_mask = keep_mask;
+    a.seed = seed;
+    a.scale = 1.0f / float(batch);
+    a.tail = TAIL_ADAM;
+    a.p_rw = params;
+    a.m = m;
+    a.v = v;
+    a.state = state;
+    a.loss_out = loss_out;
+    return launch_grid(ctx, a, MODE_TRAIN, (cudaStream_t)stream, "wx_train_step_raw");
+}
+
+int wx_train_steps_small(wx_ctx* ctx, float* params, float* m, float* v, int64_t* state, const float* x,
+                         const int64_t* y, const int64_t* row_idx, int64_t row0, int64_t batch, int64_t n_steps,
+                         int dropout_mode, const uint64_t* keep_mask, uint64_t seed, float* loss_out, void* stream) {
+    WX_CHECK_ARG(ctx != nullptr, "wx_train_steps_small: ctx is NULL");
+    WX_CHECK_ARG(params && m && v && state && x && y && loss_out, "wx_train_steps_small: NULL pointer");
+    WX_CHECK_ARG(batch >= 1 && batch <= WARPS * R, "wx_train_steps_small: batch=%lld outside 1..%d (use wx_train_step)",
+                 (long long)batch, WARPS * R);
+    WX_CHECK_ARG(n_steps >= 0, "wx_train_steps_small: n_steps < 0");
+    WX_CHECK_ARG(row_idx != nullptr || row0 >= 0, "wx_train_steps_small: row0 < 0");
+    int rc = check_dropout(dropout_mode, keep_mask, "wx_train_steps_small");
+    if (rc) return rc;
+    if (n_steps == 0) return WX_OK;
+    SmallArgs sa;
+    memset(&sa, 0, sizeof(sa));
+    sa.params = params;
+    sa.m = m;
+    sa.v = v;
+    sa.state = state;
+    sa.desc = ctx->desc;
+    sa.x = x;
+    sa.y = y;
+    sa.row_idx = row_idx;
+    sa.row0 = row0;
+    sa.batch = batch;
+    sa.n_steps = n_steps;
+    sa.dropout_mode = dropout_mode;
+    sa.keep_mask = keep_mask;
+    sa.seed = seed;
+    sa.loss_out = loss_out;
+    int smem = 0;
+    small_kernel_t k = pick_small_kernel(ctx->desc.n_features, &smem);
+    WX_CHECK_ARG(k != nullptr, "wx_train_steps_small: no kernel for F=%d", ctx->desc.n_features);
+    WX_CUDA(cudaSetDevice(ctx->device));
+    WX_CUDA(cudaFuncSetAttribute(reinterpret_cast<const void*>(k), cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    void* args[] = {&sa};
+    WX_CUDA(cudaLaunchKernel(reinterpret_cast<const void*>(k), dim3(1), dim3(THREADS), args, smem, (cudaStream_t)stream));
+    WX_LAUNCH_CHECK(ctx);
+    return WX_OK;
+}
+
+int wx_mlp_eval(wx_ctx* ctx, const float* params, const float* x, const int64_t* y, const int64_t* row_idx,
+                int64_t row0, int64_t batch, double* out, void* stream) {
+    WX_CHECK_ARG(ctx != nullptr, "wx_mlp_eval: ctx is NULL");
+    WX_CHECK_ARG(params && x && y && out, "wx_mlp_eval: NULL pointer");
+    WX_CHECK_ARG(batch >= 0, "wx_mlp_eval: batch < 0");
+    WX_CHECK_ARG(row_idx != nullptr || row0 >= 0, "wx_mlp_eval: row0 < 0");
+    if (batch == 0) {
+        WX_CUDA(cudaSetDevice(ctx->device));
+        WX_CUDA(cudaMemsetAsync(out, 0, 2 * sizeof(double), (cudaStream_t)stream));
+        return WX_OK;
+    }
+    GridArgs a;
+    zero_args(a);
+    a.params = params;
+    a.loader = LOAD_ROWMAJOR;
+    a.x = x;
+    a.y = y;
+    a.row_idx = row_idx;
+    a.row0 = row0;
+    a.batch = batch;
+    a.dropout_mode = WX_DROPOUT_OFF;
+    a.scale = 1.0f;
+    a.eval_out = out;
+    return launch_grid(ctx, a, MODE_EVAL, (cudaStream_t)stream, "wx_mlp_eval");
+}
+
+int wx_mlp_predict(wx_ctx* ctx, const float* params, const float* x, int64_t n, float* probs_out, void* stream) {
+    WX_CHECK_ARG(ctx != nullptr, "wx_mlp_predict: ctx is NULL");
+    WX_CHECK_ARG(n >= 0, "wx_mlp_predict: n < 0");
+    if (n == 0) return WX_OK;
+    WX_CHECK_ARG(params && x && probs_out, "wx_mlp_predict: NULL pointer");
+    GridArgs a;
+    zero_args(a);
+    a.params = params;
+    a.loader = LOAD_ROWMAJOR;
+    a.x = x;
+    a.y = nullptr;
+    a.row0 = 0;
+    a.batch = n;
+    a.dropout_mode = WX_DROPOUT_OFF;
+    a.scale = 1.0f;
+    a.probs_out = probs_out;
+    return launch_grid(ctx, a, MODE_PREDICT, (cudaStream_t)stream, "wx_mlp_predict");
+}
+
+}  // extern "C"

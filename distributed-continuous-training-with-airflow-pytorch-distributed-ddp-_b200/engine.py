@@ -1,0 +1,130 @@
+"""StepEngine: the user-facing training-step object (one per process / GPU).
+
+Holds the flat parameter vector, Adam moments and step counter on the device and drives the CUDA step
+kernels.  Mirrors what Lightning's automatic optimisation does around the reference's
+`training_step` (jobs/train_lightning_ddp.py:66-71) and `configure_optimizers` (:87-88): forward, loss,
+backward, gradient mean over ranks (DDP, :136), Adam, and the rank-mean `train_loss` (:70).
+"""
+from __future__ import annotations
+
+import torch
+
+from ._lib import DROPOUT_MASK, DROPOUT_OFF, DROPOUT_PHILOX, IMPUTE_MEAN, IMPUTE_NONE, WxError
+from .ops import Context, n_params
+
+
+def init_params_like_reference(n_features: int) -> torch.Tensor:
+    """Flat fp32 parameters drawn exactly as `WeatherClassifier(input_dim)` draws them (:57-62): two
+    nn.Linear default inits from the CURRENT global torch generator, in module order."""
+    from torch import nn
+
+    l1 = nn.Linear(n_features, 64)
+    l2 = nn.Linear(64, 2)
+    return torch.cat([l1.weight.detach().reshape(-1), l1.bias.detach(), l2.weight.detach().reshape(-1),
+                      l2.bias.detach()]).clone()
+
+
+class StepEngine:
+    def __init__(self, n_features: int, device=0, world: int = 1, rank: int = 0, process_group=None,
+                 params: torch.Tensor | None = None, seed: int = 42, lr: float = 0.01, dropout_p: float = 0.2):
+        self.ctx = Context(n_features, device=device, dropout_p=dropout_p, lr=lr)
+        self.device = self.ctx.device
+        self.F = n_features
+        self.P = n_params(n_features)
+        self.world, self.rank = world, rank
+        self.dist = process_group           # the torch.distributed module (NCCL) when world > 1
+        if world > 1 and process_group is None:
+            raise WxError("world > 1 needs an initialised torch.distributed (NCCL) handle")
+        if params is None:
+            params = init_params_like_reference(n_features)
+        self.params = params.detach().to(self.device, torch.float32).contiguous().clone()
+        self.m = torch.zeros(self.P, device=self.device)
+        self.v = torch.zeros(self.P, device=self.device)
+        self.state = torch.zeros(2, dtype=torch.int64, device=self.device)   # [steps done, reserved]
+        self.loss = torch.zeros(1, device=self.device)
+        self.bucket = torch.zeros(self.P + 1, device=self.device)            # grads + loss scalar (DDP bucket)
+        self.seed = seed
+        self.steps_done = 0
+        self.stats = None
+        self._stage = None
+        self._loss_host = torch.zeros(1).pin_memory() if torch.cuda.is_available() else torch.zeros(1)
+        if world > 1:
+            self.dist.broadcast(self.params, src=0)                          # C1: DDP's initial parameter broadcast
+
+    # ---- statistics ------------------------------------------------------------------------------
+    def set_stats(self, stats: torch.Tensor) -> None:
+        self.stats = stats
+
+    def fit_stats(self, cols) -> torch.Tensor:
+        """preprocess.py:32-36 over this rank's shard, Chan-merged across ranks."""
+        st = self.ctx.col_stats(cols)
+        if self.world > 1:
+            parts = [torch.empty_like(st) for _ in range(self.world)]
+            self.dist.all_gather(parts, st)
+            st = self.ctx.stats_merge(torch.stack(parts).contiguous())
+        self.stats = st
+        return st
+
+    # ---- steps -----------------------------------------------------------------------------------
+    def _dropout_seed(self) -> int:
+        # perf-mode streams are decorrelated across ranks; parity runs pass explicit masks instead
+        return (self.seed + 0x9E3779B97F4A7C15 * self.rank) & 0xFFFFFFFFFFFFFFFF
+
+    def step(self, x, y, *, row_idx=None, row0: int = 0, batch: int | None = None, dropout: int = DROPOUT_PHILOX,
+             keep_mask=None) -> torch.Tensor:
+        """One optimizer step on standardised row-major features.  Returns the device scalar `train_loss`."""
+        if self.world == 1:
+            self.ctx.train_step(self.params, self.m, self.v, self.state, x, y, self.loss, row_idx=row_idx, row0=row0,
+                                batch=batch, dropout=dropout, keep_mask=keep_mask, seed=self._dropout_seed())
+            self.steps_done += 1
+            return self.loss
+        b = batch if batch is not None else (row_idx.numel() if row_idx is not None else x.shape[0] - row0)
+        self.ctx.mlp_grad(self.params, x, y, row_idx=row_idx, row0=row0, batch=b, dropout=dropout, keep_mask=keep_mask,
+                          seed=self._dropout_seed(), step=self.steps_done, scale=1.0 / (self.world * b),
+                          out=self.bucket)
+        self.dist.all_reduce(self.bucket)                                    # C2 + C3 in one bucket
+        self.steps_done += 1
+        self.ctx.adam_step(self.params, self.bucket, self.m, self.v, self.steps_done, n=self.P)
+        return self.bucket[self.P:self.P + 1]
+
+    def step_raw(self, cols, y, *, row0: int = 0, batch: int | None = None, impute: int = IMPUTE_MEAN,
+                 dropout: int = DROPOUT_PHILOX, keep_mask=None) -> torch.Tensor:
+        """One optimizer step straight from raw columns (standardisation fused into the step kernel)."""
+        if self.stats is None:
+            raise WxError("call fit_stats()/set_stats() before step_raw()")
+        if self.world == 1:
+            self.ctx.train_step_raw(self.params, self.m, self.v, self.state, cols, self.stats, y, self.loss, row0=row0,
+                                    batch=batch, impute=impute, dropout=dropout, keep_mask=keep_mask,
+                                    seed=self._dropout_seed())
+            self.steps_done += 1
+            return self.loss
+        n = cols[0].numel()
+        b = batch if batch is not None else n - row0
+        feats, _ = self.ctx.normalize_pack([c[row0:row0 + b] for c in cols], self.stats, impute=impute,
+                                           want_nullmask=False)
+        return self.step(feats, y[row0:row0 + b].contiguous(), dropout=dropout, keep_mask=keep_mask)
+
+    def step_host(self, cols_host: torch.Tensor, y_host: torch.Tensor) -> float:
+        """End-to-end step from HOST buffers: H2D of the raw [F,B] fp32 columns and int64 labels (pinned memory
+        recommended), the fused step, and a D2H read of the loss.  Returns the loss as a Python float."""
+        f, b = cols_host.shape
+        if self._stage is None or self._stage[0].shape[1] != b:
+            self._stage = (torch.empty(f, b, dtype=torch.float32, device=self.device),
+                           torch.empty(b, dtype=torch.int64, device=self.device))
+        dc, dy = self._stage
+        dc.copy_(cols_host, non_blocking=True)
+        dy.copy_(y_host, non_blocking=True)
+        loss = self.step_raw([dc[j] for j in range(f)], dy, row0=0, batch=b)
+        self._loss_host.copy_(loss.reshape(1), non_blocking=True)
+        torch.cuda.current_stream(self.device).synchronize()
+        return float(self._loss_host.item())
+
+    def evaluate(self, x, y, *, row_idx=None, row0: int = 0, batch: int | None = None):
+        """validation pass (:73-85) over this rank's rows -> (val_loss, val_acc) as rank-weighted means (C4)."""
+        out = self.ctx.mlp_eval(self.params, x, y, row_idx=row_idx, row0=row0, batch=batch)
+        b = batch if batch is not None else (row_idx.numel() if row_idx is not None else x.shape[0] - row0)
+        tot = torch.cat([out, torch.tensor([float(b)], dtype=torch.float64, device=self.device)])
+        if self.world > 1:
+            self.dist.all_reduce(tot)
+        tot = tot.cpu()
+        return float(tot[0] / tot[2]), float(tot[1] / tot[2])

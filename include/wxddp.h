@@ -1,0 +1,181 @@
+/*
+ * wxddp.h -- C ABI of libwxddp.so: the B200 (sm_100a) implementation of the one data-parallel hot
+ * path of MustaphaMensouri/Distributed-Continuous-Training-with-Airflow-PyTorch-Distributed-DDP-:
+ * the training step of jobs/train_lightning_ddp.py plus the standardisation / label encoding of
+ * jobs/preprocess.py that feeds it.
+ *
+ * The reference has no FFI of its own (it is pure Python over torch / Lightning / Spark wheels);
+ * each entry point below names the reference lines whose arithmetic it replaces.  Citations are
+ * relative to /root/reference/jobs/.
+ *
+ * Conventions
+ *   - extern "C"; every call returns 0 (WX_OK) or a negative WX_E* code; wx_last_error() gives a
+ *     thread-local message.  Nothing throws, nothing calls exit().
+ *   - All tensors are CALLER-OWNED DEVICE pointers unless a parameter says "host".  They must stay
+ *     alive until the work queued on `stream` has completed.
+ *   - `stream` is a cudaStream_t passed as void* (NULL = the legacy default stream).  Launch
+ *     functions are asynchronous; none of them synchronises the device or allocates memory.
+ *   - wx_ctx is an opaque per-process / per-GPU object that owns only scratch memory (partial-sum
+ *     slabs, tickets).  One ctx per GPU; a ctx is not thread-safe; calls that share a ctx must be
+ *     ordered on one stream.
+ *   - Flat parameter layout (fp32, P = 64*F + 64 + 128 + 2 values), identical to the reference
+ *     module's state_dict order (train_lightning_ddp.py:57-62):
+ *         W1[64][F] (net.0.weight) | b1[64] (net.0.bias) | W2[2][64] (net.3.weight) | b2[2] (net.3.bias)
+ *   - There is no CPU fallback anywhere in this library.
+ */
+#ifndef WXDDP_H_
+#define WXDDP_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define WX_OK 0
+#define WX_EINVAL (-1)   /* bad argument (message says which) */
+#define WX_ECUDA (-2)    /* a CUDA runtime call failed */
+#define WX_ENOMEM (-3)   /* scratch too small for the request */
+#define WX_EARCH (-4)    /* device is not compute capability 10.x */
+
+#define WX_HIDDEN 64     /* train_lightning_ddp.py:58 */
+#define WX_CLASSES 2     /* train_lightning_ddp.py:61 */
+#define WX_MAX_FEATURES 32
+
+/* column element types accepted by the preprocessing kernels */
+#define WX_F32 0
+#define WX_F64 1
+
+/* null handling in wx_normalize_pack / wx_train_step_raw */
+#define WX_IMPUTE_NONE 0 /* reference behaviour: null stays null -> NaN feature (preprocess.py:38-41) */
+#define WX_IMPUTE_MEAN 1 /* extension: null -> column mean, i.e. 0.0f after standardisation */
+
+/* dropout source in the training step (train_lightning_ddp.py:60) */
+#define WX_DROPOUT_OFF 0    /* eval semantics */
+#define WX_DROPOUT_MASK 1   /* caller supplies keep bits: uint64 per row, bit j = keep hidden unit j */
+#define WX_DROPOUT_PHILOX 2 /* in-kernel Philox4x32-10 keyed by (seed, step, row, unit), p_keep = 52429/65536 */
+
+typedef struct wx_ctx wx_ctx;
+
+typedef struct wx_model_desc {
+    int32_t n_features; /* F, 1..32   (input_dim, train_lightning_ddp.py:52,125) */
+    int32_t hidden;     /* must be 64 (:58) */
+    int32_t classes;    /* must be 2  (:61) */
+    float dropout_p;    /* 0.2        (:60); only 0.2 and 0.0 are supported */
+    double lr;          /* 0.01       (:88) -- doubles, as torch holds them (Python floats) */
+    double beta1;       /* 0.9   torch.optim.Adam default used by :88 */
+    double beta2;       /* 0.999 */
+    double eps;         /* 1e-8 */
+} wx_model_desc;
+
+/* ---- library / context --------------------------------------------------------------------- */
+int wx_version(void);               /* 10000*major + 100*minor + patch */
+const char* wx_build_arch(void);    /* "sm_100a" */
+const char* wx_last_error(void);    /* thread-local, never NULL */
+
+/* Creates the per-GPU context on `device` and its scratch (one cudaMalloc, here and only here). */
+int wx_create(int device, const wx_model_desc* desc, wx_ctx** out);
+int wx_destroy(wx_ctx* ctx);
+int64_t wx_n_params(const wx_ctx* ctx);   /* P */
+int wx_num_sms(const wx_ctx* ctx);
+/* Number of kernels this context has launched since creation (bench.py's gpu_launches claim). */
+int64_t wx_launch_count(const wx_ctx* ctx);
+
+/* ---- K1: preprocessing (jobs/preprocess.py) ------------------------------------------------ */
+
+/* Label encode: labels_out[i] = 1 iff string i is valid and equals "rain" exactly, else 0.
+ * Replaces `when(col("Rain") == "rain", 1).otherwise(0)` (preprocess.py:23-25) and the int64 widening
+ * at train_lightning_ddp.py:46.  Strings are in Arrow utf8 layout: int32 offsets[n+1], byte data,
+ * optional LSB-first validity bitmap (NULL = all valid).  labels32_out may be NULL. */
+int wx_label_encode(wx_ctx* ctx, const int32_t* offsets, const uint8_t* data, const uint8_t* validity,
+                    int64_t n, int64_t* labels_out, int32_t* labels32_out, void* stream);
+
+/* Column statistics: for each of the F columns, over non-null rows, in float64:
+ *   stats_out[j] = { count, mean, M2 = sum (x-mean)^2, std_val }
+ * std_val = sqrt(M2/(count-1)) with the reference's zero guard (`std if std != 0 else 1.0`), NaN when
+ * count < 2 (Spark returns null there).  Replaces `df.select(mean(c), stddev(c)).first()` and the guard
+ * (preprocess.py:32-36) -- one pass over all columns instead of F Spark jobs.
+ * cols: HOST array of F DEVICE pointers to columns of `dtype`; a cell is null if it is NaN or if
+ * validity (HOST array of F device bitmaps, or NULL, entries may be NULL) has its bit clear. */
+int wx_col_stats(wx_ctx* ctx, const void* const* cols, int dtype, const uint8_t* const* validity,
+                 int64_t n, double* stats_out /* device [F][4] */, void* stream);
+
+/* Chan merge of per-shard statistics (multi-GPU: all-gather the [F][4] blocks, then merge in rank
+ * order).  parts: device [n_parts][F][4]; out: device [F][4], std_val recomputed.  SURVEY 8(e). */
+int wx_stats_merge(wx_ctx* ctx, const double* parts, int n_parts, double* out, void* stream);
+
+/* Standardise + pack: features_out[i][j] = (float)((double)col_j[i] - mean_j) / std_val_j), row-major
+ * fp32 [n][F] -- exactly what WeatherDataset.features holds after preprocess.py:38-41 and the cast at
+ * train_lightning_ddp.py:45.  Nulls: WX_IMPUTE_NONE -> NaN, WX_IMPUTE_MEAN -> 0.0f.
+ * nullmask_out (may be NULL): uint32 per row, bit j set <=> feature j was null. */
+int wx_normalize_pack(wx_ctx* ctx, const void* const* cols, int dtype, const uint8_t* const* validity,
+                      int64_t n, const double* stats /* device [F][4] */, int impute_mode,
+                      float* features_out, uint32_t* nullmask_out, void* stream);
+
+/* Ascending flat indices (row*F + col) of every null cell recorded in nullmask -- the "imputation
+ * indices" of the north star.  idx_out has room for `capacity` entries; *count_out (device) receives
+ * the total number of null cells even when it exceeds capacity (then only the first `capacity` are
+ * written).  No counterpart in the reference (it never imputes); defined by oracle/preprocess_ref.py. */
+int wx_impute_index_list(wx_ctx* ctx, const uint32_t* nullmask, int64_t n, int64_t* idx_out,
+                         int64_t capacity, int64_t* count_out, void* stream);
+
+/* ---- K2/K3/K5: the training step (jobs/train_lightning_ddp.py) ------------------------------- */
+
+/* Forward + cross-entropy + backward over one local batch, gradients only (no update).
+ * Replaces WeatherClassifier.forward / training_step and autograd's backward (:57-71).
+ *   x: fp32 row-major [*, F] (WeatherDataset.features, :45); y: int64 labels (:46).
+ *   Rows of the batch: row_idx[0..batch) if row_idx != NULL (the sampler's indices), else
+ *   row0, row0+1, ..., row0+batch-1.
+ *   keep_mask: [batch] uint64 for WX_DROPOUT_MASK (bit j of entry b keeps unit j of batch row b).
+ *   out[0..P) = scale * sum_rows d(loss_row)/d(param); out[P] = scale * sum_rows loss_row.
+ * With scale = 1/batch this is the mean loss and its gradient; under DDP pass 1/(W*batch) and SUM
+ * across ranks (what torch's reducer does at :136). */
+int wx_mlp_grad(wx_ctx* ctx, const float* params, const float* x, const int64_t* y,
+                const int64_t* row_idx, int64_t row0, int64_t batch, int dropout_mode,
+                const uint64_t* keep_mask, uint64_t seed, uint64_t step, float scale,
+                float* out /* device [P+1] */, void* stream);
+
+/* Adam update of a flat fp32 vector, torch.optim.Adam semantics with the desc's hyper-parameters
+ * (:88; torch/optim/adam.py _single_tensor_adam).  step is 1-based.  grads may hold extra trailing
+ * values (they are ignored).  Also the stand-alone HBM-bound K3 for long vectors (28 B/param). */
+int wx_adam_step(wx_ctx* ctx, float* params, const float* grads, float* m, float* v, int64_t n,
+                 int64_t step, void* stream);
+
+/* One optimizer step in ONE launch: wx_mlp_grad + grid reduction + Adam in the kernel's tail.
+ * state: device int64[2] = { step counter (number of completed steps), reserved }; the tail
+ * increments it, so the call can be replayed from a CUDA graph.  loss_out: device fp32, receives
+ * the batch-mean loss (`train_loss`, :70).  Single-GPU form of :66-71 + :88. */
+int wx_train_step(wx_ctx* ctx, float* params, float* m, float* v, int64_t* state, const float* x,
+                  const int64_t* y, const int64_t* row_idx, int64_t row0, int64_t batch,
+                  int dropout_mode, const uint64_t* keep_mask, uint64_t seed, float* loss_out,
+                  void* stream);
+
+/* Same step, but reading RAW columnar features and standardising in registers on the way in
+ * (preprocess.py:38-41 fused in front of train_lightning_ddp.py:66-71,:88): rows row0..row0+batch of
+ * F columns of `dtype`, stats from wx_col_stats.  Nulls (NaN cells) follow impute_mode. */
+int wx_train_step_raw(wx_ctx* ctx, float* params, float* m, float* v, int64_t* state,
+                      const void* const* cols, int dtype, const double* stats, int impute_mode,
+                      const int64_t* y, int64_t row0, int64_t batch, int dropout_mode,
+                      const uint64_t* keep_mask, uint64_t seed, float* loss_out, void* stream);
+
+/* Many tiny optimizer steps in one launch (the reference's regime: batch 4, :122): a single resident
+ * CTA runs steps s = 0..n_steps-1 over rows row_idx[s*batch .. (s+1)*batch) (or row0 + s*batch ...),
+ * forward/backward/Adam each, writing loss_out[s].  keep_mask is [n_steps*batch]. */
+int wx_train_steps_small(wx_ctx* ctx, float* params, float* m, float* v, int64_t* state,
+                         const float* x, const int64_t* y, const int64_t* row_idx, int64_t row0,
+                         int64_t batch, int64_t n_steps, int dropout_mode, const uint64_t* keep_mask,
+                         uint64_t seed, float* loss_out /* [n_steps] */, void* stream);
+
+/* Validation pass (validation_step, :73-85): eval-mode forward over the given rows.
+ * out: device double[2] = { sum of per-row cross-entropy, number of rows with argmax == label }. */
+int wx_mlp_eval(wx_ctx* ctx, const float* params, const float* x, const int64_t* y,
+                const int64_t* row_idx, int64_t row0, int64_t batch, double* out, void* stream);
+
+/* Inference forward (score.py run(), dags/azure_auto_deploy.py:99-103): probs_out[i][c] = softmax. */
+int wx_mlp_predict(wx_ctx* ctx, const float* params, const float* x, int64_t n, float* probs_out,
+                   void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* WXDDP_H_ */
