@@ -40,7 +40,8 @@ def _source_digest() -> str:
             h.update(name.encode())
             with open(path, "rb") as fh:
                 h.update(fh.read())
-    h.update(" ".join(NVCC_FLAGS).encode())
+    # flags without the absolute -I paths, so the stamp stays valid when the tree is copied elsewhere
+    h.update(" ".join(fl for fl in NVCC_FLAGS if not fl.startswith("-I")).encode())
     return h.hexdigest()
 
 

@@ -54,7 +54,8 @@ int launch_grid(wx_ctx* ctx, GridArgs& a, int mode, cudaStream_t st, const char*
     return WX_OK;
 }
 
-int check_dropout(int mode, const uint64_t* keep_mask, const char* who) {
+int check_dropout(const wx_ctx* ctx, int& mode, const uint64_t* keep_mask, const char* who) {
+    if (ctx->desc.dropout_p == 0.0f) mode = WX_DROPOUT_OFF;   // a model built without dropout never drops
     WX_CHECK_ARG(mode == WX_DROPOUT_OFF || mode == WX_DROPOUT_MASK || mode == WX_DROPOUT_PHILOX, "%s: dropout_mode=%d",
                  who, mode);
     WX_CHECK_ARG(mode != WX_DROPOUT_MASK || keep_mask != nullptr, "%s: WX_DROPOUT_MASK needs keep_mask", who);
@@ -74,7 +75,7 @@ int wx_mlp_grad(wx_ctx* ctx, const float* params, const float* x, const int64_t*
     WX_CHECK_ARG(params && x && y && out, "wx_mlp_grad: NULL params/x/y/out");
     WX_CHECK_ARG(batch >= 1, "wx_mlp_grad: batch=%lld must be >= 1", (long long)batch);
     WX_CHECK_ARG(row_idx != nullptr || row0 >= 0, "wx_mlp_grad: row0 < 0");
-    int rc = check_dropout(dropout_mode, keep_mask, "wx_mlp_grad");
+    int rc = check_dropout(ctx, dropout_mode, keep_mask, "wx_mlp_grad");
     if (rc) return rc;
     GridArgs a;
     zero_args(a);
@@ -131,7 +132,7 @@ int wx_train_step(wx_ctx* ctx, float* params, float* m, float* v, int64_t* state
     WX_CHECK_ARG(params && m && v && state && x && y && loss_out, "wx_train_step: NULL pointer");
     WX_CHECK_ARG(batch >= 1, "wx_train_step: batch=%lld must be >= 1", (long long)batch);
     WX_CHECK_ARG(row_idx != nullptr || row0 >= 0, "wx_train_step: row0 < 0");
-    int rc = check_dropout(dropout_mode, keep_mask, "wx_train_step");
+    int rc = check_dropout(ctx, dropout_mode, keep_mask, "wx_train_step");
     if (rc) return rc;
     GridArgs a;
     zero_args(a);
@@ -164,7 +165,7 @@ int wx_train_step_raw(wx_ctx* ctx, float* params, float* m, float* v, int64_t* s
     WX_CHECK_ARG(dtype == WX_F32 || dtype == WX_F64, "wx_train_step_raw: dtype=%d", dtype);
     WX_CHECK_ARG(impute_mode == WX_IMPUTE_NONE || impute_mode == WX_IMPUTE_MEAN, "wx_train_step_raw: impute_mode=%d",
                  impute_mode);
-    int rc = check_dropout(dropout_mode, keep_mask, "wx_train_step_raw");
+    int rc = check_dropout(ctx, dropout_mode, keep_mask, "wx_train_step_raw");
     if (rc) return rc;
     GridArgs a;
     zero_args(a);
@@ -204,7 +205,7 @@ int wx_train_steps_small(wx_ctx* ctx, float* params, float* m, float* v, int64_t
                  (long long)batch, WARPS * R);
     WX_CHECK_ARG(n_steps >= 0, "wx_train_steps_small: n_steps < 0");
     WX_CHECK_ARG(row_idx != nullptr || row0 >= 0, "wx_train_steps_small: row0 < 0");
-    int rc = check_dropout(dropout_mode, keep_mask, "wx_train_steps_small");
+    int rc = check_dropout(ctx, dropout_mode, keep_mask, "wx_train_steps_small");
     if (rc) return rc;
     if (n_steps == 0) return WX_OK;
     SmallArgs sa;

@@ -192,6 +192,7 @@ __global__ void __launch_bounds__(THREADS) mlp_grid_kernel(const GridArgs a) {
     st.zero_grads();
 
     const uint64_t step_word = (a.state != nullptr) ? uint64_t(a.state[0]) : a.step;
+    const float drop_scale = (a.dropout_mode == WX_DROPOUT_OFF) ? 1.0f : 1.25f;
     const uint2 key = make_uint2(uint32_t(a.seed), uint32_t(a.seed >> 32));
 
     const int64_t nchunks = (a.batch + R - 1) / R;
@@ -224,7 +225,7 @@ __global__ void __launch_bounds__(THREADS) mlp_grid_kernel(const GridArgs a) {
         uint32_t keepbits = 0xffffu;
         if (MODE == MODE_TRAIN)
             keepbits = chunk_keep_bits(a.dropout_mode, cur, lane, c * R, key, uint32_t(step_word), uint32_t(step_word >> 32));
-        process_chunk<F, MODE>(st, xs, cur, keepbits, a.scale, lane, a.probs_out);
+        process_chunk<F, MODE>(st, xs, cur, keepbits, drop_scale, a.scale, lane, a.probs_out);
         __syncwarp();
         buf ^= 1;
     }
@@ -441,7 +442,8 @@ __global__ void __launch_bounds__(THREADS, 1) mlp_small_steps_kernel(const Small
             const uint64_t step_word = uint64_t(step0 + s);
             const uint32_t keepbits = chunk_keep_bits(sa.dropout_mode, cur, lane, int64_t(warp) * R, key,
                                                       uint32_t(step_word), uint32_t(step_word >> 32));
-            process_chunk<F, MODE_TRAIN>(st, stg0 + buf * R * D::FS, cur, keepbits, scale, lane, nullptr);
+            process_chunk<F, MODE_TRAIN>(st, stg0 + buf * R * D::FS, cur, keepbits,
+                                         (sa.dropout_mode == WX_DROPOUT_OFF) ? 1.0f : 1.25f, scale, lane, nullptr);
             // fold into the slab in warp order
             for (int w = 0; w < nchunks; ++w) {
                 if (warp == w) st.flush_to_slab(slab, lane, w == 0);

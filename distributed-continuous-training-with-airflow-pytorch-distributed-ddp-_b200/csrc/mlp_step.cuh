@@ -217,11 +217,14 @@ __device__ __forceinline__ uint32_t chunk_keep_bits(int mode, const ChunkMeta& c
 //   MODE: 0 = train (grads), 1 = eval (loss sum + correct), 2 = predict (probs written to probs_out)
 template <int F, int MODE>
 __device__ __forceinline__ void process_chunk(LaneState<F>& st, const float* __restrict__ xs, const ChunkMeta& cm,
-                                              uint32_t keepbits, float scale, int lane, float* probs_out) {
+                                              uint32_t keepbits, float drop_scale, float scale, int lane,
+                                              float* probs_out) {
     using D = Dim<F>;
     float aa[R], ab[R];
     float v[2 * R];
-    constexpr float DROP_SCALE = 1.25f;   // 1/(1-0.2): ATen's noise.div_(1-p), train_lightning_ddp.py:60
+    // drop_scale: 1.25f = 1/(1-0.2) when dropout is active (ATen's noise.div_(1-p), train_lightning_ddp.py:60),
+    // 1.0f when it is off (eval semantics / dropout_p == 0)
+    const float DROP_SCALE = drop_scale;
 #pragma unroll
     for (int r = 0; r < R; ++r) {
         // keep the scheduler from hoisting every row's LDS.128 to the top (register pressure): rows are

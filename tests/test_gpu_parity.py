@@ -165,7 +165,7 @@ def test_normalize_pack_bit_exact_given_stats(wx, f, n, dtype, impute):
     assert got.shape == (n, f) and got.dtype == np.float32
     np.testing.assert_array_equal(np.isnan(got), np.isnan(want["features"]))
     ok = ~np.isnan(want["features"])
-    if impute:
+    if impute and n > 1:
         assert ok.all()
     np.testing.assert_array_equal(got[ok].view(np.uint32), want["features"][ok].view(np.uint32))
     np.testing.assert_array_equal(nm.cpu().numpy().view(np.uint32), want["nullmask"])
