@@ -37,7 +37,7 @@ def _source_digest() -> str:
     for name in files:
         path = name if os.path.isabs(name) else os.path.join(CSRC, name)
         if os.path.isfile(path) and path.endswith((".cu", ".cuh", ".h")):
-            h.update(name.encode())
+            h.update(os.path.basename(name).encode())
             with open(path, "rb") as fh:
                 h.update(fh.read())
     # flags without the absolute -I paths, so the stamp stays valid when the tree is copied elsewhere
