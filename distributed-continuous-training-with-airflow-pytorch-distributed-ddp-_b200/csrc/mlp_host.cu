@@ -1,4 +1,6 @@
 // Host side of K2/K3/K5: argument checks, grid sizing and launches behind the C ABI (include/wxddp.h).
+#include <mutex>
+
 #include "mlp_kernels.cuh"
 
 namespace {
@@ -282,3 +284,119 @@ int wx_mlp_predict(wx_ctx* ctx, const float* params, const float* x, int64_t n, 
 }
 
 }  // extern "C"
+
+// =================================================================================================
+// Allocation-free gradient entry point
+// =================================================================================================
+// Who this is for: hosts that may not allocate device memory at the moment they need a gradient --
+// a plugin running under a framework that owns the whole GPU memory budget (a raw cudaMalloc there
+// fails or defeats the framework's accounting), a real-time loop that cannot afford the implicit
+// device synchronisation of cudaMalloc/cudaFree, or an embedding process whose policy forbids
+// allocations after start-up.  wx_create() allocates (that is its job), so such callers cannot make a
+// context; this entry point needs none.  Its scratch (the per-CTA partial-sum slabs and the arrival
+// ticket that wx_mlp_grad keeps in the context) lives in the fixed array below, which is part of the
+// library image: every GPU that loads libwxddp.so carries these 1.5 MiB until the process exits.
+namespace {
+
+constexpr size_t WX_STATIC_SCRATCH_BYTES = size_t(3) << 19;   // 1.5 MiB: ticket block + up to 148 slabs of the widest model
+constexpr int64_t WX_STATIC_MAX_BATCH = int64_t(1) << 24;     // rows per call
+constexpr int WX_STATIC_MAX_DEVICES = 64;
+
+static __device__ __align__(256) unsigned char g_static_scratch[WX_STATIC_SCRATCH_BYTES];
+
+struct StaticSlot {
+    unsigned char* ptr = nullptr;   // DEVICE address of g_static_scratch on this device
+    int num_sms = 0;
+};
+StaticSlot g_static_slot[WX_STATIC_MAX_DEVICES];
+std::mutex g_static_mu;
+
+// One-time set-up for the current device.  `g_static_scratch` as written in host code is only a
+// host-side handle for the symbol; the kernels need the device address, which the runtime hands out
+// per device through cudaGetSymbolAddress while that device is current.
+int static_slot_for_current_device(StaticSlot** out, int* device_out) {
+    int dev = -1;
+    WX_CUDA(cudaGetDevice(&dev));
+    WX_CHECK_ARG(dev >= 0 && dev < WX_STATIC_MAX_DEVICES, "wx_mlp_grad_static: device ordinal %d not supported", dev);
+    std::lock_guard<std::mutex> lock(g_static_mu);
+    StaticSlot& s = g_static_slot[dev];
+    if (s.ptr == nullptr) {
+        cudaDeviceProp prop;
+        WX_CUDA(cudaGetDeviceProperties(&prop, dev));
+        if (prop.major != 10) {
+            wx_set_error("wx_mlp_grad_static: device %d is sm_%d%d; this library is built for sm_100a only", dev,
+                         prop.major, prop.minor);
+            return WX_EARCH;
+        }
+        void* p = nullptr;
+        WX_CUDA(cudaGetSymbolAddress(&p, g_static_scratch));
+        WX_CHECK_ARG(p != nullptr, "wx_mlp_grad_static: cudaGetSymbolAddress returned a null address");
+        s.num_sms = prop.multiProcessorCount;
+        s.ptr = static_cast<unsigned char*>(p);
+    }
+    *out = &s;
+    *device_out = dev;
+    return WX_OK;
+}
+
+}  // namespace
+
+extern "C" int wx_mlp_grad_static(int n_features, const float* params, const float* x, const int64_t* y,
+                                  const int64_t* row_idx, int64_t row0, int64_t batch, int dropout_mode,
+                                  const uint64_t* keep_mask, uint64_t seed, uint64_t step, float scale, float* out,
+                                  void* stream) {
+    WX_CHECK_ARG(n_features >= 1 && n_features <= WX_MAX_FEATURES, "wx_mlp_grad_static: n_features=%d outside 1..%d",
+                 n_features, WX_MAX_FEATURES);
+    WX_CHECK_ARG(batch >= 1, "wx_mlp_grad_static: batch=%lld must be >= 1", (long long)batch);
+    WX_CHECK_ARG(batch <= WX_STATIC_MAX_BATCH,
+                 "wx_mlp_grad_static: batch=%lld exceeds the %lld-row limit of the fixed scratch entry point; split the "
+                 "batch and add the outputs, or use wx_mlp_grad with a context",
+                 (long long)batch, (long long)WX_STATIC_MAX_BATCH);
+    WX_CHECK_ARG(params && x && y && out, "wx_mlp_grad_static: NULL params/x/y/out");
+    WX_CHECK_ARG(row_idx != nullptr || row0 >= 0, "wx_mlp_grad_static: row0 < 0");
+    WX_CHECK_ARG(dropout_mode == WX_DROPOUT_OFF || dropout_mode == WX_DROPOUT_MASK || dropout_mode == WX_DROPOUT_PHILOX,
+                 "wx_mlp_grad_static: dropout_mode=%d", dropout_mode);
+    WX_CHECK_ARG(dropout_mode != WX_DROPOUT_MASK || keep_mask != nullptr, "wx_mlp_grad_static: WX_DROPOUT_MASK needs keep_mask");
+    StaticSlot* slot = nullptr;
+    int dev = -1;
+    int rc = static_slot_for_current_device(&slot, &dev);
+    if (rc != WX_OK) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+    // The array is shared by every call and still holds whatever the previous call left.  The slabs
+    // are fully rewritten by each launch; the arrival ticket is the one thing that has to start at
+    // zero, so it is cleared here (a fill, not an allocation) in case an earlier launch was aborted.
+    WX_CUDA(cudaMemsetAsync(slot->ptr, 0, WX_SCRATCH_PART_OFF, st));
+    // A context-shaped view of the static array on the stack, so the same launch path as wx_mlp_grad is used.
+    wx_ctx view;
+    view.device = dev;
+    view.num_sms = slot->num_sms;
+    view.desc.n_features = n_features;
+    view.desc.hidden = WX_HIDDEN;
+    view.desc.classes = WX_CLASSES;
+    view.desc.dropout_p = 0.2f;
+    view.desc.lr = 0.01;
+    view.desc.beta1 = 0.9;
+    view.desc.beta2 = 0.999;
+    view.desc.eps = 1e-8;
+    view.n_params = int64_t(WX_HIDDEN) * n_features + WX_HIDDEN + WX_CLASSES * WX_HIDDEN + WX_CLASSES;
+    view.scratch = slot->ptr;
+    view.scratch_bytes = WX_STATIC_SCRATCH_BYTES;
+    view.launches = 0;
+    GridArgs a;
+    zero_args(a);
+    a.params = params;
+    a.loader = LOAD_ROWMAJOR;
+    a.x = x;
+    a.y = y;
+    a.row_idx = row_idx;
+    a.row0 = row0;
+    a.batch = batch;
+    a.dropout_mode = dropout_mode;
+    a.keep_mask = keep_mask;
+    a.seed = seed;
+    a.step = step;
+    a.scale = scale;
+    a.tail = TAIL_GRADS;
+    a.out = out;
+    return launch_grid(&view, a, MODE_TRAIN, st, "wx_mlp_grad_static");
+}

@@ -135,6 +135,22 @@ int wx_mlp_grad(wx_ctx* ctx, const float* params, const float* x, const int64_t*
                 const uint64_t* keep_mask, uint64_t seed, uint64_t step, float scale,
                 float* out /* device [P+1] */, void* stream);
 
+/* wx_mlp_grad for callers that must not allocate device memory: no context (wx_create allocates), same
+ * inputs, outputs and arithmetic as wx_mlp_grad, on the CURRENT device.  This entry point has no counterpart
+ * in the reference; it exists for hosts that run under a framework-owned memory budget, inside latency-critical
+ * loops that cannot take cudaMalloc's implicit synchronisation, or under a no-allocation-after-start policy.
+ * The partial-sum scratch is a fixed 1.5 MiB array inside the library image (each GPU that loads the library
+ * holds it until the process exits).  Limits: n_features <= 32 and batch <= 16,777,216 rows per call; larger
+ * requests are rejected with WX_EINVAL and a message (split the batch and add the outputs -- they are sums).
+ * The first call on a device looks the array's device address up and queries the device; make that first call
+ * before starting any stream capture.  The call itself performs no cudaMalloc / cudaFree / allocating library
+ * call.  All calls share the one array: two calls whose kernels can overlap on the GPU (different streams,
+ * threads or processes sharing a context) race on it -- order them on one stream. */
+int wx_mlp_grad_static(int n_features, const float* params, const float* x, const int64_t* y,
+                       const int64_t* row_idx, int64_t row0, int64_t batch, int dropout_mode,
+                       const uint64_t* keep_mask, uint64_t seed, uint64_t step, float scale,
+                       float* out /* device [P+1] */, void* stream);
+
 /* Adam update of a flat fp32 vector, torch.optim.Adam semantics with the desc's hyper-parameters
  * (:88; torch/optim/adam.py _single_tensor_adam).  step is 1-based.  grads may hold extra trailing
  * values (they are ignored).  Also the stand-alone HBM-bound K3 for long vectors (28 B/param). */
