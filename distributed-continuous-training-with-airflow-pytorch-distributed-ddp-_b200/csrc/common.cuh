@@ -26,6 +26,7 @@ struct wx_ctx {
     unsigned char* scratch;      // device
     size_t scratch_bytes;
     int64_t launches;
+    long long* debug_times;   // optional device buffer [grid][4]: smid, t_start, t_loop_end, t_exit (globaltimer ns)
 };
 
 void wx_set_error(const char* fmt, ...);

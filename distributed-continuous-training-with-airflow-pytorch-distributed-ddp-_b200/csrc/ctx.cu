@@ -45,6 +45,7 @@ int wx_create(int device, const wx_model_desc* desc, wx_ctx** out) {
     c->n_params = int64_t(WX_HIDDEN) * desc->n_features + WX_HIDDEN + WX_CLASSES * WX_HIDDEN + WX_CLASSES;
     c->scratch_bytes = WX_SCRATCH_BYTES;
     c->launches = 0;
+    c->debug_times = nullptr;
     cudaError_t e = cudaMalloc(&c->scratch, c->scratch_bytes);
     if (e != cudaSuccess) {
         wx_set_error("wx_create: cudaMalloc(%zu) failed: %s", c->scratch_bytes, cudaGetErrorString(e));
@@ -73,5 +74,11 @@ int wx_destroy(wx_ctx* ctx) {
 int64_t wx_n_params(const wx_ctx* ctx) { return ctx ? ctx->n_params : -1; }
 int wx_num_sms(const wx_ctx* ctx) { return ctx ? ctx->num_sms : -1; }
 int64_t wx_launch_count(const wx_ctx* ctx) { return ctx ? ctx->launches : -1; }
+
+int wx_debug_cta_times(wx_ctx* ctx, long long* device_buf) {
+    if (!ctx) return WX_EINVAL;
+    ctx->debug_times = device_buf;
+    return WX_OK;
+}
 
 }  // extern "C"

@@ -50,6 +50,7 @@ int launch_grid(wx_ctx* ctx, GridArgs& a, int mode, cudaStream_t st, const char*
     a.part = reinterpret_cast<float*>(ctx->scratch + WX_SCRATCH_PART_OFF);
     a.ticket = reinterpret_cast<unsigned int*>(ctx->scratch) + (mode == MODE_TRAIN ? 1 : 2);
     a.desc = ctx->desc;
+    a.dbg = ctx->debug_times;
     void* args[] = {&a};
     WX_CUDA(cudaLaunchKernel(reinterpret_cast<const void*>(k), dim3((unsigned)grid), dim3(THREADS), args, smem, st));
     WX_LAUNCH_CHECK(ctx);
@@ -382,6 +383,7 @@ extern "C" int wx_mlp_grad_static(int n_features, const float* params, const flo
     view.scratch = slot->ptr;
     view.scratch_bytes = WX_STATIC_SCRATCH_BYTES;
     view.launches = 0;
+    view.debug_times = nullptr;
     GridArgs a;
     zero_args(a);
     a.params = params;

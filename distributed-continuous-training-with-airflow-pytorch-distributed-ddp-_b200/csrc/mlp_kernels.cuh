@@ -47,6 +47,7 @@ struct GridArgs {
     int64_t* state;
     float* loss_out;
     double* eval_out;       // MODE_EVAL: [2]
+    long long* dbg;         // optional per-CTA timestamps (wx_debug_cta_times)
     float* probs_out;       // MODE_PREDICT
 };
 
@@ -187,6 +188,14 @@ __global__ void __launch_bounds__(THREADS) mlp_grid_kernel(const GridArgs a) {
         __syncthreads();
     }
 
+    if (a.dbg != nullptr && tid == 0) {
+        unsigned smid;
+        long long t;
+        asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        a.dbg[blockIdx.x * 4 + 0] = smid;
+        a.dbg[blockIdx.x * 4 + 1] = t;
+    }
     LaneState<F> st;
     st.load_weights(a.params, lane);
     st.zero_grads();
@@ -233,6 +242,14 @@ __global__ void __launch_bounds__(THREADS) mlp_grid_kernel(const GridArgs a) {
     if (MODE == MODE_PREDICT) return;
 
     __shared__ bool s_last;
+    if (a.dbg != nullptr) {
+        __syncthreads();
+        if (tid == 0) {
+            long long t;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+            a.dbg[blockIdx.x * 4 + 2] = t;
+        }
+    }
     __shared__ AdamScalars s_adam;
     __syncthreads();   // staging memory is dead from here on; the slab aliases it
 
@@ -285,32 +302,67 @@ __global__ void __launch_bounds__(THREADS) mlp_grid_kernel(const GridArgs a) {
     __syncthreads();
     if (tid == 0) s_last = atomicAdd(a.ticket, 1u) == gridDim.x - 1;
     __syncthreads();
+    if (a.dbg != nullptr && tid == 0) {
+        long long t;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        a.dbg[blockIdx.x * 4 + 3] = t;
+    }
     if (!s_last) return;
     __threadfence();
 
     // last CTA: sum the slabs in CTA order, then either publish grads or apply Adam in place
     if (a.tail == TAIL_ADAM && tid == 0) s_adam = adam_scalars(a.desc, a.state[0] + 1);
     __syncthreads();
+    // Each thread owns up to GPT groups of 4 consecutive outputs and walks the slabs in CTA order with
+    // independent 128-bit loads in flight (the order per element is b = 0,1,2,... -> deterministic).
     const unsigned nparts = gridDim.x;
-    for (int i = tid; i < D::P + 1; i += THREADS) {
-        float s = 0.0f;
-        const float* q = a.part + i;
+    constexpr int NG = D::SLAB / 4;
+    constexpr int GPT = (NG + THREADS - 1) / THREADS;
+    float4 acc[GPT];
+#pragma unroll
+    for (int k = 0; k < GPT; ++k) acc[k] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+    const float4* q4 = reinterpret_cast<const float4*>(a.part);
 #pragma unroll 8
-        for (unsigned b = 0; b < nparts; ++b) s += __ldcg(q + size_t(b) * D::SLAB);
-        if (i == D::P) s *= a.scale;   // loss: rows were summed unscaled
-        if (a.tail == TAIL_GRADS) {
-            a.out[i] = s;
-        } else if (i < D::P) {
-            float p = a.p_rw[i], m = a.m[i], v = a.v[i];
-            adam_apply(p, s, m, v, s_adam);
-            a.p_rw[i] = p;
-            a.m[i] = m;
-            a.v[i] = v;
-        } else {
-            *a.loss_out = s;
+    for (unsigned b = 0; b < nparts; ++b) {
+#pragma unroll
+        for (int k = 0; k < GPT; ++k) {
+            int g = tid + k * THREADS;
+            g = g < NG ? g : NG - 1;          // surplus threads re-read the last group (branch-free, result unused)
+            const float4 t = __ldcg(q4 + size_t(b) * NG + g);
+            acc[k].x += t.x;
+            acc[k].y += t.y;
+            acc[k].z += t.z;
+            acc[k].w += t.w;
+        }
+    }
+#pragma unroll
+    for (int k = 0; k < GPT; ++k) {
+        const float vals[4] = {acc[k].x, acc[k].y, acc[k].z, acc[k].w};
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+            const int i = 4 * (tid + k * THREADS) + e;
+            if (i > D::P) continue;
+            float s = vals[e];
+            if (i == D::P) s *= a.scale;   // loss: rows were summed unscaled
+            if (a.tail == TAIL_GRADS) {
+                a.out[i] = s;
+            } else if (i < D::P) {
+                float p = a.p_rw[i], m = a.m[i], v = a.v[i];
+                adam_apply(p, s, m, v, s_adam);
+                a.p_rw[i] = p;
+                a.m[i] = m;
+                a.v[i] = v;
+            } else {
+                *a.loss_out = s;
+            }
         }
     }
     if (tid == 0) {
+        if (a.dbg != nullptr) {
+            long long t;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+            a.dbg[blockIdx.x * 4 + 3] = t;
+        }
         *a.ticket = 0u;
         if (a.tail == TAIL_ADAM) a.state[0] += 1;
     }

@@ -81,6 +81,10 @@ int wx_num_sms(const wx_ctx* ctx);
 /* Number of kernels this context has launched since creation (bench.py's gpu_launches claim). */
 int64_t wx_launch_count(const wx_ctx* ctx);
 
+/* Developer aid, not part of the reference-facing surface: when device_buf (int64 [grid][4]) is non-NULL the step
+ * kernels record per CTA { smid, t_start, t_main_loop_end, t_exit } in globaltimer ns.  NULL switches it off. */
+int wx_debug_cta_times(wx_ctx* ctx, long long* device_buf);
+
 /* ---- K1: preprocessing (jobs/preprocess.py) ------------------------------------------------ */
 
 /* Label encode: labels_out[i] = 1 iff string i is valid and equals "rain" exactly, else 0.

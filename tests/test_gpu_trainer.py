@@ -1,0 +1,168 @@
+"""GPU tests of the host mirror: the fit loop, the CLI drop-in, the checkpoint/metric surface, the Lightning-shaped
+module and the ETL front end -- all running the CUDA kernels through the C ABI."""
+import json
+import os
+import shutil
+import subprocess
+import sys
+import tempfile
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import preprocess_ref, synth, train_ref
+
+pytestmark = pytest.mark.gpu
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+GOLDEN = os.path.join(ROOT, "tests", "golden")
+
+
+def test_fit_parity_mode_tracks_reference_loop_w1():
+    """trainer.fit(parity=True) vs the 2-epoch loop driven through the reference's own classes (loop_W1.npz)."""
+    from wxddp import trainer
+
+    g = np.load(os.path.join(GOLDEN, "loop_W1.npz"))
+    h = trainer.fit(torch.from_numpy(g["features"]), torch.from_numpy(g["labels"]), device=0, batch_size=4,
+                    max_epochs=2, parity=True, sanity_check=False, verbose=False)
+    assert h["steps"] == len(g["train_loss"]) == 82
+    np.testing.assert_allclose(h["train_loss"], g["train_loss"], rtol=2e-4, atol=1e-6)      # free-running, 82 Adam steps
+    np.testing.assert_allclose(h["val_loss"], g["val_loss"], rtol=2e-4)
+    np.testing.assert_allclose(h["val_acc"], g["val_acc"], rtol=1e-6)
+    np.testing.assert_allclose(h["params"].numpy(), g["params"], rtol=2e-3, atol=2e-5)
+
+
+def test_fit_parity_mode_matches_oracle_fit_with_sanity_draw():
+    from wxddp import trainer
+
+    t = synth.synth_table(8, 403, 20, const_col=19)
+    pp = preprocess_ref.preprocess_table(t["raw"], t["labels"])
+    feats, labels = torch.from_numpy(pp["features"]), torch.from_numpy(pp["labels"])
+    ref = train_ref.fit(feats, labels, max_epochs=1, batch_size=16)
+    h = trainer.fit(feats, labels, device=0, batch_size=16, max_epochs=1, parity=True, verbose=False)
+    np.testing.assert_allclose(h["train_loss"], ref["train_loss"], rtol=2e-4, atol=1e-6)
+    np.testing.assert_allclose(h["val_loss"], ref["val_loss"], rtol=2e-4)
+
+
+def _make_processed_dir(tmp, n=3000, f=5, seed=3):
+    t = synth.synth_table(seed, n, f)
+    pp = preprocess_ref.preprocess_table(t["raw"], t["labels"])
+    preprocess_ref.write_parquet_dir(os.path.join(tmp, "processed"), t["names"], pp["norm"], pp["labels32"], n_parts=2)
+    return t, pp
+
+
+def test_cli_drop_in_writes_checkpoints_and_metrics():
+    """`python jobs/train_lightning_ddp.py` with no argv: exit 0, top-1 + last.ckpt, metric names, loadable model."""
+    tmp = tempfile.mkdtemp()
+    try:
+        t, pp = _make_processed_dir(tmp)
+        env = dict(os.environ, WX_DATA_DIR=os.path.join(tmp, "processed"), WX_MODEL_DIR=os.path.join(tmp, "models"),
+                   WX_MAX_EPOCHS="3", WX_METRICS_DIR=os.path.join(tmp, "metrics"), WORLD_SIZE="1")
+        r = subprocess.run([sys.executable, os.path.join(ROOT, "jobs", "train_lightning_ddp.py")], env=env,
+                           capture_output=True, text=True, timeout=600)
+        assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+        assert "Training with 5 features" in r.stdout and "Training finished." in r.stdout
+        files = sorted(os.listdir(os.path.join(tmp, "models")))
+        assert "last.ckpt" in files and len(files) == 2 and files[1].startswith("weather-best-epoch=0")
+        mfile = [f for f in os.listdir(os.path.join(tmp, "metrics")) if f.endswith(".jsonl")]
+        recs = [json.loads(l) for l in open(os.path.join(tmp, "metrics", mfile[0]))]
+        steps = [r_["step"] for r_ in recs if "train_loss" in r_]
+        assert steps[:3] == [5, 10, 15]                                    # log_every_n_steps=5 (:139)
+        vals = [r_ for r_ in recs if "val_loss" in r_]
+        assert len(vals) == 3 and all("val_acc" in v for v in vals)
+        assert vals[-1]["val_loss"] < 0.45 and vals[-1]["val_acc"] > 0.8   # it learns
+        assert any(r_.get("artifact_path") == "best_checkpoints" for r_ in recs)
+        # the deploy consumer's call (score.py): load_from_checkpoint(path, input_dim=5), softmax(model(x))
+        from wxddp.module import WeatherClassifier
+        best = os.path.join(tmp, "models", files[1])
+        model = WeatherClassifier.load_from_checkpoint(best, input_dim=5).cuda().eval()
+        x = torch.from_numpy(pp["features"][:256]).cuda()
+        with torch.no_grad():
+            probs = torch.softmax(model(x), dim=1).cpu()
+        ref = train_ref.WeatherNet(5)
+        ref.load_state_dict(torch.load(best, weights_only=False)["state_dict"])
+        ref.eval()
+        with torch.no_grad():
+            want = torch.softmax(ref(torch.from_numpy(pp["features"][:256])), dim=1)
+        np.testing.assert_allclose(probs.numpy(), want.numpy(), rtol=1e-5, atol=1e-7)
+    finally:
+        shutil.rmtree(tmp)
+
+
+def test_cli_fails_loudly_when_data_is_missing():
+    tmp = tempfile.mkdtemp()
+    try:
+        env = dict(os.environ, WX_DATA_DIR=os.path.join(tmp, "nothing"), WX_MODEL_DIR=os.path.join(tmp, "models"),
+                   WX_DISABLE_MLFLOW="1")
+        r = subprocess.run([sys.executable, os.path.join(ROOT, "jobs", "train_lightning_ddp.py")], env=env,
+                           capture_output=True, text=True, timeout=300)
+        assert r.returncode != 0 and "CRITICAL ERROR: Data not found" in r.stderr
+    finally:
+        shutil.rmtree(tmp)
+
+
+def test_lightning_shaped_module_runs_the_kernels():
+    """WeatherClassifier.training_step/validation_step on CUDA batches, driven the way Lightning drives them."""
+    from wxddp.module import WeatherClassifier
+
+    torch.manual_seed(0)
+    m = WeatherClassifier(5).cuda()
+    ref = train_ref.WeatherNet(5)
+    ref.load_state_dict(m.state_dict())
+    g = torch.Generator().manual_seed(1)
+    x = torch.randn(64, 5, generator=g); y = (torch.rand(64, generator=g) < 0.3).long()
+    # eval mode -> dropout off -> comparable with autograd on the CPU copy
+    m.eval(); ref.eval()
+    loss = m.training_step((x.cuda(), y.cuda()), 0)
+    loss.backward()
+    rl = torch.nn.functional.cross_entropy(ref(x), y)
+    rl.backward()
+    np.testing.assert_allclose(loss.item(), rl.item(), rtol=1e-5)
+    for (k, p), (_, q) in zip(m.named_parameters(), ref.named_parameters()):
+        np.testing.assert_allclose(p.grad.cpu().numpy(), q.grad.numpy(), rtol=1e-5, atol=1e-7, err_msg=k)
+    # optimizer from configure_optimizers steps the same parameters Lightning would step
+    opt = m.configure_optimizers(); opt.step()
+    ropt = torch.optim.Adam(ref.parameters(), lr=0.01); ropt.step()
+    big = (ref.net[0].weight.grad.abs() > 1e-6).numpy()
+    np.testing.assert_allclose(m.net[0].weight.detach().cpu().numpy()[big], ref.net[0].weight.detach().numpy()[big],
+                               rtol=1e-5, atol=2e-7)
+    vl = m.validation_step((x.cuda(), y.cuda()), 0)
+    with torch.no_grad():
+        want = torch.nn.functional.cross_entropy(ref(x), y)
+        acc = (ref(x).argmax(1) == y).float().mean()
+    np.testing.assert_allclose(vl.item(), want.item(), rtol=1e-5)
+    assert abs(m.logged["val_acc"].item() - acc.item()) < 1e-6
+    # train mode uses the in-kernel dropout stream and still yields finite gradients
+    m.train(); m.zero_grad()
+    l2 = m.training_step((x.cuda(), y.cuda()), 1)
+    l2.backward()
+    assert torch.isfinite(l2) and all(torch.isfinite(p.grad).all() for p in m.parameters())
+
+
+def test_etl_front_end_matches_oracle_and_feeds_the_trainer():
+    import pyarrow as pa
+
+    from wxddp import etl
+    from wxddp.module import WeatherDataset
+
+    t = synth.synth_table(21, 5000, 5, null_rate=0.01)
+    cols = {n: pa.array(t["raw"][j], mask=np.isnan(t["raw"][j])) for j, n in enumerate(t["names"])}
+    cols["Rain"] = pa.array(t["labels"], type=pa.string())
+    table = pa.table(cols)
+    res = etl.preprocess_table(table, device=0)
+    want = preprocess_ref.preprocess_table(t["raw"], t["labels"])
+    np.testing.assert_array_equal(res["labels32"], want["labels32"])
+    np.testing.assert_allclose(res["norm"], want["norm"], rtol=1e-12, atol=1e-12, equal_nan=True)
+    np.testing.assert_array_equal(res["nullmask"].cpu().numpy().view(np.uint32), want["nullmask"])
+    tmp = tempfile.mkdtemp()
+    try:
+        etl.write_parquet_dir(os.path.join(tmp, "data.parquet"), t["names"], res["norm"], res["labels32"])
+        ds = WeatherDataset(tmp)
+        assert ds.feature_cols == [f"{n}_norm" for n in t["names"]]
+        ulp = np.abs(ds.features.numpy().view(np.int32).astype(np.int64) - want["features"].view(np.int32).astype(np.int64))
+        ok = ~np.isnan(want["features"])
+        assert ulp[ok].max() <= 1 and np.array_equal(np.isnan(ds.features.numpy()), ~ok)
+        np.testing.assert_array_equal(ds.labels.numpy(), want["labels"])
+    finally:
+        shutil.rmtree(tmp)
