@@ -1,0 +1,74 @@
+"""Multi-GPU tests (need >= 2 GPUs; skipped otherwise): one process per GPU, NCCL for the [P+1] bucket.
+The W-GPU run is compared with the W-process gloo DDP run of the oracle (the reference's topology)."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import preprocess_ref, synth, train_ref
+
+pytestmark = pytest.mark.gpu
+
+
+def _need(n):
+    if not torch.cuda.is_available() or torch.cuda.device_count() < n:
+        pytest.skip(f"needs {n} GPUs")
+
+
+def _nccl_worker(rank, world, port, feats, labels, q):
+    import torch.distributed as dist
+
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    from wxddp import trainer
+
+    h = trainer.fit(feats, labels, device=torch.device("cuda", rank), rank=rank, world=world, dist=dist, batch_size=4,
+                    max_epochs=2, parity=True, verbose=False)
+    q.put((rank, h["train_loss"], h["val_loss"], h["val_acc"], h["params"].numpy()))
+    dist.destroy_process_group()
+
+
+def _gloo_worker(rank, world, port, feats, labels, q):
+    import torch.distributed as dist
+
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    torch.set_num_threads(1)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    ref = train_ref.fit(feats, labels, rank=rank, world=world, use_ddp=True, max_epochs=2)
+    q.put((rank, ref["train_loss"], ref["val_loss"], ref["val_acc"], ref["params"].numpy()))
+    dist.destroy_process_group()
+
+
+def _run(worker, world, port, feats, labels):
+    import torch.multiprocessing as mp
+
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=worker, args=(r, world, port, feats, labels, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = sorted([q.get(timeout=600) for _ in range(world)], key=lambda r: r[0])
+    for p in procs:
+        p.join(timeout=120)
+        assert p.exitcode == 0
+    return res
+
+
+@pytest.mark.parametrize("world", [2])
+def test_ddp_on_gpus_matches_gloo_ddp_oracle(world):
+    _need(world)
+    t = synth.synth_table(31, 203, 5)
+    pp = preprocess_ref.preprocess_table(t["raw"], t["labels"])
+    feats, labels = torch.from_numpy(pp["features"]), torch.from_numpy(pp["labels"])
+    got = _run(_nccl_worker, world, 29671, feats, labels)
+    ref = _run(_gloo_worker, world, 29673, feats, labels)
+    for g, r in zip(got, ref):
+        np.testing.assert_allclose(g[1], r[1], rtol=2e-4, atol=1e-6)      # per-step rank-mean train_loss
+        np.testing.assert_allclose(g[2], r[2], rtol=2e-4)
+        np.testing.assert_allclose(g[3], r[3], rtol=1e-6)
+        np.testing.assert_allclose(g[4], r[4], rtol=2e-3, atol=2e-5)
+    np.testing.assert_array_equal(got[0][4], got[1][4])                   # replicas stay bit-identical
