@@ -39,6 +39,7 @@ SIGNATURES = {
     "wx_num_sms": (_int, [_vp]),
     "wx_launch_count": (_i64, [_vp]),
     "wx_debug_cta_times": (_int, [_vp, _vp]),
+    "wx_tc_selftest": (_int, [_vp, _vp, _vp, _vp, _int, _vp, _vp, _vp, _vp]),
     "wx_label_encode": (_int, [_vp, _vp, _vp, _vp, _i64, _vp, _vp, _vp]),
     "wx_col_stats": (_int, [_vp, C.POINTER(_vp), _int, C.POINTER(_vp), _i64, _vp, _vp]),
     "wx_stats_merge": (_int, [_vp, _vp, _int, _vp, _vp]),
