@@ -32,10 +32,12 @@ struct Dim {
 };
 
 // ---------------------------------------------------------------------------------------------
-// Philox4x32-10 (Salmon et al., SC'11).  Dropout stream contract (WX_DROPOUT_PHILOX):
-//   key = (seed_lo, seed_hi); counter = (b >> 2, lane, step_lo, step_hi) for batch position b;
-//   word k = b & 3 of the output: low 16 bits decide unit `lane`, high 16 bits unit `lane + 32`;
-//   keep <=> bits < 52429  (52429/65536 = 0.80000305).
+// Philox4x32-10 (Salmon et al., SC'11).  Dropout stream contract (WX_DROPOUT_PHILOX), one 64-bit keep mask per
+// batch position b (bit j = keep hidden unit j):
+//   key = (seed_lo, seed_hi); for q = 0..7: counter = (b_lo, b_hi, step_lo, (step_hi << 3) | q) -> words W[4q..4q+3];
+//   the 32 words form 16 digit planes U_d = W[2d] | W[2d+1] << 32 (d = 0 most significant): bit j of U_d is binary
+//   digit d of a 16-bit uniform u_j;  keep_j <=> u_j < 0xCCCD (= 52429, 52429/65536 = 0.80000305), evaluated for all
+//   64 units at once: lt = 0; for d = 15..0: lt = T_d ? (~U_d | lt) : (~U_d & lt), T = 0xCCCD MSB first.
 // ---------------------------------------------------------------------------------------------
 __device__ __forceinline__ uint4 philox4x32_10(uint4 c, uint2 k) {
     constexpr uint32_t M0 = 0xD2511F53u, M1 = 0xCD9E8D57u, W0 = 0x9E3779B9u, W1 = 0xBB67AE85u;
@@ -49,7 +51,35 @@ __device__ __forceinline__ uint4 philox4x32_10(uint4 c, uint2 k) {
     }
     return c;
 }
-constexpr uint32_t PHILOX_KEEP_THRESH = 52429u;
+constexpr uint32_t PHILOX_KEEP_THRESH = 52429u;   // 0xCCCD
+
+// digits d0 .. d0+3 of the comparison, most significant of the four last (call order: d = d0+3, .., d0)
+__device__ __forceinline__ uint64_t keep_digits4(uint64_t lt, const uint32_t (&w)[8], int d0) {
+#pragma unroll
+    for (int k = 3; k >= 0; --k) {
+        const uint64_t u = uint64_t(w[2 * k]) | (uint64_t(w[2 * k + 1]) << 32);
+        const bool t = (PHILOX_KEEP_THRESH >> (15 - (d0 + k))) & 1u;
+        lt = t ? (~u | lt) : (~u & lt);
+    }
+    return lt;
+}
+
+// the whole 64-bit keep mask of batch position b (8 Philox calls); used where one thread owns a row
+__device__ __forceinline__ uint64_t philox_keep_mask(uint64_t b, uint2 key, uint64_t step) {
+    uint64_t lt = 0;
+#pragma unroll
+    for (int sub = 3; sub >= 0; --sub) {
+        uint32_t w[8];
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            const uint4 o = philox4x32_10(make_uint4(uint32_t(b), uint32_t(b >> 32), uint32_t(step),
+                                                     (uint32_t(step >> 32) << 3) | uint32_t(2 * sub + h)), key);
+            w[4 * h] = o.x; w[4 * h + 1] = o.y; w[4 * h + 2] = o.z; w[4 * h + 3] = o.w;
+        }
+        lt = keep_digits4(lt, w, 4 * sub);
+    }
+    return lt;
+}
 
 __device__ __forceinline__ void cp_async4(void* smem_dst, const void* gsrc) {
     const uint32_t d = (uint32_t)__cvta_generic_to_shared(smem_dst);
@@ -195,19 +225,30 @@ __device__ __forceinline__ uint32_t chunk_keep_bits(int mode, const ChunkMeta& c
         }
         return kb;
     }
-    // WX_DROPOUT_PHILOX: chunk_pos0 is a multiple of 8 -> two counter groups of 4 batch positions
+    // WX_DROPOUT_PHILOX: lane -> (row r = lane >> 2 of the chunk, quarter sub = lane & 3 of that row's 8 Philox calls).
+    // The four lanes of a row chain their digit planes (sub 3 -> 0) with shuffles, then every lane picks its two
+    // units' bits out of each row's mask.
+    const int sub = lane & 3;
+    const uint64_t b = uint64_t(chunk_pos0) + uint64_t(lane >> 2);
+    uint32_t w[8];
 #pragma unroll
-    for (int g = 0; g < 2; ++g) {
-        const uint64_t grp = (uint64_t(chunk_pos0) >> 2) + g;
-        // the group index is 62 bits at most; its high part is folded into the step_hi word
-        const uint4 o = philox4x32_10(make_uint4(uint32_t(grp), uint32_t(lane), step_lo, step_hi ^ uint32_t(grp >> 32)), key);
-        const uint32_t w[4] = {o.x, o.y, o.z, o.w};
+    for (int h = 0; h < 2; ++h) {
+        const uint4 o = philox4x32_10(make_uint4(uint32_t(b), uint32_t(b >> 32), step_lo, (step_hi << 3) | uint32_t(2 * sub + h)), key);
+        w[4 * h] = o.x; w[4 * h + 1] = o.y; w[4 * h + 2] = o.z; w[4 * h + 3] = o.w;
+    }
+    uint64_t cur = 0;
 #pragma unroll
-        for (int k = 0; k < 4; ++k) {
-            const int r = g * 4 + k;
-            kb |= uint32_t((w[k] & 0xffffu) < PHILOX_KEEP_THRESH) << (2 * r);
-            kb |= uint32_t((w[k] >> 16) < PHILOX_KEEP_THRESH) << (2 * r + 1);
-        }
+    for (int st = 3; st >= 0; --st) {
+        const uint64_t mine = keep_digits4(cur, w, 4 * sub);                 // meaningful on the lane with sub == st
+        cur = __shfl_sync(0xffffffffu, mine, (lane & ~3) | st);
+    }
+    const uint32_t mlo = uint32_t(cur), mhi = uint32_t(cur >> 32);
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+        const uint32_t lo = __shfl_sync(0xffffffffu, mlo, 4 * r);
+        const uint32_t hi = __shfl_sync(0xffffffffu, mhi, 4 * r);
+        kb |= ((lo >> lane) & 1u) << (2 * r);
+        kb |= ((hi >> lane) & 1u) << (2 * r + 1);
     }
     return kb;
 }

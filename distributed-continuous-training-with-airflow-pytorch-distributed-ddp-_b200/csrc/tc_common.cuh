@@ -35,8 +35,11 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
 }
 // Bounded wait: returns false if the barrier did not flip within ~2 s (a protocol bug must not hang the GPU).
 __device__ __forceinline__ bool mbar_wait(uint64_t* bar, uint32_t parity) {
-    for (uint32_t spin = 0; spin < (1u << 26); ++spin)
+    if (mbar_try_wait(bar, parity)) return true;
+    for (uint32_t spin = 0; spin < (1u << 24); ++spin) {
+        __nanosleep(40);                      // back off: idle roles must not steal issue slots from the row workers
         if (mbar_try_wait(bar, parity)) return true;
+    }
     return false;
 }
 

@@ -1,0 +1,573 @@
+// Tensor-core (tcgen05) version of the fused weather-MLP step: forward + cross-entropy + backward (+ Adam).
+// Replaces /root/reference/jobs/train_lightning_ddp.py:57-71,:88 like mlp_grid_kernel, but the two F x 64
+// contractions run on the 5th-generation tensor cores:
+//
+//   GEMM1   z[128 x 64]     = Xaug[128 x K1] . W1aug[64 x K1]^T      (M=128, N=64, K1 = ceil((F+1)/8)*8, K-major, SW128)
+//   GEMM2   G[64 x N2]     += DH[128 x 64]^T . Xaug[128 x N2]        (M=64,  N2 = ceil((F+3)/8)*8, K=128 rows, MN-major, SW128_B32)
+//
+// with Xaug = [x_0..x_{F-1}, 1, dlogit_0, dlogit_1, 0...]: the ones column turns b1 into a GEMM1 weight and db1 into a
+// GEMM2 output; G accumulates in TMEM over ALL tiles of the CTA (dW1 | db1 never leave tensor memory until the end).
+// fp32 accuracy is kept with a 3-term tf32 split of both operands (hi*lo + lo*hi + hi*hi, ~2^-21 relative), so the
+// result meets the same 1e-5 parity bound as the FFMA kernel.
+//
+// Roles (192 threads, one CTA per SM, persistent over 128-row tiles):
+//   warps 0-3  row workers: thread r <-> tile row r <-> TMEM lane r.  They turn the TMA-landed fp32 rows into the
+//              swizzled hi/lo operand tiles, read z from TMEM, do ReLU / dropout / logits / softmax / dlogits /
+//              dh in registers (row-local: no shuffles), write DH and Xaug for GEMM2, and keep dW2 / db2 / loss sums
+//              in registers for the whole kernel.
+//   warp 4     TMA producer: cp.async.bulk of the tile's rows, labels and dropout keep bits into a 3-stage ring.
+//   warp 5     MMA issuer: one elected thread issues tcgen05.mma and commits to mbarriers.
+#include <math.h>
+#include <string.h>
+
+#include "mlp_kernels.cuh"
+#include "tc_common.cuh"
+
+namespace {
+using namespace wxtc;
+using wxk::AdamScalars;
+using wxk::GridArgs;
+
+constexpr int TILE = 128;
+constexpr int TC_THREADS = 192;
+constexpr int STAGES = 3;
+constexpr int MAXF_TC = 29;              // F + 3 columns must fit the 32-column operand tile
+constexpr int TMEM_COLS = 256;           // D1 x2 (2 x 64) + G (32)
+
+struct TcSmem {
+    // operand tiles (all 1024-byte aligned)
+    float w_hi[64 * 32], w_lo[64 * 32];          // W1aug [n][32]   K-major SW128
+    float xk_hi[TILE * 32], xk_lo[TILE * 32];    // Xaug  [row][32] K-major SW128      (GEMM1 A)
+    float xm_hi[TILE * 32], xm_lo[TILE * 32];    // Xaug  [row][32] MN-major SW128_B32 (GEMM2 B)
+    float a_hi[64 * TILE], a_lo[64 * TILE];      // DH    [k=row][m=64]  MN-major SW128_B32 (GEMM2 A); reused for the final dW2 reduce
+    // TMA landing ring
+    float land_x[STAGES][TILE * MAXF_TC];
+    long long land_y[STAGES][TILE];
+    unsigned long long land_m[STAGES][TILE];
+    __align__(16) float w2[2 * 64 + 4];          // W2[c][j], b2[0..1]
+    float slab[64 * 32 + 64 + 128 + 2 + 4];      // CTA partial in flat-parameter order (+ loss)
+    float red_small[TILE][4];                    // db2_0, db2_1, loss per row worker
+    uint64_t land_full[STAGES], land_empty[STAGES];
+    uint64_t xk_ready, a2_ready, a2_free, d1_full[2];
+    uint32_t tmem_base;
+    int err;
+    bool last;
+    AdamScalars adam;
+};
+
+__device__ __forceinline__ float4 ld4(const float* p) { return *reinterpret_cast<const float4*>(p); }
+__device__ __forceinline__ void st4(void* base, uint32_t off, float a, float b, float c, float d) {
+    *reinterpret_cast<float4*>(static_cast<unsigned char*>(base) + off) = make_float4(a, b, c, d);
+}
+
+__global__ void __launch_bounds__(TC_THREADS, 1) tc_step_kernel(const GridArgs a, const int F, int* __restrict__ err_out) {
+    extern __shared__ __align__(1024) unsigned char raw[];     // 1024-byte alignment: the swizzle atoms need it
+    TcSmem& s = *reinterpret_cast<TcSmem*>(raw);               // direct cast keeps the shared address space (LDS/STS)
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int P = 64 * F + 194;
+    const int OFF_B1 = 64 * F, OFF_W2 = 64 * F + 64, OFF_B2 = 64 * F + 192;
+    const int slab_stride = (P + 1 + 3) & ~3;
+    const int K1 = ((F + 1) + 7) & ~7;            // GEMM1 K extent
+    const int N2 = ((F + 3) + 7) & ~7;            // GEMM2 N extent
+    const int64_t ntiles = (a.batch + TILE - 1) / TILE;
+    const int64_t my_tiles = (ntiles - blockIdx.x + gridDim.x - 1) / gridDim.x;     // >= 1 by construction of the grid
+
+    if (tid == 0 && (smem_u32(raw) & 1023u) != 0) atomicExch(err_out, 99);   // dynamic smem base not 1024-aligned
+    if (a.dbg != nullptr && tid == 0) {
+        unsigned smid;
+        long long t;
+        asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        a.dbg[blockIdx.x * 4 + 0] = smid;
+        a.dbg[blockIdx.x * 4 + 1] = t;
+    }
+    if (tid == 0) {
+        for (int i = 0; i < STAGES; ++i) {
+            mbar_init(&s.land_full[i], 1);
+            mbar_init(&s.land_empty[i], TILE);
+        }
+        mbar_init(&s.xk_ready, TILE);
+        mbar_init(&s.a2_ready, TILE);
+        mbar_init(&s.a2_free, 1);
+        mbar_init(&s.d1_full[0], 1);
+        mbar_init(&s.d1_full[1], 1);
+        fence_mbar_init();
+        s.err = 0;
+    }
+    if (warp == 0) tmem_alloc(&s.tmem_base, TMEM_COLS);
+    // W1aug operand (hi/lo, K-major SW128): row n = [W1[n][0..F-1], b1[n], 0 ...]; W2 / b2 to smem
+    if (tid < 64) {
+        const int n = tid;
+#pragma unroll
+        for (int c4 = 0; c4 < 8; ++c4) {
+            float hi[4], lo[4];
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+                const int c = c4 * 4 + e;
+                const float v = c < F ? a.params[n * F + c] : (c == F ? a.params[OFF_B1 + n] : 0.0f);
+                split_tf32(v, hi[e], lo[e]);
+            }
+            const uint32_t off = sw128_offset(n, c4 * 4);
+            st4(s.w_hi, off, hi[0], hi[1], hi[2], hi[3]);
+            st4(s.w_lo, off, lo[0], lo[1], lo[2], lo[3]);
+        }
+    }
+    for (int i = tid; i < 130; i += TC_THREADS) s.w2[i] = a.params[OFF_W2 + i];     // W2[2][64] then b2[2] (contiguous)
+    fence_proxy_async();
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tm = s.tmem_base;
+    const uint32_t d1_base = tm;                // columns [0,128): two 64-column accumulators
+    const uint32_t g_base = tm + 128;           // columns [128,160)
+    const uint64_t step_word = (a.state != nullptr) ? uint64_t(a.state[0]) : a.step;
+
+    auto tile_rows = [&](int64_t t) -> int {
+        const int64_t left = a.batch - t * TILE;
+        return left < TILE ? int(left) : TILE;
+    };
+
+    if (warp == 4) {
+        // ================= TMA producer =================
+        for (int64_t i = 0; i < my_tiles; ++i) {
+            const int st = int(i % STAGES);
+            const int64_t tile = blockIdx.x + i * gridDim.x;
+            if (i >= STAGES && !mbar_wait(&s.land_empty[st], uint32_t((i / STAGES - 1) & 1))) s.err = 2;
+            const int nr = tile_rows(tile);
+            const int64_t row = a.row0 + tile * TILE;
+            const float* gx = a.x + row * F;
+            const bool bulk_ok = nr == TILE;    // full tiles: sizes are multiples of 16 B; start alignment checked on the host
+            if (bulk_ok) {
+                if (lane == 0) {
+                    const uint32_t bx = uint32_t(TILE) * F * 4, by = TILE * 8;
+                    const bool has_m = a.dropout_mode == WX_DROPOUT_MASK;
+                    mbar_arrive_expect_tx(&s.land_full[st], bx + by + (has_m ? by : 0u));
+                    bulk_g2s(s.land_x[st], gx, bx, &s.land_full[st]);
+                    bulk_g2s(s.land_y[st], a.y + row, by, &s.land_full[st]);
+                    if (has_m) bulk_g2s(s.land_m[st], a.keep_mask + tile * TILE, by, &s.land_full[st]);
+                }
+            } else {
+                // ragged last tile: plain loads by the whole warp, then a normal arrive
+                for (int e = lane; e < nr * F; e += 32) s.land_x[st][e] = gx[e];
+                for (int e = lane; e < nr; e += 32) {
+                    s.land_y[st][e] = a.y[row + e];
+                    if (a.dropout_mode == WX_DROPOUT_MASK) s.land_m[st][e] = a.keep_mask[tile * TILE + e];
+                }
+                __threadfence_block();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&s.land_full[st]);
+            }
+        }
+    } else if (warp == 5) {
+        // ================= MMA issuer =================
+        if (lane == 0) {
+            const uint32_t id1 = make_idesc_tf32(128, 64, false, false);
+            const uint32_t id2 = make_idesc_tf32(64, N2, true, true);
+            const uint32_t xk[2] = {smem_u32(s.xk_hi), smem_u32(s.xk_lo)};
+            const uint32_t wk[2] = {smem_u32(s.w_hi), smem_u32(s.w_lo)};
+            const uint32_t am[2] = {smem_u32(s.a_hi), smem_u32(s.a_lo)};
+            const uint32_t xm[2] = {smem_u32(s.xm_hi), smem_u32(s.xm_lo)};
+            auto gemm2 = [&](bool first) {
+                // small terms first: hi*lo, lo*hi, then hi*hi
+                bool acc = !first;
+#pragma unroll
+                for (int term = 0; term < 3; ++term) {
+                    const uint32_t ab = am[term == 1 ? 1 : 0], bb = xm[term == 0 ? 1 : 0];
+                    for (int k = 0; k < TILE / 8; ++k) {
+                        umma_tf32(g_base, make_smem_desc(ab + k * 2048, 512, 1024, LAYOUT_SW128_B32),
+                                  make_smem_desc(bb + k * 1024, 512, 512, LAYOUT_SW128_B32), id2, acc);
+                        acc = true;
+                    }
+                }
+            };
+            for (int64_t i = 0; i < my_tiles; ++i) {
+                if (!mbar_wait(&s.xk_ready, uint32_t(i & 1))) s.err = 3;
+                tc_fence_after();
+                const uint32_t d1 = d1_base + uint32_t(i & 1) * 64;
+                bool acc = false;
+#pragma unroll
+                for (int term = 0; term < 3; ++term) {
+                    const uint32_t ab = xk[term == 1 ? 1 : 0], bb = wk[term == 0 ? 1 : 0];
+                    for (int k = 0; k < K1 / 8; ++k) {
+                        umma_tf32(d1, make_smem_desc(ab + k * 32, 16, 1024), make_smem_desc(bb + k * 32, 16, 1024), id1, acc);
+                        acc = true;
+                    }
+                }
+                umma_commit(&s.d1_full[i & 1]);
+                if (i > 0) {
+                    if (!mbar_wait(&s.a2_ready, uint32_t((i - 1) & 1))) s.err = 4;
+                    tc_fence_after();
+                    gemm2(i - 1 == 0);
+                    umma_commit(&s.a2_free);
+                }
+            }
+            if (!mbar_wait(&s.a2_ready, uint32_t((my_tiles - 1) & 1))) s.err = 4;
+            tc_fence_after();
+            gemm2(my_tiles - 1 == 0);
+            umma_commit(&s.a2_free);
+        }
+    } else {
+        // ================= row workers (warps 0-3) =================
+        const int r = tid;                                        // tile row == TMEM lane
+        const uint32_t lane_addr = uint32_t(warp * 32) << 16;
+        const bool drop = a.dropout_mode != WX_DROPOUT_OFF;
+        const float ds = drop ? 1.25f : 1.0f;                     // 1/(1-0.2), train_lightning_ddp.py:60
+        const uint2 key = make_uint2(uint32_t(a.seed), uint32_t(a.seed >> 32));
+        float gw2_0[64], gw2_1[64];
+#pragma unroll
+        for (int j = 0; j < 64; ++j) gw2_0[j] = gw2_1[j] = 0.0f;
+        float gb2_0 = 0.0f, gb2_1 = 0.0f, loss_acc = 0.0f;
+        const float b2_0 = s.w2[128], b2_1 = s.w2[129];
+
+        // Xaug row of tile-slot `i` -> K-major hi/lo operand tile (GEMM1 A)
+        auto convert = [&](int64_t i) {
+            const int st = int(i % STAGES);
+            const int64_t tile = blockIdx.x + i * gridDim.x;
+            if (!mbar_wait(&s.land_full[st], uint32_t((i / STAGES) & 1))) s.err = 5;
+            const bool valid = r < tile_rows(tile);
+            const float* lx = s.land_x[st] + r * F;
+#pragma unroll
+            for (int c4 = 0; c4 < 8; ++c4) {
+                float hi[4], lo[4];
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                    const int c = c4 * 4 + e;
+                    float v = 0.0f;
+                    if (valid) v = c < F ? lx[c] : (c == F ? 1.0f : 0.0f);
+                    split_tf32(v, hi[e], lo[e]);
+                }
+                const uint32_t off = sw128_offset(r, c4 * 4);
+                st4(s.xk_hi, off, hi[0], hi[1], hi[2], hi[3]);
+                st4(s.xk_lo, off, lo[0], lo[1], lo[2], lo[3]);
+            }
+            fence_proxy_async();
+            mbar_arrive(&s.xk_ready);
+        };
+
+        convert(0);
+        for (int64_t i = 0; i < my_tiles; ++i) {
+            const int st = int(i % STAGES);
+            const int64_t tile = blockIdx.x + i * gridDim.x;
+            const bool valid = r < tile_rows(tile);
+            const uint32_t d1 = d1_base + uint32_t(i & 1) * 64 + lane_addr;
+            if (!mbar_wait(&s.d1_full[i & 1], uint32_t((i >> 1) & 1))) s.err = 6;
+            tc_fence_after();
+            if (i + 1 < my_tiles) convert(i + 1);                 // GEMM1(i+1) overlaps the pointwise work below
+
+            // ---- dropout keep bits for this row ----
+            uint64_t keep = ~0ull;
+            if (a.dropout_mode == WX_DROPOUT_MASK) keep = s.land_m[st][r];
+            else if (a.dropout_mode == WX_DROPOUT_PHILOX) keep = wxk::philox_keep_mask(uint64_t(tile * TILE + r), key, step_word);
+            const int yv = int(s.land_y[st][r]);
+
+            // ---- phase A: a = dropout(relu(z)), logits ----
+            float lg0 = 0.0f, lg1 = 0.0f, lg0b = 0.0f, lg1b = 0.0f;
+            uint64_t gate = 0;
+#pragma unroll
+            for (int cc = 0; cc < 4; ++cc) {
+                float z[16];
+                tmem_ld16(d1 + cc * 16, z);
+                tmem_ld_wait();
+                float w0[16], w1[16];
+#pragma unroll
+                for (int q4 = 0; q4 < 4; ++q4) {
+                    const float4 u = ld4(&s.w2[cc * 16 + q4 * 4]), t = ld4(&s.w2[64 + cc * 16 + q4 * 4]);
+                    w0[q4 * 4] = u.x; w0[q4 * 4 + 1] = u.y; w0[q4 * 4 + 2] = u.z; w0[q4 * 4 + 3] = u.w;
+                    w1[q4 * 4] = t.x; w1[q4 * 4 + 1] = t.y; w1[q4 * 4 + 2] = t.z; w1[q4 * 4 + 3] = t.w;
+                }
+                const uint32_t kb = uint32_t(keep >> (cc * 16)) & 0xffffu;
+                uint32_t gb = 0;
+#pragma unroll
+                for (int q = 0; q < 16; ++q) {
+                    const float h = (z[q] <= 0.0f) ? 0.0f : z[q];                     // relu, NaN passes like torch
+                    const float av = h * (((kb >> q) & 1u) ? ds : 0.0f);
+                    if (q & 1) {
+                        lg0b = fmaf(av, w0[q], lg0b);
+                        lg1b = fmaf(av, w1[q], lg1b);
+                    } else {
+                        lg0 = fmaf(av, w0[q], lg0);
+                        lg1 = fmaf(av, w1[q], lg1);
+                    }
+                    gb |= uint32_t(!(av <= 0.0f)) << q;
+                }
+                gate |= uint64_t(gb) << (cc * 16);
+            }
+            lg0 = (lg0 + lg0b) + b2_0;
+            lg1 = (lg1 + lg1b) + b2_1;
+            // ---- softmax / loss / dlogits, ATen's operation order ----
+            const float mx = fmaxf(lg0, lg1);
+            const float s0 = lg0 - mx, s1 = lg1 - mx;
+            const float lsum = logf(expf(s0) + expf(s1));
+            const float lp0 = s0 - lsum, lp1 = s1 - lsum;
+            float dl0 = 0.0f, dl1 = 0.0f;
+            if (valid) {
+                loss_acc += -(yv ? lp1 : lp0);
+                dl0 = (expf(lp0) - (yv == 0 ? 1.0f : 0.0f)) * a.scale;
+                dl1 = (expf(lp1) - (yv == 1 ? 1.0f : 0.0f)) * a.scale;
+                gb2_0 += dl0;
+                gb2_1 += dl1;
+            }
+            // ---- GEMM2 operands may be rewritten once the previous tile's GEMM2 has drained ----
+            if (i > 0 && !mbar_wait(&s.a2_free, uint32_t((i - 1) & 1))) s.err = 7;
+            // Xaug row (MN-major): features, 1, dl0, dl1
+            {
+                const float* lx = s.land_x[st] + r * F;
+#pragma unroll
+                for (int g8 = 0; g8 < 4; ++g8) {
+                    float hi[8], lo[8];
+#pragma unroll
+                    for (int e = 0; e < 8; ++e) {
+                        const int c = g8 * 8 + e;
+                        float v = 0.0f;
+                        if (valid) v = c < F ? lx[c] : (c == F ? 1.0f : (c == F + 1 ? dl0 : (c == F + 2 ? dl1 : 0.0f)));
+                        split_tf32(v, hi[e], lo[e]);
+                    }
+                    const uint32_t off = mn32_offset(g8 * 8, r, 512, 512);
+                    st4(s.xm_hi, off, hi[0], hi[1], hi[2], hi[3]);
+                    st4(s.xm_hi, off + 16, hi[4], hi[5], hi[6], hi[7]);
+                    st4(s.xm_lo, off, lo[0], lo[1], lo[2], lo[3]);
+                    st4(s.xm_lo, off + 16, lo[4], lo[5], lo[6], lo[7]);
+                }
+            }
+            // ---- phase B: dW2 sums in registers, dh -> GEMM2 A operand ----
+#pragma unroll
+            for (int cc = 0; cc < 4; ++cc) {
+                float z[16];
+                tmem_ld16(d1 + cc * 16, z);
+                tmem_ld_wait();
+                const uint32_t kb = uint32_t(keep >> (cc * 16)) & 0xffffu;
+                const uint32_t gb = uint32_t(gate >> (cc * 16)) & 0xffffu;
+#pragma unroll
+                for (int g8 = 0; g8 < 2; ++g8) {
+                    float hi[8], lo[8];
+                    const float4 u0 = ld4(&s.w2[cc * 16 + g8 * 8]), u1 = ld4(&s.w2[cc * 16 + g8 * 8 + 4]);
+                    const float4 t0 = ld4(&s.w2[64 + cc * 16 + g8 * 8]), t1 = ld4(&s.w2[64 + cc * 16 + g8 * 8 + 4]);
+                    const float w0[8] = {u0.x, u0.y, u0.z, u0.w, u1.x, u1.y, u1.z, u1.w};
+                    const float w1[8] = {t0.x, t0.y, t0.z, t0.w, t1.x, t1.y, t1.z, t1.w};
+#pragma unroll
+                    for (int e = 0; e < 8; ++e) {
+                        const int q = g8 * 8 + e, j = cc * 16 + q;
+                        const float h = (z[q] <= 0.0f) ? 0.0f : z[q];
+                        const float av = h * (((kb >> q) & 1u) ? ds : 0.0f);
+                        gw2_0[j] = fmaf(dl0, av, gw2_0[j]);
+                        gw2_1[j] = fmaf(dl1, av, gw2_1[j]);
+                        const float t = fmaf(dl1, w1[e], dl0 * w0[e]);
+                        const float dh = ((gb >> q) & 1u) ? t * ds : 0.0f;
+                        split_tf32(dh, hi[e], lo[e]);
+                    }
+                    const uint32_t off = mn32_offset(cc * 16 + g8 * 8, r, 512, 1024);
+                    st4(s.a_hi, off, hi[0], hi[1], hi[2], hi[3]);
+                    st4(s.a_hi, off + 16, hi[4], hi[5], hi[6], hi[7]);
+                    st4(s.a_lo, off, lo[0], lo[1], lo[2], lo[3]);
+                    st4(s.a_lo, off + 16, lo[4], lo[5], lo[6], lo[7]);
+                }
+            }
+            fence_proxy_async();
+            tc_fence_before();
+            mbar_arrive(&s.a2_ready);
+            mbar_arrive(&s.land_empty[st]);
+        }
+        // ---- all tiles done: wait for the last GEMM2, then assemble the CTA slab ----
+        if (!mbar_wait(&s.a2_free, uint32_t((my_tiles - 1) & 1))) s.err = 8;
+        tc_fence_after();
+        // G[m][n] (M=64 accumulator: row m = 16*warp + lane, lanes 0-15 of each sub-partition)
+        for (int c0 = 0; c0 < N2; c0 += 16) {
+            float v[16];
+            tmem_ld16(g_base + lane_addr + c0, v);
+            tmem_ld_wait();
+            if (lane < 16) {
+                const int m = warp * 16 + lane;
+#pragma unroll
+                for (int q = 0; q < 16; ++q) {
+                    const int n = c0 + q;
+                    if (n < F) s.slab[m * F + n] = v[q];             // dW1[m][n]
+                    else if (n == F) s.slab[OFF_B1 + m] = v[q];      // db1[m]
+                }
+            }
+        }
+        // dW2: every row worker holds 128 partial sums -> ordered column sums through smem (a_hi/a_lo are free now)
+        float* red = s.a_hi;                                          // [128 rows][128] floats = 64 KB = a_hi + a_lo
+#pragma unroll
+        for (int j = 0; j < 64; ++j) {
+            red[r * 128 + j] = gw2_0[j];
+            red[r * 128 + 64 + j] = gw2_1[j];
+        }
+        s.red_small[r][0] = gb2_0;
+        s.red_small[r][1] = gb2_1;
+        s.red_small[r][2] = loss_acc;
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+        {
+            float acc = 0.0f;
+            for (int k = 0; k < TILE; ++k) acc += red[k * 128 + r];
+            s.slab[OFF_W2 + r] = acc;
+            if (r < 3) {
+                float t = 0.0f;
+                for (int k = 0; k < TILE; ++k) t += s.red_small[k][r];
+                s.slab[r < 2 ? OFF_B2 + r : P] = t;
+            }
+        }
+    }
+    if (a.dbg != nullptr && tid == 0) {
+        long long t;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        a.dbg[blockIdx.x * 4 + 2] = t;
+        a.dbg[blockIdx.x * 4 + 3] = t;
+    }
+    // ================= CTA slab -> global, last CTA reduces (same deterministic protocol as mlp_grid_kernel) ==========
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 0) tmem_dealloc(tm, TMEM_COLS);
+    float* mypart = a.part + size_t(blockIdx.x) * slab_stride;
+    for (int i = tid; i < P + 1; i += TC_THREADS) mypart[i] = s.slab[i];
+    if (tid == 0 && s.err != 0) atomicExch(err_out, s.err);
+    __threadfence();
+    __syncthreads();
+    if (tid == 0) s.last = atomicAdd(a.ticket, 1u) == gridDim.x - 1;
+    __syncthreads();
+    if (!s.last) return;
+    __threadfence();
+    if (a.tail == wxk::TAIL_ADAM && tid == 0) s.adam = wxk::adam_scalars(a.desc, a.state[0] + 1);
+    __syncthreads();
+    const unsigned nparts = gridDim.x;
+    for (int i = tid; i < P + 1; i += TC_THREADS) {
+        float acc[4] = {0.0f, 0.0f, 0.0f, 0.0f};
+        const float* q = a.part + i;
+        unsigned b = 0;
+        float sum = 0.0f;
+        for (; b + 4 <= nparts; b += 4) {
+#pragma unroll
+            for (int u = 0; u < 4; ++u) acc[u] = __ldcg(q + size_t(b + u) * slab_stride);
+            sum += acc[0];
+            sum += acc[1];
+            sum += acc[2];
+            sum += acc[3];
+        }
+        for (; b < nparts; ++b) sum += __ldcg(q + size_t(b) * slab_stride);
+        if (i == P) sum *= a.scale;
+        if (a.tail == wxk::TAIL_GRADS) {
+            a.out[i] = sum;
+        } else if (i < P) {
+            float p = a.p_rw[i], m = a.m[i], v = a.v[i];
+            wxk::adam_apply(p, sum, m, v, s.adam);
+            a.p_rw[i] = p;
+            a.m[i] = m;
+            a.v[i] = v;
+        } else {
+            *a.loss_out = sum;
+        }
+    }
+    if (tid == 0) {
+        if (a.dbg != nullptr) {
+            long long t;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+            a.dbg[blockIdx.x * 4 + 3] = t;
+        }
+        *a.ticket = 0u;
+        if (a.tail == wxk::TAIL_ADAM) a.state[0] += 1;
+    }
+}
+
+int tc_launch(wx_ctx* ctx, GridArgs& a, cudaStream_t st, const char* who) {
+    const int f = ctx->desc.n_features;
+    WX_CHECK_ARG(f <= MAXF_TC, "%s: the tensor-core path is built for n_features <= %d (got %d)", who, MAXF_TC, f);
+    WX_CHECK_ARG(a.row_idx == nullptr, "%s: the tensor-core path takes contiguous rows only (row_idx must be NULL)", who);
+    WX_CHECK_ARG(((reinterpret_cast<uintptr_t>(a.x) + size_t(a.row0) * f * 4) & 15) == 0,
+                 "%s: first row of the batch must start on a 16-byte boundary for the TMA loads", who);
+    WX_CHECK_ARG(((reinterpret_cast<uintptr_t>(a.y) + size_t(a.row0) * 8) & 15) == 0,
+                 "%s: labels of the batch must start on a 16-byte boundary for the TMA loads", who);
+    WX_CHECK_ARG(a.dropout_mode != WX_DROPOUT_MASK || (reinterpret_cast<uintptr_t>(a.keep_mask) & 15) == 0,
+                 "%s: keep_mask must be 16-byte aligned", who);
+    WX_CUDA(cudaSetDevice(ctx->device));
+    const int smem = int(sizeof(TcSmem));
+    static bool attr_set = false;
+    if (!attr_set) {
+        WX_CUDA(cudaFuncSetAttribute(tc_step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        attr_set = true;
+    }
+    const int64_t ntiles = (a.batch + TILE - 1) / TILE;
+    int64_t grid = ntiles < ctx->num_sms ? ntiles : ctx->num_sms;
+    const size_t slab = (size_t(64) * f + 194 + 1 + 3) & ~size_t(3);
+    if (WX_SCRATCH_PART_OFF + size_t(grid) * slab * 4 > ctx->scratch_bytes) {
+        wx_set_error("%s: scratch too small", who);
+        return WX_ENOMEM;
+    }
+    a.part = reinterpret_cast<float*>(ctx->scratch + WX_SCRATCH_PART_OFF);
+    a.ticket = reinterpret_cast<unsigned int*>(ctx->scratch) + 1;
+    a.desc = ctx->desc;
+    a.dbg = ctx->debug_times;
+    int* err = reinterpret_cast<int*>(ctx->scratch) + 8;       // word 8 of the ticket block: sticky protocol-error code
+    tc_step_kernel<<<(unsigned)grid, TC_THREADS, smem, st>>>(a, f, err);
+    WX_LAUNCH_CHECK(ctx);
+    return WX_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int wx_tc_mlp_grad(wx_ctx* ctx, const float* params, const float* x, const int64_t* y, int64_t row0, int64_t batch,
+                   int dropout_mode, const uint64_t* keep_mask, uint64_t seed, uint64_t step, float scale, float* out,
+                   void* stream) {
+    WX_CHECK_ARG(ctx != nullptr, "wx_tc_mlp_grad: ctx is NULL");
+    WX_CHECK_ARG(params && x && y && out, "wx_tc_mlp_grad: NULL params/x/y/out");
+    WX_CHECK_ARG(batch >= 1 && row0 >= 0, "wx_tc_mlp_grad: batch=%lld row0=%lld", (long long)batch, (long long)row0);
+    WX_CHECK_ARG(dropout_mode == WX_DROPOUT_OFF || dropout_mode == WX_DROPOUT_MASK || dropout_mode == WX_DROPOUT_PHILOX,
+                 "wx_tc_mlp_grad: dropout_mode=%d", dropout_mode);
+    WX_CHECK_ARG(dropout_mode != WX_DROPOUT_MASK || keep_mask != nullptr, "wx_tc_mlp_grad: WX_DROPOUT_MASK needs keep_mask");
+    if (ctx->desc.dropout_p == 0.0f) dropout_mode = WX_DROPOUT_OFF;
+    GridArgs a;
+    memset(&a, 0, sizeof(a));
+    a.params = params;
+    a.x = x;
+    a.y = y;
+    a.row0 = row0;
+    a.batch = batch;
+    a.dropout_mode = dropout_mode;
+    a.keep_mask = keep_mask;
+    a.seed = seed;
+    a.step = step;
+    a.scale = scale;
+    a.tail = wxk::TAIL_GRADS;
+    a.out = out;
+    return tc_launch(ctx, a, (cudaStream_t)stream, "wx_tc_mlp_grad");
+}
+
+int wx_tc_train_step(wx_ctx* ctx, float* params, float* m, float* v, int64_t* state, const float* x, const int64_t* y,
+                     int64_t row0, int64_t batch, int dropout_mode, const uint64_t* keep_mask, uint64_t seed,
+                     float* loss_out, void* stream) {
+    WX_CHECK_ARG(ctx != nullptr, "wx_tc_train_step: ctx is NULL");
+    WX_CHECK_ARG(params && m && v && state && x && y && loss_out, "wx_tc_train_step: NULL pointer");
+    WX_CHECK_ARG(batch >= 1 && row0 >= 0, "wx_tc_train_step: batch=%lld row0=%lld", (long long)batch, (long long)row0);
+    WX_CHECK_ARG(dropout_mode == WX_DROPOUT_OFF || dropout_mode == WX_DROPOUT_MASK || dropout_mode == WX_DROPOUT_PHILOX,
+                 "wx_tc_train_step: dropout_mode=%d", dropout_mode);
+    WX_CHECK_ARG(dropout_mode != WX_DROPOUT_MASK || keep_mask != nullptr, "wx_tc_train_step: WX_DROPOUT_MASK needs keep_mask");
+    if (ctx->desc.dropout_p == 0.0f) dropout_mode = WX_DROPOUT_OFF;
+    GridArgs a;
+    memset(&a, 0, sizeof(a));
+    a.params = params;
+    a.x = x;
+    a.y = y;
+    a.row0 = row0;
+    a.batch = batch;
+    a.dropout_mode = dropout_mode;
+    a.keep_mask = keep_mask;
+    a.seed = seed;
+    a.scale = 1.0f / float(batch);
+    a.tail = wxk::TAIL_ADAM;
+    a.p_rw = params;
+    a.m = m;
+    a.v = v;
+    a.state = state;
+    a.loss_out = loss_out;
+    return tc_launch(ctx, a, (cudaStream_t)stream, "wx_tc_train_step");
+}
+
+/* Sticky protocol-error code of the tensor-core kernels (0 = none): a bounded mbarrier wait that expired. */
+int wx_tc_last_status(wx_ctx* ctx, int* host_out) {
+    WX_CHECK_ARG(ctx != nullptr && host_out != nullptr, "wx_tc_last_status: NULL argument");
+    WX_CUDA(cudaSetDevice(ctx->device));
+    WX_CUDA(cudaMemcpy(host_out, reinterpret_cast<int*>(ctx->scratch) + 8, sizeof(int), cudaMemcpyDeviceToHost));
+    return WX_OK;
+}
+
+}  // extern "C"

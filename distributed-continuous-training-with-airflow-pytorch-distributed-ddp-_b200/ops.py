@@ -180,6 +180,34 @@ class Context:
                                    _p(keep_mask), seed, step, scale, _p(out), self._stream()))
         return out
 
+    def tc_mlp_grad(self, params, x, y, *, row0: int = 0, batch: int | None = None, dropout: int = DROPOUT_OFF,
+                    keep_mask=None, seed: int = 0, step: int = 0, scale: float | None = None,
+                    out: torch.Tensor | None = None) -> torch.Tensor:
+        """wx_mlp_grad on the tensor cores (tcgen05 tf32x3): contiguous rows, F <= 29."""
+        self._chk(params, torch.float32, "params", self.P)
+        batch = self._batch_args(x, y, None, row0, batch, keep_mask, dropout)
+        if scale is None:
+            scale = 1.0 / batch
+        if out is None:
+            out = torch.empty(self.P + 1, dtype=torch.float32, device=self.device)
+        self._chk(out, torch.float32, "out", self.P + 1)
+        check(self.lib.wx_tc_mlp_grad(self._h, _p(params), _p(x), _p(y), row0, batch, dropout, _p(keep_mask), seed, step,
+                                      scale, _p(out), self._stream()))
+        return out
+
+    def tc_train_step(self, params, m, v, state, x, y, loss_out, *, row0: int = 0, batch: int | None = None,
+                      dropout: int = DROPOUT_PHILOX, keep_mask=None, seed: int = 0) -> None:
+        """wx_train_step on the tensor cores: one launch per optimizer step."""
+        self._opt_args(params, m, v, state, loss_out)
+        batch = self._batch_args(x, y, None, row0, batch, keep_mask, dropout)
+        check(self.lib.wx_tc_train_step(self._h, _p(params), _p(m), _p(v), _p(state), _p(x), _p(y), row0, batch, dropout,
+                                        _p(keep_mask), seed, _p(loss_out), self._stream()))
+
+    def tc_status(self) -> int:
+        out = C.c_int(0)
+        check(self.lib.wx_tc_last_status(self._h, C.byref(out)))
+        return out.value
+
     def adam_step(self, params, grads, m, v, step: int, n: int | None = None) -> None:
         """train_lightning_ddp.py:88, torch.optim.Adam single-tensor arithmetic; step is 1-based."""
         n = params.numel() if n is None else n

@@ -53,7 +53,7 @@ extern "C" {
 /* dropout source in the training step (train_lightning_ddp.py:60) */
 #define WX_DROPOUT_OFF 0    /* eval semantics */
 #define WX_DROPOUT_MASK 1   /* caller supplies keep bits: uint64 per row, bit j = keep hidden unit j */
-#define WX_DROPOUT_PHILOX 2 /* in-kernel Philox4x32-10 keyed by (seed, step, row, unit), p_keep = 52429/65536 */
+#define WX_DROPOUT_PHILOX 2 /* in-kernel Philox4x32-10 keyed by (seed, step, row); 16-bit thresholds, p_keep = 52429/65536 */
 
 typedef struct wx_ctx wx_ctx;
 
@@ -161,6 +161,19 @@ int wx_mlp_grad_static(int n_features, const float* params, const float* x, cons
                        const int64_t* row_idx, int64_t row0, int64_t batch, int dropout_mode,
                        const uint64_t* keep_mask, uint64_t seed, uint64_t step, float scale,
                        float* out /* device [P+1] */, void* stream);
+
+/* Tensor-core (tcgen05, kind::tf32 with a 3-term hi/lo split -> fp32-level accuracy) versions of wx_mlp_grad and
+ * wx_train_step: same arithmetic contract and outputs (train_lightning_ddp.py:57-71,:88), the two F x 64 contractions
+ * run on the 5th-generation tensor cores, rows arrive by TMA bulk copies.  Restrictions: n_features <= 29, contiguous
+ * rows only (no row_idx), x + row0*F*4 and y + row0*8 16-byte aligned.  wx_tc_last_status reads a sticky protocol
+ * error code (0 = none) that the kernel sets if one of its bounded barrier waits expired. */
+int wx_tc_mlp_grad(wx_ctx* ctx, const float* params, const float* x, const int64_t* y, int64_t row0, int64_t batch,
+                   int dropout_mode, const uint64_t* keep_mask, uint64_t seed, uint64_t step, float scale,
+                   float* out /* device [P+1] */, void* stream);
+int wx_tc_train_step(wx_ctx* ctx, float* params, float* m, float* v, int64_t* state, const float* x, const int64_t* y,
+                     int64_t row0, int64_t batch, int dropout_mode, const uint64_t* keep_mask, uint64_t seed,
+                     float* loss_out, void* stream);
+int wx_tc_last_status(wx_ctx* ctx, int* host_out);
 
 /* Adam update of a flat fp32 vector, torch.optim.Adam semantics with the desc's hyper-parameters
  * (:88; torch/optim/adam.py _single_tensor_adam).  step is 1-based.  grads may hold extra trailing

@@ -2,7 +2,7 @@
 
 No counterpart in the reference: torch's CPU dropout draws from the mt19937 global generator
 (train_lightning_ddp.py:60), which a massively parallel kernel cannot replay; parity with the
-reference uses WX_DROPOUT_MASK instead.  This file pins the kernel's own counter-based stream
+reference uses WX_DROPOUT_MASK instead.  This file pins the kernels' own counter-based stream
 (csrc/mlp_step.cuh) so the perf-mode dropout is testable bit-for-bit.
 Known-answer test (Random123 kat_vectors, philox4x32-10): ctr=0,key=0 -> 6627e8d5 e169c58d bc57ac4c 9b00dbd8.
 """
@@ -10,7 +10,7 @@ import numpy as np
 
 M0, M1 = np.uint64(0xD2511F53), np.uint64(0xCD9E8D57)
 W0, W1 = 0x9E3779B9, 0xBB67AE85
-KEEP_THRESH = 52429
+KEEP_THRESH = 52429        # 0xCCCD; P(keep) = 52429/65536
 
 
 def philox4x32_10(c0, c1, c2, c3, k0, k1):
@@ -31,19 +31,24 @@ def philox4x32_10(c0, c1, c2, c3, k0, k1):
 
 
 def dropout_keep_mask(batch: int, seed: int, step: int) -> np.ndarray:
-    """[batch, 64] bool keep mask the kernel uses for (seed, step): batch position b, hidden unit j.
+    """[batch, 64] bool keep mask the kernels use for (seed, step): batch position b, hidden unit j.
 
-    counter = (b >> 2, j & 31, step_lo, step_hi ^ ((b >> 2) >> 32)); word b & 3; low half -> j < 32, high -> j >= 32.
+    For q = 0..7: counter (b_lo, b_hi, step_lo, (step_hi << 3) | q) -> words W[4q..4q+3]; digit plane
+    U_d = W[2d] | W[2d+1] << 32 (d = 0 most significant); bit j of U_d is binary digit d of a 16-bit uniform u_j;
+    keep_j <=> u_j < 0xCCCD.
     """
     b = np.arange(batch, dtype=np.uint64)
-    grp = b >> np.uint64(2)
-    lane = np.arange(32, dtype=np.uint32)
-    c0 = (grp & np.uint64(0xFFFFFFFF)).astype(np.uint32)[:, None]
-    c3 = (np.uint32((step >> 32) & 0xFFFFFFFF) ^ (grp >> np.uint64(32)).astype(np.uint32))[:, None]
-    out = philox4x32_10(c0, lane[None, :], np.uint32(step & 0xFFFFFFFF), c3, seed & 0xFFFFFFFF, (seed >> 32) & 0xFFFFFFFF)
-    words = np.stack(out, axis=0)                        # [4, batch, 32]
-    w = words[(b & np.uint64(3)).astype(np.int64), np.arange(batch)]   # [batch, 32]
-    keep = np.empty((batch, 64), dtype=bool)
-    keep[:, :32] = (w & np.uint32(0xFFFF)) < KEEP_THRESH
-    keep[:, 32:] = (w >> np.uint32(16)) < KEEP_THRESH
-    return keep
+    b_lo = (b & np.uint64(0xFFFFFFFF)).astype(np.uint32)
+    b_hi = (b >> np.uint64(32)).astype(np.uint32)
+    words = np.empty((32, batch), dtype=np.uint32)
+    for q in range(8):
+        c3 = np.uint32((((step >> 32) << 3) | q) & 0xFFFFFFFF)
+        out = philox4x32_10(b_lo, b_hi, np.uint32(step & 0xFFFFFFFF), c3, seed & 0xFFFFFFFF, (seed >> 32) & 0xFFFFFFFF)
+        for i in range(4):
+            words[4 * q + i] = out[i]
+    u = np.zeros((batch, 64), dtype=np.uint32)                      # the 16-bit uniform of every (row, unit)
+    for d in range(16):
+        plane = words[2 * d].astype(np.uint64) | (words[2 * d + 1].astype(np.uint64) << np.uint64(32))
+        bits = ((plane[:, None] >> np.arange(64, dtype=np.uint64)) & np.uint64(1)).astype(np.uint32)
+        u |= bits << np.uint32(15 - d)
+    return u < KEEP_THRESH
