@@ -165,6 +165,7 @@ def main() -> int:
     ap.add_argument("--cpu-rows-per-step", type=int, default=65536,
                     help="CPU arms: rows per step of the bounded sample (0 = --rows-per-step)")
     ap.add_argument("--cpu-steps", type=int, default=8)
+    ap.add_argument("--kernel", default="auto", choices=["auto", "tc", "ffma"], help="step kernel at N=1")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     args = ap.parse_args()
@@ -217,13 +218,17 @@ def main() -> int:
         feats, _ = ctx.normalize_pack(cols, stats, impute=wxddp.IMPUTE_MEAN)
     n_windows = (T - B) // B + 1
     step_no = [0]
+    use_tc = args.kernel != "ffma" and ctx.tc_ok_raw(cols, y, 0) and B % 4 == 0
+    step_raw = ctx.tc_train_step_raw if use_tc else ctx.train_step_raw
+    kernel_name = ("tc_step_kernel (tcgen05 tf32x3, wx_tc_train_step_raw)" if use_tc
+                   else "mlp_grid_kernel<F,TRAIN,RAW_F32> (FFMA, wx_train_step_raw)")
 
     def one_step():
         s = step_no[0]
         row0 = (s % n_windows) * B
         if world == 1:
-            ctx.train_step_raw(params, m, v, state, cols, stats, y, loss, row0=row0, batch=B,
-                               impute=wxddp.IMPUTE_MEAN, dropout=wxddp.DROPOUT_PHILOX, seed=42)
+            step_raw(params, m, v, state, cols, stats, y, loss, row0=row0, batch=B,
+                     impute=wxddp.IMPUTE_MEAN, dropout=wxddp.DROPOUT_PHILOX, seed=42)
         else:
             # DDP: local sums pre-scaled by 1/(W*B), SUM across ranks (what torch's reducer does, :136),
             # loss scalar rides in the same bucket (element P), then Adam
@@ -301,7 +306,7 @@ def main() -> int:
     achieved = B * bytes_per_row / kernel_s / 1e9
     flops_per_row = 2 * (2 * f * 64 + 3 * 64 * 2)
     roof = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-            "traffic": None, "kernel": "mlp_grid_kernel<F,TRAIN,RAW_F32> (wx_train_step_raw)" if world == 1
+            "traffic": None, "kernel": kernel_name if world == 1
             else "mlp_grid_kernel<F,TRAIN,ROWMAJOR> (wx_mlp_grad) + NCCL all-reduce + adam_kernel",
             "peak_source": peak_src, "algorithmic_bytes_per_row": bytes_per_row,
             "fp32_pipe": {"achieved_tflops": B * flops_per_row / kernel_s / 1e12, "peak_tflops": 74.4,

@@ -49,6 +49,8 @@ SIGNATURES = {
     "wx_mlp_grad_static": (_int, [_int, _vp, _vp, _vp, _vp, _i64, _i64, _int, _vp, _u64, _u64, C.c_float, _vp, _vp]),
     "wx_tc_mlp_grad": (_int, [_vp, _vp, _vp, _vp, _i64, _i64, _int, _vp, _u64, _u64, C.c_float, _vp, _vp]),
     "wx_tc_train_step": (_int, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _i64, _i64, _int, _vp, _u64, _vp, _vp]),
+    "wx_tc_train_step_raw": (_int, [_vp, _vp, _vp, _vp, _vp, C.POINTER(_vp), _vp, _int, _vp, _i64, _i64, _int, _vp, _u64,
+                                    _vp, _vp]),
     "wx_tc_last_status": (_int, [_vp, C.POINTER(_int)]),
     "wx_adam_step": (_int, [_vp, _vp, _vp, _vp, _vp, _i64, _i64, _vp]),
     "wx_train_step": (_int, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i64, _i64, _int, _vp, _u64, _vp, _vp]),

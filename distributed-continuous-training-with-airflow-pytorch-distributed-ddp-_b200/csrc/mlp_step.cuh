@@ -67,7 +67,7 @@ __device__ __forceinline__ uint64_t keep_digits4(uint64_t lt, const uint32_t (&w
 // the whole 64-bit keep mask of batch position b (8 Philox calls); used where one thread owns a row
 __device__ __forceinline__ uint64_t philox_keep_mask(uint64_t b, uint2 key, uint64_t step) {
     uint64_t lt = 0;
-#pragma unroll
+#pragma unroll 1
     for (int sub = 3; sub >= 0; --sub) {
         uint32_t w[8];
 #pragma unroll

@@ -1,6 +1,7 @@
-// Tensor-core (tcgen05) version of the fused weather-MLP step: forward + cross-entropy + backward (+ Adam).
-// Replaces /root/reference/jobs/train_lightning_ddp.py:57-71,:88 like mlp_grid_kernel, but the two F x 64
-// contractions run on the 5th-generation tensor cores:
+// Tensor-core (tcgen05) version of the fused weather-MLP step: [standardise +] forward + cross-entropy + backward
+// (+ Adam).  Replaces /root/reference/jobs/train_lightning_ddp.py:57-71,:88 (and, with the raw-column loader,
+// /root/reference/jobs/preprocess.py:38-41) like mlp_grid_kernel, but the two F x 64 contractions run on the
+// 5th-generation tensor cores:
 //
 //   GEMM1   z[128 x 64]     = Xaug[128 x K1] . W1aug[64 x K1]^T      (M=128, N=64, K1 = ceil((F+1)/8)*8, K-major, SW128)
 //   GEMM2   G[64 x N2]     += DH[128 x 64]^T . Xaug[128 x N2]        (M=64,  N2 = ceil((F+3)/8)*8, K=128 rows, MN-major, SW128_B32)
@@ -10,13 +11,15 @@
 // fp32 accuracy is kept with a 3-term tf32 split of both operands (hi*lo + lo*hi + hi*hi, ~2^-21 relative), so the
 // result meets the same 1e-5 parity bound as the FFMA kernel.
 //
-// Roles (192 threads, one CTA per SM, persistent over 128-row tiles):
-//   warps 0-3  row workers: thread r <-> tile row r <-> TMEM lane r.  They turn the TMA-landed fp32 rows into the
-//              swizzled hi/lo operand tiles, read z from TMEM, do ReLU / dropout / logits / softmax / dlogits /
-//              dh in registers (row-local: no shuffles), write DH and Xaug for GEMM2, and keep dW2 / db2 / loss sums
-//              in registers for the whole kernel.
-//   warp 4     TMA producer: cp.async.bulk of the tile's rows, labels and dropout keep bits into a 3-stage ring.
-//   warp 5     MMA issuer: one elected thread issues tcgen05.mma and commits to mbarriers.
+// Roles (320 threads, one CTA per SM, persistent over 128-row tiles; tile i belongs to worker group i & 1):
+//   warps 0-3 / 4-7  two row-worker groups: thread r <-> tile row r <-> TMEM lane r.  A group turns the TMA-landed rows
+//              of its tile into the swizzled hi/lo operand tiles (standardising raw columns on the way), reads z from
+//              TMEM, does ReLU / dropout / logits / softmax / dlogits / dh in registers (row-local: no shuffles),
+//              writes DH and Xaug for GEMM2, and keeps its dW2 sums in its own TMEM columns (read-modify-write),
+//              db2 / loss sums in registers.  While one group is in its pointwise phase the other converts / waits.
+//   warp 8     TMA producer: cp.async.bulk of the tile's rows (or F column segments), labels and dropout keep bits
+//              into a 3-stage ring.
+//   warp 9     MMA issuer: one elected thread issues tcgen05.mma and commits to mbarriers.
 #include <math.h>
 #include <string.h>
 
@@ -29,10 +32,14 @@ using wxk::AdamScalars;
 using wxk::GridArgs;
 
 constexpr int TILE = 128;
-constexpr int TC_THREADS = 192;
+constexpr int NGROUPS = 2;
+constexpr int WORKERS = NGROUPS * TILE;          // 256 row-worker threads
+constexpr int TC_THREADS = WORKERS + 64;         // + producer warp + MMA warp
+constexpr int PRODUCER_WARP = WORKERS / 32, MMA_WARP = WORKERS / 32 + 1;
 constexpr int STAGES = 3;
-constexpr int MAXF_TC = 29;              // F + 3 columns must fit the 32-column operand tile
-constexpr int TMEM_COLS = 256;           // D1 x2 (2 x 64) + G (32)
+constexpr int MAXF_TC = 29;                      // F + 3 columns must fit the 32-column operand tile
+constexpr int TMEM_COLS = 512;                   // D1 x2 [0,128) | G [128,160) | dW2 sums of group g [256+128g, 384+128g)
+constexpr int TM_G = 128, TM_ACC = 256;
 
 struct TcSmem {
     // operand tiles (all 1024-byte aligned)
@@ -40,13 +47,14 @@ struct TcSmem {
     float xk_hi[TILE * 32], xk_lo[TILE * 32];    // Xaug  [row][32] K-major SW128      (GEMM1 A)
     float xm_hi[TILE * 32], xm_lo[TILE * 32];    // Xaug  [row][32] MN-major SW128_B32 (GEMM2 B)
     float a_hi[64 * TILE], a_lo[64 * TILE];      // DH    [k=row][m=64]  MN-major SW128_B32 (GEMM2 A); reused for the final dW2 reduce
-    // TMA landing ring
+    // TMA landing ring: dense rows [128][F] (row-major loader) or column segments [F][128] (raw loader)
     float land_x[STAGES][TILE * MAXF_TC];
     long long land_y[STAGES][TILE];
     unsigned long long land_m[STAGES][TILE];
     __align__(16) float w2[2 * 64 + 4];          // W2[c][j], b2[0..1]
+    double mean[32], rstd[32];                   // raw loader: column mean and 1/std_val
     float slab[64 * 32 + 64 + 128 + 2 + 4];      // CTA partial in flat-parameter order (+ loss)
-    float red_small[TILE][4];                    // db2_0, db2_1, loss per row worker
+    float red_small[WORKERS][4];                 // db2_0, db2_1, loss per row worker
     uint64_t land_full[STAGES], land_empty[STAGES];
     uint64_t xk_ready, a2_ready, a2_free, d1_full[2];
     uint32_t tmem_base;
@@ -69,6 +77,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_step_kernel(const GridArgs a
     const int slab_stride = (P + 1 + 3) & ~3;
     const int K1 = ((F + 1) + 7) & ~7;            // GEMM1 K extent
     const int N2 = ((F + 3) + 7) & ~7;            // GEMM2 N extent
+    const bool raw_cols = a.loader != wxk::LOAD_ROWMAJOR;
     const int64_t ntiles = (a.batch + TILE - 1) / TILE;
     const int64_t my_tiles = (ntiles - blockIdx.x + gridDim.x - 1) / gridDim.x;     // >= 1 by construction of the grid
 
@@ -95,7 +104,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_step_kernel(const GridArgs a
         s.err = 0;
     }
     if (warp == 0) tmem_alloc(&s.tmem_base, TMEM_COLS);
-    // W1aug operand (hi/lo, K-major SW128): row n = [W1[n][0..F-1], b1[n], 0 ...]; W2 / b2 to smem
+    // W1aug operand (hi/lo, K-major SW128): row n = [W1[n][0..F-1], b1[n], 0 ...]; W2 / b2 / statistics to smem
     if (tid < 64) {
         const int n = tid;
 #pragma unroll
@@ -113,13 +122,17 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_step_kernel(const GridArgs a
         }
     }
     for (int i = tid; i < 130; i += TC_THREADS) s.w2[i] = a.params[OFF_W2 + i];     // W2[2][64] then b2[2] (contiguous)
+    if (raw_cols && tid < F) {
+        s.mean[tid] = a.stats[tid * 4 + 1];
+        s.rstd[tid] = 1.0 / a.stats[tid * 4 + 3];
+    }
     fence_proxy_async();
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
     const uint32_t tm = s.tmem_base;
-    const uint32_t d1_base = tm;                // columns [0,128): two 64-column accumulators
-    const uint32_t g_base = tm + 128;           // columns [128,160)
+    const uint32_t d1_base = tm;
+    const uint32_t g_base = tm + TM_G;
     const uint64_t step_word = (a.state != nullptr) ? uint64_t(a.state[0]) : a.step;
 
     auto tile_rows = [&](int64_t t) -> int {
@@ -127,7 +140,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_step_kernel(const GridArgs a
         return left < TILE ? int(left) : TILE;
     };
 
-    if (warp == 4) {
+    if (warp == PRODUCER_WARP) {
         // ================= TMA producer =================
         for (int64_t i = 0; i < my_tiles; ++i) {
             const int st = int(i % STAGES);
@@ -135,30 +148,41 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_step_kernel(const GridArgs a
             if (i >= STAGES && !mbar_wait(&s.land_empty[st], uint32_t((i / STAGES - 1) & 1))) s.err = 2;
             const int nr = tile_rows(tile);
             const int64_t row = a.row0 + tile * TILE;
-            const float* gx = a.x + row * F;
-            const bool bulk_ok = nr == TILE;    // full tiles: sizes are multiples of 16 B; start alignment checked on the host
-            if (bulk_ok) {
+            const bool has_m = a.dropout_mode == WX_DROPOUT_MASK;
+            if (nr == TILE) {           // full tile: every size is a multiple of 16 B; start alignment is checked on the host
+                const uint32_t by = TILE * 8;
+                if (lane == 0) mbar_arrive_expect_tx(&s.land_full[st], uint32_t(TILE) * F * 4 + by + (has_m ? by : 0u));
+                __syncwarp();
+                if (!raw_cols) {
+                    if (lane == 0) bulk_g2s(s.land_x[st], a.x + row * F, uint32_t(TILE) * F * 4, &s.land_full[st]);
+                } else if (lane < F) {  // one 512-byte column segment per lane
+                    bulk_g2s(s.land_x[st] + lane * TILE, static_cast<const float*>(a.cols.col[lane]) + row, TILE * 4,
+                             &s.land_full[st]);
+                }
                 if (lane == 0) {
-                    const uint32_t bx = uint32_t(TILE) * F * 4, by = TILE * 8;
-                    const bool has_m = a.dropout_mode == WX_DROPOUT_MASK;
-                    mbar_arrive_expect_tx(&s.land_full[st], bx + by + (has_m ? by : 0u));
-                    bulk_g2s(s.land_x[st], gx, bx, &s.land_full[st]);
                     bulk_g2s(s.land_y[st], a.y + row, by, &s.land_full[st]);
                     if (has_m) bulk_g2s(s.land_m[st], a.keep_mask + tile * TILE, by, &s.land_full[st]);
                 }
             } else {
                 // ragged last tile: plain loads by the whole warp, then a normal arrive
-                for (int e = lane; e < nr * F; e += 32) s.land_x[st][e] = gx[e];
+                if (!raw_cols) {
+                    const float* gx = a.x + row * F;
+                    for (int e = lane; e < nr * F; e += 32) s.land_x[st][e] = gx[e];
+                } else {
+                    for (int c = 0; c < F; ++c)
+                        for (int e = lane; e < nr; e += 32)
+                            s.land_x[st][c * TILE + e] = static_cast<const float*>(a.cols.col[c])[row + e];
+                }
                 for (int e = lane; e < nr; e += 32) {
                     s.land_y[st][e] = a.y[row + e];
-                    if (a.dropout_mode == WX_DROPOUT_MASK) s.land_m[st][e] = a.keep_mask[tile * TILE + e];
+                    if (has_m) s.land_m[st][e] = a.keep_mask[tile * TILE + e];
                 }
                 __threadfence_block();
                 __syncwarp();
                 if (lane == 0) mbar_arrive(&s.land_full[st]);
             }
         }
-    } else if (warp == 5) {
+    } else if (warp == MMA_WARP) {
         // ================= MMA issuer =================
         if (lane == 0) {
             const uint32_t id1 = make_idesc_tf32(128, 64, false, false);
@@ -207,33 +231,66 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_step_kernel(const GridArgs a
             umma_commit(&s.a2_free);
         }
     } else {
-        // ================= row workers (warps 0-3) =================
-        const int r = tid;                                        // tile row == TMEM lane
-        const uint32_t lane_addr = uint32_t(warp * 32) << 16;
+        // ================= row workers: group 0 = warps 0-3, group 1 = warps 4-7 =================
+        const int grp = warp >> 2;
+        const int r = tid & (TILE - 1);                           // tile row == TMEM lane
+        const uint32_t lane_addr = uint32_t((warp & 3) * 32) << 16;
+        const uint32_t acc_base = tm + TM_ACC + uint32_t(grp) * 128 + lane_addr;
         const bool drop = a.dropout_mode != WX_DROPOUT_OFF;
         const float ds = drop ? 1.25f : 1.0f;                     // 1/(1-0.2), train_lightning_ddp.py:60
         const uint2 key = make_uint2(uint32_t(a.seed), uint32_t(a.seed >> 32));
-        float gw2_0[64], gw2_1[64];
-#pragma unroll
-        for (int j = 0; j < 64; ++j) gw2_0[j] = gw2_1[j] = 0.0f;
         float gb2_0 = 0.0f, gb2_1 = 0.0f, loss_acc = 0.0f;
         const float b2_0 = s.w2[128], b2_1 = s.w2[129];
+        // optional phase timers (wx_debug_cta_times): cycles spent per phase by row 0 of each group, summed over tiles
+        const bool timing = a.dbg != nullptr && r == 0;
+        long long tph[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+        long long tmark = timing ? clock64() : 0;
+#define WX_TPH(k)                               \
+    do {                                        \
+        if (timing) {                           \
+            const long long now__ = clock64();  \
+            tph[k] += now__ - tmark;            \
+            tmark = now__;                      \
+        }                                       \
+    } while (0)
+        {   // zero this thread's dW2 sums in TMEM
+            float zero[16];
+#pragma unroll
+            for (int q = 0; q < 16; ++q) zero[q] = 0.0f;
+#pragma unroll
+            for (int c = 0; c < 8; ++c) tmem_st16(acc_base + c * 16, zero);
+            tmem_st_wait();
+        }
 
-        // Xaug row of tile-slot `i` -> K-major hi/lo operand tile (GEMM1 A)
+        // Xaug row of tile-slot `i` -> K-major hi/lo operand tile (GEMM1 A).  With the raw loader the row is
+        // standardised here, ((double)x - mean) * (1/std) rounded to fp32 (preprocess.py:38-41 + the cast at
+        // train_lightning_ddp.py:45, to within 1 ulp of the exact division), and written back to the landing buffer
+        // for its second use in phase B.
         auto convert = [&](int64_t i) {
             const int st = int(i % STAGES);
             const int64_t tile = blockIdx.x + i * gridDim.x;
             if (!mbar_wait(&s.land_full[st], uint32_t((i / STAGES) & 1))) s.err = 5;
             const bool valid = r < tile_rows(tile);
-            const float* lx = s.land_x[st] + r * F;
-#pragma unroll
+            float* lx = s.land_x[st];
+#pragma unroll 1
             for (int c4 = 0; c4 < 8; ++c4) {
                 float hi[4], lo[4];
 #pragma unroll
                 for (int e = 0; e < 4; ++e) {
                     const int c = c4 * 4 + e;
                     float v = 0.0f;
-                    if (valid) v = c < F ? lx[c] : (c == F ? 1.0f : 0.0f);
+                    if (valid && c < F) {
+                        if (!raw_cols) {
+                            v = lx[r * F + c];
+                        } else {
+                            const float xr = lx[c * TILE + r];
+                            v = __double2float_rn((double(xr) - s.mean[c]) * s.rstd[c]);
+                            if (xr != xr) v = (a.impute == WX_IMPUTE_MEAN) ? 0.0f : __int_as_float(0x7fc00000);
+                            lx[c * TILE + r] = v;
+                        }
+                    } else if (valid && c == F) {
+                        v = 1.0f;
+                    }
                     split_tf32(v, hi[e], lo[e]);
                 }
                 const uint32_t off = sw128_offset(r, c4 * 4);
@@ -244,30 +301,35 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_step_kernel(const GridArgs a
             mbar_arrive(&s.xk_ready);
         };
 
-        convert(0);
-        for (int64_t i = 0; i < my_tiles; ++i) {
+        // One convert call site (keeps the code small): each pass first converts this group's next tile-slot -- slot 0
+        // at once, any later slot once XK is back, i.e. GEMM1 of the slot before it has completed -- then processes it.
+        for (int64_t i = grp;; i += NGROUPS) {
+            if (i >= my_tiles) break;
+            if (i > 0 && !mbar_wait(&s.d1_full[(i - 1) & 1], uint32_t(((i - 1) >> 1) & 1))) s.err = 10;
+            convert(i);
+            WX_TPH(6);
             const int st = int(i % STAGES);
             const int64_t tile = blockIdx.x + i * gridDim.x;
             const bool valid = r < tile_rows(tile);
             const uint32_t d1 = d1_base + uint32_t(i & 1) * 64 + lane_addr;
-            if (!mbar_wait(&s.d1_full[i & 1], uint32_t((i >> 1) & 1))) s.err = 6;
-            tc_fence_after();
-            if (i + 1 < my_tiles) convert(i + 1);                 // GEMM1(i+1) overlaps the pointwise work below
-
-            // ---- dropout keep bits for this row ----
+            WX_TPH(7);
+            // ---- dropout keep bits for this row: independent of GEMM1, so they are generated while it runs ----
             uint64_t keep = ~0ull;
             if (a.dropout_mode == WX_DROPOUT_MASK) keep = s.land_m[st][r];
             else if (a.dropout_mode == WX_DROPOUT_PHILOX) keep = wxk::philox_keep_mask(uint64_t(tile * TILE + r), key, step_word);
             const int yv = int(s.land_y[st][r]);
+            WX_TPH(1);
+            if (!mbar_wait(&s.d1_full[i & 1], uint32_t((i >> 1) & 1))) s.err = 6;
+            tc_fence_after();
+            WX_TPH(0);
 
             // ---- phase A: a = dropout(relu(z)), logits ----
             float lg0 = 0.0f, lg1 = 0.0f, lg0b = 0.0f, lg1b = 0.0f;
             uint64_t gate = 0;
-#pragma unroll
+#pragma unroll 1
             for (int cc = 0; cc < 4; ++cc) {
                 float z[16];
                 tmem_ld16(d1 + cc * 16, z);
-                tmem_ld_wait();
                 float w0[16], w1[16];
 #pragma unroll
                 for (int q4 = 0; q4 < 4; ++q4) {
@@ -277,6 +339,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_step_kernel(const GridArgs a
                 }
                 const uint32_t kb = uint32_t(keep >> (cc * 16)) & 0xffffu;
                 uint32_t gb = 0;
+                tmem_ld_wait();
 #pragma unroll
                 for (int q = 0; q < 16; ++q) {
                     const float h = (z[q] <= 0.0f) ? 0.0f : z[q];                     // relu, NaN passes like torch
@@ -307,19 +370,24 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_step_kernel(const GridArgs a
                 gb2_0 += dl0;
                 gb2_1 += dl1;
             }
+            WX_TPH(2);
             // ---- GEMM2 operands may be rewritten once the previous tile's GEMM2 has drained ----
             if (i > 0 && !mbar_wait(&s.a2_free, uint32_t((i - 1) & 1))) s.err = 7;
+            WX_TPH(3);
             // Xaug row (MN-major): features, 1, dl0, dl1
             {
-                const float* lx = s.land_x[st] + r * F;
-#pragma unroll
+                const float* lx = s.land_x[st];
+#pragma unroll 1
                 for (int g8 = 0; g8 < 4; ++g8) {
                     float hi[8], lo[8];
 #pragma unroll
                     for (int e = 0; e < 8; ++e) {
                         const int c = g8 * 8 + e;
                         float v = 0.0f;
-                        if (valid) v = c < F ? lx[c] : (c == F ? 1.0f : (c == F + 1 ? dl0 : (c == F + 2 ? dl1 : 0.0f)));
+                        if (valid) {
+                            if (c < F) v = raw_cols ? lx[c * TILE + r] : lx[r * F + c];
+                            else v = c == F ? 1.0f : (c == F + 1 ? dl0 : (c == F + 2 ? dl1 : 0.0f));
+                        }
                         split_tf32(v, hi[e], lo[e]);
                     }
                     const uint32_t off = mn32_offset(g8 * 8, r, 512, 512);
@@ -329,14 +397,17 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_step_kernel(const GridArgs a
                     st4(s.xm_lo, off + 16, lo[4], lo[5], lo[6], lo[7]);
                 }
             }
-            // ---- phase B: dW2 sums in registers, dh -> GEMM2 A operand ----
-#pragma unroll
+            WX_TPH(4);
+            // ---- phase B: dW2 sums (TMEM read-modify-write), dh -> GEMM2 A operand ----
+#pragma unroll 1
             for (int cc = 0; cc < 4; ++cc) {
-                float z[16];
+                float z[16], g0[16], g1[16];
                 tmem_ld16(d1 + cc * 16, z);
-                tmem_ld_wait();
+                tmem_ld16(acc_base + cc * 16, g0);
+                tmem_ld16(acc_base + 64 + cc * 16, g1);
                 const uint32_t kb = uint32_t(keep >> (cc * 16)) & 0xffffu;
                 const uint32_t gb = uint32_t(gate >> (cc * 16)) & 0xffffu;
+                tmem_ld_wait();
 #pragma unroll
                 for (int g8 = 0; g8 < 2; ++g8) {
                     float hi[8], lo[8];
@@ -346,11 +417,11 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_step_kernel(const GridArgs a
                     const float w1[8] = {t0.x, t0.y, t0.z, t0.w, t1.x, t1.y, t1.z, t1.w};
 #pragma unroll
                     for (int e = 0; e < 8; ++e) {
-                        const int q = g8 * 8 + e, j = cc * 16 + q;
+                        const int q = g8 * 8 + e;
                         const float h = (z[q] <= 0.0f) ? 0.0f : z[q];
                         const float av = h * (((kb >> q) & 1u) ? ds : 0.0f);
-                        gw2_0[j] = fmaf(dl0, av, gw2_0[j]);
-                        gw2_1[j] = fmaf(dl1, av, gw2_1[j]);
+                        g0[q] = fmaf(dl0, av, g0[q]);
+                        g1[q] = fmaf(dl1, av, g1[q]);
                         const float t = fmaf(dl1, w1[e], dl0 * w0[e]);
                         const float dh = ((gb >> q) & 1u) ? t * ds : 0.0f;
                         split_tf32(dh, hi[e], lo[e]);
@@ -361,48 +432,69 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_step_kernel(const GridArgs a
                     st4(s.a_lo, off, lo[0], lo[1], lo[2], lo[3]);
                     st4(s.a_lo, off + 16, lo[4], lo[5], lo[6], lo[7]);
                 }
+                tmem_st16(acc_base + cc * 16, g0);
+                tmem_st16(acc_base + 64 + cc * 16, g1);
             }
+            tmem_st_wait();
             fence_proxy_async();
             tc_fence_before();
             mbar_arrive(&s.a2_ready);
             mbar_arrive(&s.land_empty[st]);
+            WX_TPH(5);
         }
+        if (timing)
+            for (int k = 0; k < 8; ++k) a.dbg[1184 * 4 + (blockIdx.x * 2 + grp) * 8 + k] = tph[k];
         // ---- all tiles done: wait for the last GEMM2, then assemble the CTA slab ----
         if (!mbar_wait(&s.a2_free, uint32_t((my_tiles - 1) & 1))) s.err = 8;
         tc_fence_after();
-        // G[m][n] (M=64 accumulator: row m = 16*warp + lane, lanes 0-15 of each sub-partition)
-        for (int c0 = 0; c0 < N2; c0 += 16) {
-            float v[16];
-            tmem_ld16(g_base + lane_addr + c0, v);
-            tmem_ld_wait();
-            if (lane < 16) {
-                const int m = warp * 16 + lane;
+        asm volatile("bar.sync 1, 256;" ::: "memory");
+        if (grp == 0) {
+            // G[m][n] (M=64 accumulator: row m = 16*warp + lane, lanes 0-15 of each sub-partition)
+            for (int c0 = 0; c0 < N2; c0 += 16) {
+                float v[16];
+                tmem_ld16(g_base + lane_addr + c0, v);
+                tmem_ld_wait();
+                if (lane < 16) {
+                    const int m = (warp & 3) * 16 + lane;
 #pragma unroll
-                for (int q = 0; q < 16; ++q) {
-                    const int n = c0 + q;
-                    if (n < F) s.slab[m * F + n] = v[q];             // dW1[m][n]
-                    else if (n == F) s.slab[OFF_B1 + m] = v[q];      // db1[m]
+                    for (int q = 0; q < 16; ++q) {
+                        const int n = c0 + q;
+                        if (n < F) s.slab[m * F + n] = v[q];             // dW1[m][n]
+                        else if (n == F) s.slab[OFF_B1 + m] = v[q];      // db1[m]
+                    }
                 }
             }
         }
-        // dW2: every row worker holds 128 partial sums -> ordered column sums through smem (a_hi/a_lo are free now)
+        // dW2 / db2 / loss: per-thread sums -> ordered column sums through smem (a_hi/a_lo are free now), one group at a time
         float* red = s.a_hi;                                          // [128 rows][128] floats = 64 KB = a_hi + a_lo
+        s.red_small[tid][0] = gb2_0;
+        s.red_small[tid][1] = gb2_1;
+        s.red_small[tid][2] = loss_acc;
+        float colsum = 0.0f;
+#pragma unroll 1
+        for (int g = 0; g < NGROUPS; ++g) {
+            if (grp == g) {
+#pragma unroll 1
+                for (int c = 0; c < 8; ++c) {
+                    float v[16];
+                    tmem_ld16(acc_base + c * 16, v);
+                    tmem_ld_wait();
 #pragma unroll
-        for (int j = 0; j < 64; ++j) {
-            red[r * 128 + j] = gw2_0[j];
-            red[r * 128 + 64 + j] = gw2_1[j];
+                    for (int q4 = 0; q4 < 4; ++q4)
+                        *reinterpret_cast<float4*>(&red[r * 128 + c * 16 + q4 * 4]) =
+                            make_float4(v[q4 * 4], v[q4 * 4 + 1], v[q4 * 4 + 2], v[q4 * 4 + 3]);
+                }
+            }
+            asm volatile("bar.sync 1, 256;" ::: "memory");
+            if (grp == 0)
+                for (int k = 0; k < TILE; ++k) colsum += red[k * 128 + r];
+            asm volatile("bar.sync 1, 256;" ::: "memory");
         }
-        s.red_small[r][0] = gb2_0;
-        s.red_small[r][1] = gb2_1;
-        s.red_small[r][2] = loss_acc;
-        asm volatile("bar.sync 1, 128;" ::: "memory");
-        {
-            float acc = 0.0f;
-            for (int k = 0; k < TILE; ++k) acc += red[k * 128 + r];
-            s.slab[OFF_W2 + r] = acc;
+        if (grp == 0) {
+            s.slab[OFF_W2 + r] = colsum;
             if (r < 3) {
                 float t = 0.0f;
-                for (int k = 0; k < TILE; ++k) t += s.red_small[k][r];
+                for (int k = 0; k < WORKERS; ++k) t += s.red_small[k][r];
                 s.slab[r < 2 ? OFF_B2 + r : P] = t;
             }
         }
@@ -430,17 +522,15 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_step_kernel(const GridArgs a
     __syncthreads();
     const unsigned nparts = gridDim.x;
     for (int i = tid; i < P + 1; i += TC_THREADS) {
-        float acc[4] = {0.0f, 0.0f, 0.0f, 0.0f};
         const float* q = a.part + i;
         unsigned b = 0;
         float sum = 0.0f;
-        for (; b + 4 <= nparts; b += 4) {
+        for (; b + 8 <= nparts; b += 8) {
+            float t[8];
 #pragma unroll
-            for (int u = 0; u < 4; ++u) acc[u] = __ldcg(q + size_t(b + u) * slab_stride);
-            sum += acc[0];
-            sum += acc[1];
-            sum += acc[2];
-            sum += acc[3];
+            for (int u = 0; u < 8; ++u) t[u] = __ldcg(q + size_t(b + u) * slab_stride);
+#pragma unroll
+            for (int u = 0; u < 8; ++u) sum += t[u];
         }
         for (; b < nparts; ++b) sum += __ldcg(q + size_t(b) * slab_stride);
         if (i == P) sum *= a.scale;
@@ -471,8 +561,14 @@ int tc_launch(wx_ctx* ctx, GridArgs& a, cudaStream_t st, const char* who) {
     const int f = ctx->desc.n_features;
     WX_CHECK_ARG(f <= MAXF_TC, "%s: the tensor-core path is built for n_features <= %d (got %d)", who, MAXF_TC, f);
     WX_CHECK_ARG(a.row_idx == nullptr, "%s: the tensor-core path takes contiguous rows only (row_idx must be NULL)", who);
-    WX_CHECK_ARG(((reinterpret_cast<uintptr_t>(a.x) + size_t(a.row0) * f * 4) & 15) == 0,
-                 "%s: first row of the batch must start on a 16-byte boundary for the TMA loads", who);
+    if (a.loader == wxk::LOAD_ROWMAJOR) {
+        WX_CHECK_ARG(((reinterpret_cast<uintptr_t>(a.x) + size_t(a.row0) * f * 4) & 15) == 0,
+                     "%s: first row of the batch must start on a 16-byte boundary for the TMA loads", who);
+    } else {
+        for (int j = 0; j < f; ++j)
+            WX_CHECK_ARG(((reinterpret_cast<uintptr_t>(a.cols.col[j]) + size_t(a.row0) * 4) & 15) == 0,
+                         "%s: column %d must be 16-byte aligned at row0 for the TMA loads (row0 %% 4 == 0)", who, j);
+    }
     WX_CHECK_ARG(((reinterpret_cast<uintptr_t>(a.y) + size_t(a.row0) * 8) & 15) == 0,
                  "%s: labels of the batch must start on a 16-byte boundary for the TMA loads", who);
     WX_CHECK_ARG(a.dropout_mode != WX_DROPOUT_MASK || (reinterpret_cast<uintptr_t>(a.keep_mask) & 15) == 0,
@@ -501,6 +597,15 @@ int tc_launch(wx_ctx* ctx, GridArgs& a, cudaStream_t st, const char* who) {
     return WX_OK;
 }
 
+int tc_check_common(wx_ctx* ctx, int& dropout_mode, const uint64_t* keep_mask, int64_t row0, int64_t batch, const char* who) {
+    WX_CHECK_ARG(batch >= 1 && row0 >= 0, "%s: batch=%lld row0=%lld", who, (long long)batch, (long long)row0);
+    WX_CHECK_ARG(dropout_mode == WX_DROPOUT_OFF || dropout_mode == WX_DROPOUT_MASK || dropout_mode == WX_DROPOUT_PHILOX,
+                 "%s: dropout_mode=%d", who, dropout_mode);
+    WX_CHECK_ARG(dropout_mode != WX_DROPOUT_MASK || keep_mask != nullptr, "%s: WX_DROPOUT_MASK needs keep_mask", who);
+    if (ctx->desc.dropout_p == 0.0f) dropout_mode = WX_DROPOUT_OFF;
+    return WX_OK;
+}
+
 }  // namespace
 
 extern "C" {
@@ -510,14 +615,12 @@ int wx_tc_mlp_grad(wx_ctx* ctx, const float* params, const float* x, const int64
                    void* stream) {
     WX_CHECK_ARG(ctx != nullptr, "wx_tc_mlp_grad: ctx is NULL");
     WX_CHECK_ARG(params && x && y && out, "wx_tc_mlp_grad: NULL params/x/y/out");
-    WX_CHECK_ARG(batch >= 1 && row0 >= 0, "wx_tc_mlp_grad: batch=%lld row0=%lld", (long long)batch, (long long)row0);
-    WX_CHECK_ARG(dropout_mode == WX_DROPOUT_OFF || dropout_mode == WX_DROPOUT_MASK || dropout_mode == WX_DROPOUT_PHILOX,
-                 "wx_tc_mlp_grad: dropout_mode=%d", dropout_mode);
-    WX_CHECK_ARG(dropout_mode != WX_DROPOUT_MASK || keep_mask != nullptr, "wx_tc_mlp_grad: WX_DROPOUT_MASK needs keep_mask");
-    if (ctx->desc.dropout_p == 0.0f) dropout_mode = WX_DROPOUT_OFF;
+    int rc = tc_check_common(ctx, dropout_mode, keep_mask, row0, batch, "wx_tc_mlp_grad");
+    if (rc) return rc;
     GridArgs a;
     memset(&a, 0, sizeof(a));
     a.params = params;
+    a.loader = wxk::LOAD_ROWMAJOR;
     a.x = x;
     a.y = y;
     a.row0 = row0;
@@ -537,14 +640,12 @@ int wx_tc_train_step(wx_ctx* ctx, float* params, float* m, float* v, int64_t* st
                      float* loss_out, void* stream) {
     WX_CHECK_ARG(ctx != nullptr, "wx_tc_train_step: ctx is NULL");
     WX_CHECK_ARG(params && m && v && state && x && y && loss_out, "wx_tc_train_step: NULL pointer");
-    WX_CHECK_ARG(batch >= 1 && row0 >= 0, "wx_tc_train_step: batch=%lld row0=%lld", (long long)batch, (long long)row0);
-    WX_CHECK_ARG(dropout_mode == WX_DROPOUT_OFF || dropout_mode == WX_DROPOUT_MASK || dropout_mode == WX_DROPOUT_PHILOX,
-                 "wx_tc_train_step: dropout_mode=%d", dropout_mode);
-    WX_CHECK_ARG(dropout_mode != WX_DROPOUT_MASK || keep_mask != nullptr, "wx_tc_train_step: WX_DROPOUT_MASK needs keep_mask");
-    if (ctx->desc.dropout_p == 0.0f) dropout_mode = WX_DROPOUT_OFF;
+    int rc = tc_check_common(ctx, dropout_mode, keep_mask, row0, batch, "wx_tc_train_step");
+    if (rc) return rc;
     GridArgs a;
     memset(&a, 0, sizeof(a));
     a.params = params;
+    a.loader = wxk::LOAD_ROWMAJOR;
     a.x = x;
     a.y = y;
     a.row0 = row0;
@@ -560,6 +661,42 @@ int wx_tc_train_step(wx_ctx* ctx, float* params, float* m, float* v, int64_t* st
     a.state = state;
     a.loss_out = loss_out;
     return tc_launch(ctx, a, (cudaStream_t)stream, "wx_tc_train_step");
+}
+
+int wx_tc_train_step_raw(wx_ctx* ctx, float* params, float* m, float* v, int64_t* state, const void* const* cols,
+                         const double* stats, int impute_mode, const int64_t* y, int64_t row0, int64_t batch,
+                         int dropout_mode, const uint64_t* keep_mask, uint64_t seed, float* loss_out, void* stream) {
+    WX_CHECK_ARG(ctx != nullptr, "wx_tc_train_step_raw: ctx is NULL");
+    WX_CHECK_ARG(params && m && v && state && cols && stats && y && loss_out, "wx_tc_train_step_raw: NULL pointer");
+    WX_CHECK_ARG(impute_mode == WX_IMPUTE_NONE || impute_mode == WX_IMPUTE_MEAN, "wx_tc_train_step_raw: impute_mode=%d",
+                 impute_mode);
+    int rc = tc_check_common(ctx, dropout_mode, keep_mask, row0, batch, "wx_tc_train_step_raw");
+    if (rc) return rc;
+    GridArgs a;
+    memset(&a, 0, sizeof(a));
+    const int f = ctx->desc.n_features;
+    for (int j = 0; j < f; ++j) {
+        WX_CHECK_ARG(cols[j] != nullptr, "wx_tc_train_step_raw: column %d is NULL", j);
+        a.cols.col[j] = cols[j];
+    }
+    a.params = params;
+    a.loader = wxk::LOAD_RAW_F32;
+    a.stats = stats;
+    a.impute = impute_mode;
+    a.y = y;
+    a.row0 = row0;
+    a.batch = batch;
+    a.dropout_mode = dropout_mode;
+    a.keep_mask = keep_mask;
+    a.seed = seed;
+    a.scale = 1.0f / float(batch);
+    a.tail = wxk::TAIL_ADAM;
+    a.p_rw = params;
+    a.m = m;
+    a.v = v;
+    a.state = state;
+    a.loss_out = loss_out;
+    return tc_launch(ctx, a, (cudaStream_t)stream, "wx_tc_train_step_raw");
 }
 
 /* Sticky protocol-error code of the tensor-core kernels (0 = none): a bounded mbarrier wait that expired. */

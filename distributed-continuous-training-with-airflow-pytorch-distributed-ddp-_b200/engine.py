@@ -26,12 +26,14 @@ def init_params_like_reference(n_features: int) -> torch.Tensor:
 
 class StepEngine:
     def __init__(self, n_features: int, device=0, world: int = 1, rank: int = 0, process_group=None,
-                 params: torch.Tensor | None = None, seed: int = 42, lr: float = 0.01, dropout_p: float = 0.2):
+                 params: torch.Tensor | None = None, seed: int = 42, lr: float = 0.01, dropout_p: float = 0.2,
+                 use_tc: bool = True):
         self.ctx = Context(n_features, device=device, dropout_p=dropout_p, lr=lr)
         self.device = self.ctx.device
         self.F = n_features
         self.P = n_params(n_features)
         self.world, self.rank = world, rank
+        self.use_tc = use_tc                # prefer the tcgen05 step kernel where its preconditions hold
         self.dist = process_group           # the torch.distributed module (NCCL) when world > 1
         if world > 1 and process_group is None:
             raise WxError("world > 1 needs an initialised torch.distributed (NCCL) handle")
@@ -74,8 +76,16 @@ class StepEngine:
              keep_mask=None) -> torch.Tensor:
         """One optimizer step on standardised row-major features.  Returns the device scalar `train_loss`."""
         if self.world == 1:
-            self.ctx.train_step(self.params, self.m, self.v, self.state, x, y, self.loss, row_idx=row_idx, row0=row0,
-                                batch=batch, dropout=dropout, keep_mask=keep_mask, seed=self._dropout_seed())
+            # both are CUDA kernels of libwxddp.so: the tcgen05 kernel when the batch is contiguous and TMA-aligned,
+            # the FFMA kernel otherwise (sampler indices, F > 29, odd alignment)
+            big = (batch if batch is not None else x.shape[0] - row0) >= 128 if row_idx is None else False
+            mask_ok = keep_mask is None or keep_mask.data_ptr() % 16 == 0
+            if self.use_tc and big and mask_ok and self.ctx.tc_ok_rowmajor(x, y, row0, row_idx):
+                self.ctx.tc_train_step(self.params, self.m, self.v, self.state, x, y, self.loss, row0=row0, batch=batch,
+                                       dropout=dropout, keep_mask=keep_mask, seed=self._dropout_seed())
+            else:
+                self.ctx.train_step(self.params, self.m, self.v, self.state, x, y, self.loss, row_idx=row_idx, row0=row0,
+                                    batch=batch, dropout=dropout, keep_mask=keep_mask, seed=self._dropout_seed())
             self.steps_done += 1
             return self.loss
         b = batch if batch is not None else (row_idx.numel() if row_idx is not None else x.shape[0] - row0)
@@ -93,9 +103,12 @@ class StepEngine:
         if self.stats is None:
             raise WxError("call fit_stats()/set_stats() before step_raw()")
         if self.world == 1:
-            self.ctx.train_step_raw(self.params, self.m, self.v, self.state, cols, self.stats, y, self.loss, row0=row0,
-                                    batch=batch, impute=impute, dropout=dropout, keep_mask=keep_mask,
-                                    seed=self._dropout_seed())
+            mask_ok = keep_mask is None or keep_mask.data_ptr() % 16 == 0
+            fn = self.ctx.train_step_raw
+            if self.use_tc and mask_ok and self.ctx.tc_ok_raw(cols, y, row0):
+                fn = self.ctx.tc_train_step_raw
+            fn(self.params, self.m, self.v, self.state, cols, self.stats, y, self.loss, row0=row0, batch=batch,
+               impute=impute, dropout=dropout, keep_mask=keep_mask, seed=self._dropout_seed())
             self.steps_done += 1
             return self.loss
         n = cols[0].numel()

@@ -203,6 +203,37 @@ class Context:
         check(self.lib.wx_tc_train_step(self._h, _p(params), _p(m), _p(v), _p(state), _p(x), _p(y), row0, batch, dropout,
                                         _p(keep_mask), seed, _p(loss_out), self._stream()))
 
+    def tc_train_step_raw(self, params, m, v, state, cols, stats, y, loss_out, *, row0: int = 0,
+                          batch: int | None = None, impute: int = IMPUTE_NONE, dropout: int = DROPOUT_PHILOX,
+                          keep_mask=None, seed: int = 0) -> None:
+        """wx_train_step_raw on the tensor cores: raw fp32 columns in, standardised in the kernel."""
+        self._opt_args(params, m, v, state, loss_out)
+        cp, _, dt, n = self._cols(cols, None)
+        if dt != WX_F32:
+            raise WxError("tc_train_step_raw takes float32 columns (use train_step_raw for float64)")
+        self._chk(stats, torch.float64, "stats", self.n_features * 4)
+        self._chk(y, torch.int64, "y", n)
+        if batch is None:
+            batch = n - row0
+        if row0 < 0 or row0 + batch > n:
+            raise WxError(f"rows {row0}..{row0 + batch} outside the table of {n}")
+        if dropout == DROPOUT_MASK:
+            self._chk(keep_mask, torch.int64, "keep_mask", batch)
+        check(self.lib.wx_tc_train_step_raw(self._h, _p(params), _p(m), _p(v), _p(state), cp, _p(stats), impute, _p(y),
+                                            row0, batch, dropout, _p(keep_mask), seed, _p(loss_out), self._stream()))
+
+    # -- kernel choice --------------------------------------------------------------------------------
+    TC_MAX_FEATURES = 29
+
+    def tc_ok_rowmajor(self, x, y, row0: int, row_idx=None) -> bool:
+        """True when the tensor-core step kernel can take this batch (contiguous rows, F <= 29, TMA alignment)."""
+        return (row_idx is None and self.n_features <= self.TC_MAX_FEATURES
+                and (x.data_ptr() + row0 * self.n_features * 4) % 16 == 0 and (y.data_ptr() + row0 * 8) % 16 == 0)
+
+    def tc_ok_raw(self, cols, y, row0: int) -> bool:
+        return (self.n_features <= self.TC_MAX_FEATURES and cols[0].dtype == torch.float32
+                and all((c.data_ptr() + row0 * 4) % 16 == 0 for c in cols) and (y.data_ptr() + row0 * 8) % 16 == 0)
+
     def tc_status(self) -> int:
         out = C.c_int(0)
         check(self.lib.wx_tc_last_status(self._h, C.byref(out)))

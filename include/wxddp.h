@@ -173,6 +173,11 @@ int wx_tc_mlp_grad(wx_ctx* ctx, const float* params, const float* x, const int64
 int wx_tc_train_step(wx_ctx* ctx, float* params, float* m, float* v, int64_t* state, const float* x, const int64_t* y,
                      int64_t row0, int64_t batch, int dropout_mode, const uint64_t* keep_mask, uint64_t seed,
                      float* loss_out, void* stream);
+/* Same step from RAW fp32 columns (standardisation fused in front, preprocess.py:38-41): the tensor-core counterpart
+ * of wx_train_step_raw.  Columns must be 16-byte aligned at row0 (row0 % 4 == 0 for 16-byte-aligned column bases). */
+int wx_tc_train_step_raw(wx_ctx* ctx, float* params, float* m, float* v, int64_t* state, const void* const* cols,
+                         const double* stats, int impute_mode, const int64_t* y, int64_t row0, int64_t batch,
+                         int dropout_mode, const uint64_t* keep_mask, uint64_t seed, float* loss_out, void* stream);
 int wx_tc_last_status(wx_ctx* ctx, int* host_out);
 
 /* Adam update of a flat fp32 vector, torch.optim.Adam semantics with the desc's hyper-parameters

@@ -57,3 +57,34 @@ for name, fn in [("tc", c.tc_train_step), ("v1", c.train_step)]:
         e1.record(); torch.cuda.synchronize()
         ms = e0.elapsed_time(e1) / 20
         print(f"{name} mode={mode} F={f} B={B}: {ms*1e3:.1f} us/step  {B/ms/1e6:.2f} G rows/s  loss={loss.item():.4f} status={c.tc_status()}", flush=True)
+# raw-column fused step: tc vs v1 (one Adam step from zero moments: m = 0.1 * grad)
+from oracle import synth, preprocess_ref
+for f, n, r0 in [(20, 30000, 0), (5, 9001, 4), (20, 128 * 148 + 64, 128)]:
+    t = synth.synth_table(5, n + r0, f, null_rate=0.01, const_col=(f - 1 if f > 5 else None))
+    c = wxddp.Context(f)
+    cols = [torch.from_numpy(t["raw"][j].astype(np.float32)).cuda() for j in range(f)]
+    stats = c.col_stats(cols)
+    yy = torch.from_numpy(preprocess_ref.label_encode(t["labels"]).astype(np.int64)).cuda()
+    p0 = (torch.randn(c.P, generator=torch.Generator().manual_seed(1)) * 0.2)
+    res = []
+    for fn in (c.train_step_raw, c.tc_train_step_raw):
+        p = p0.cuda(); m = torch.zeros_like(p); v = torch.zeros_like(p); st = torch.zeros(2, dtype=torch.int64, device="cuda"); loss = torch.zeros(1, device="cuda")
+        fn(p, m, v, st, cols, stats, yy, loss, row0=r0, batch=n, impute=1, dropout=2, seed=9)
+        torch.cuda.synchronize()
+        res.append((loss.item(), m.cpu().numpy(), p.cpu().numpy()))
+    dm = np.abs(res[0][1] - res[1][1]).max() / np.abs(res[0][1]).max()
+    print(f"raw F={f} n={n} row0={r0}: loss v1={res[0][0]:.7f} tc={res[1][0]:.7f} m relerr={dm:.2e} status={c.tc_status()}", flush=True)
+f, B = 20, 1 << 20
+c = wxddp.Context(f)
+raw = torch.randn(f, 8 * B, device="cuda") * 5 + 20; cols = [raw[j] for j in range(f)]
+stats = c.col_stats(cols); yy = (torch.rand(8 * B, device="cuda") < 0.2).long()
+p = torch.randn(c.P, device="cuda") * 0.2; m = torch.zeros_like(p); v = torch.zeros_like(p)
+st = torch.zeros(2, dtype=torch.int64, device="cuda"); loss = torch.zeros(1, device="cuda")
+for name, fn in [("tc_raw", c.tc_train_step_raw), ("v1_raw", c.train_step_raw)]:
+    for i in range(3): fn(p, m, v, st, cols, stats, yy, loss, row0=(i % 8) * B, batch=B, impute=1, dropout=2, seed=3)
+    torch.cuda.synchronize(); e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(20): fn(p, m, v, st, cols, stats, yy, loss, row0=(i % 8) * B, batch=B, impute=1, dropout=2, seed=3)
+    e1.record(); torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / 20
+    print(f"{name} philox F={f} B={B}: {ms*1e3:.1f} us/step  {B/ms/1e6:.2f} G rows/s  loss={loss.item():.4f} status={c.tc_status()}", flush=True)
