@@ -164,7 +164,7 @@ def main() -> int:
     ap.add_argument("--table-rows", type=int, default=1 << 24)
     ap.add_argument("--cpu-rows-per-step", type=int, default=65536,
                     help="CPU arms: rows per step of the bounded sample (0 = --rows-per-step)")
-    ap.add_argument("--cpu-steps", type=int, default=8)
+    ap.add_argument("--cpu-steps", type=int, default=300)
     ap.add_argument("--kernel", default="auto", choices=["auto", "tc", "ffma"], help="step kernel at N=1")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")

@@ -40,6 +40,7 @@ SIGNATURES = {
     "wx_launch_count": (_i64, [_vp]),
     "wx_debug_cta_times": (_int, [_vp, _vp]),
     "wx_tc_selftest": (_int, [_vp, _vp, _vp, _vp, _int, _vp, _vp, _vp, _vp]),
+    "wx_tc_mma_bench": (_int, [_vp, _int, _int, _int, _vp, _vp]),
     "wx_label_encode": (_int, [_vp, _vp, _vp, _vp, _i64, _vp, _vp, _vp]),
     "wx_col_stats": (_int, [_vp, C.POINTER(_vp), _int, C.POINTER(_vp), _i64, _vp, _vp]),
     "wx_stats_merge": (_int, [_vp, _vp, _int, _vp, _vp]),

@@ -36,10 +36,19 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
 // Bounded wait: returns false if the barrier did not flip within ~2 s (a protocol bug must not hang the GPU).
 __device__ __forceinline__ bool mbar_wait(uint64_t* bar, uint32_t parity) {
     if (mbar_try_wait(bar, parity)) return true;
+#pragma unroll 1
     for (uint32_t spin = 0; spin < (1u << 24); ++spin) {
         __nanosleep(40);                      // back off: idle roles must not steal issue slots from the row workers
         if (mbar_try_wait(bar, parity)) return true;
     }
+    return false;
+}
+
+// Latency-critical variant for the MMA issuer: tight polling (try_wait itself blocks for a hardware time slice).
+__device__ __forceinline__ bool mbar_wait_hot(uint64_t* bar, uint32_t parity) {
+#pragma unroll 1
+    for (uint32_t spin = 0; spin < (1u << 28); ++spin)
+        if (mbar_try_wait(bar, parity)) return true;
     return false;
 }
 
@@ -136,6 +145,27 @@ __device__ __forceinline__ void umma_tf32(uint32_t d_tmem, uint64_t adesc, uint6
         ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(acc)
         : "memory");
 }
+// Warp-collective forms: the WHOLE warp executes the call (operands stay warp-uniform, so they can live in uniform
+// registers instead of being converted per instruction); one elected lane issues.
+__device__ __forceinline__ void umma_tf32_warp(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc, bool accumulate) {
+    const uint32_t acc = accumulate ? 1u : 0u;
+    asm volatile(
+        "{\n\t.reg .pred p, q;\n\t"
+        "elect.sync _|q, 0xffffffff;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "@q tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
+        ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(acc)
+        : "memory");
+}
+__device__ __forceinline__ void umma_commit_warp(uint64_t* bar) {
+    asm volatile(
+        "{\n\t.reg .pred q;\n\t"
+        "elect.sync _|q, 0xffffffff;\n\t"
+        "@q tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n\t}"
+        ::"r"(smem_u32(bar))
+        : "memory");
+}
+
 // make the mbarrier observe completion of all previously issued tcgen05.mma of this thread
 __device__ __forceinline__ void umma_commit(uint64_t* bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");

@@ -136,3 +136,109 @@ extern "C" int wx_tc_selftest(wx_ctx* ctx, const float* x, const float* w, const
     WX_LAUNCH_CHECK(ctx);
     return WX_OK;
 }
+
+// ---- MMA issue/throughput micro-benchmark (developer aid): cycles per tcgen05.mma for the operand layouts in play ----
+namespace {
+using namespace wxtc;
+
+__global__ void __launch_bounds__(128) tc_mma_bench_kernel(int variant, int n_dim, int reps, long long* __restrict__ out) {
+    extern __shared__ __align__(1024) unsigned char raw[];
+    __shared__ uint64_t bar;
+    __shared__ uint32_t tmem_base;
+    const int t = threadIdx.x, warp = t >> 5;
+    for (int i = t; i < 96 * 1024 / 4; i += 128) reinterpret_cast<float*>(raw)[i] = 0.0f;
+    if (t == 0) {
+        mbar_init(&bar, 1);
+        fence_mbar_init();
+    }
+    if (warp == 0) tmem_alloc(&tmem_base, 128);
+    fence_proxy_async();
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    if (variant >= 8 && warp == 0) {
+        // warp-collective issue: whole warp runs the loop, one elected lane issues each MMA
+        const uint32_t base = smem_u32(raw);
+        const long long t0 = clock64();
+        if (variant == 8) {
+            const uint32_t id = make_idesc_tf32(128, n_dim, false, false);
+            const uint64_t ad = make_smem_desc(base, 16, 1024), bd = make_smem_desc(base + 32768, 16, 1024);
+            for (int r = 0; r < reps; ++r) {
+#pragma unroll
+                for (int k = 0; k < 4; ++k) umma_tf32_warp(tmem_base, ad + uint64_t(2 * k), bd + uint64_t(2 * k), id, true);
+            }
+        } else {
+            const uint32_t id = make_idesc_tf32(64, n_dim, true, true);
+            const uint64_t ad = make_smem_desc(base, 512, 1024, LAYOUT_SW128_B32), bd = make_smem_desc(base + 65536, 512, 512, LAYOUT_SW128_B32);
+            for (int r = 0; r < reps; ++r) {
+#pragma unroll
+                for (int k = 0; k < 4; ++k) umma_tf32_warp(tmem_base, ad + uint64_t(128 * k), bd + uint64_t(64 * k), id, true);
+            }
+        }
+        const long long t1 = clock64();
+        umma_commit_warp(&bar);
+        mbar_wait_hot(&bar, 0);
+        const long long t2 = clock64();
+        if (blockIdx.x == 0 && t == 0) {
+            out[0] = t1 - t0;
+            out[1] = t2 - t0;
+        }
+    } else if (variant < 8 && t == 0) {
+        const uint32_t base = smem_u32(raw);
+        const long long t0 = clock64();
+        for (int r = 0; r < reps; ++r) {
+            if (variant == 0) {          // GEMM1 as built: K-major SW128, M=128, N=n_dim, 4 k-steps inside one 128-B row
+                const uint32_t id = make_idesc_tf32(128, n_dim, false, false);
+                for (int k = 0; k < 4; ++k)
+                    umma_tf32(tmem_base, make_smem_desc(base + k * 32, 16, 1024), make_smem_desc(base + 32768 + k * 32, 16, 1024), id, true);
+            } else if (variant == 1) {   // GEMM1 candidate: K-major, no swizzle, one contiguous [rows][8] block per k-step
+                const uint32_t id = make_idesc_tf32(128, n_dim, false, false);
+                for (int k = 0; k < 4; ++k)
+                    umma_tf32(tmem_base, make_smem_desc(base + k * 4096, 128, 256, 0), make_smem_desc(base + 32768 + k * 2048, 128, 256, 0), id, true);
+            } else if (variant == 2) {   // GEMM2 as built: MN-major SW128_B32, M=64, N=n_dim
+                const uint32_t id = make_idesc_tf32(64, n_dim, true, true);
+                for (int k = 0; k < 4; ++k)
+                    umma_tf32(tmem_base, make_smem_desc(base + k * 2048, 512, 1024, LAYOUT_SW128_B32),
+                              make_smem_desc(base + 65536 + k * 1024, 512, 512, LAYOUT_SW128_B32), id, true);
+            } else if (variant == 4) {   // GEMM1 layout, four independent accumulators (columns 0,32,64,96), N <= 32
+                const uint32_t id = make_idesc_tf32(128, n_dim, false, false);
+                const uint64_t ad = make_smem_desc(base, 16, 1024), bd = make_smem_desc(base + 32768, 16, 1024);
+                for (int k = 0; k < 4; ++k) umma_tf32(tmem_base + 32 * k, ad + uint64_t(2 * k), bd + uint64_t(2 * k), id, true);
+            } else if (variant == 5) {   // GEMM1 layout, one accumulator, descriptors hoisted (pure issue cost of a dependent chain)
+                const uint32_t id = make_idesc_tf32(128, n_dim, false, false);
+                const uint64_t ad = make_smem_desc(base, 16, 1024), bd = make_smem_desc(base + 32768, 16, 1024);
+                for (int k = 0; k < 4; ++k) umma_tf32(tmem_base, ad + uint64_t(2 * k), bd + uint64_t(2 * k), id, true);
+            } else if (variant == 6) {   // GEMM2 layout, two independent accumulators
+                const uint32_t id = make_idesc_tf32(64, n_dim, true, true);
+                const uint64_t ad = make_smem_desc(base, 512, 1024, LAYOUT_SW128_B32), bd = make_smem_desc(base + 65536, 512, 512, LAYOUT_SW128_B32);
+                for (int k = 0; k < 4; ++k) umma_tf32(tmem_base + 32 * (k & 1), ad + uint64_t(128 * k), bd + uint64_t(64 * k), id, true);
+            } else {                     // GEMM2 candidate: K-major no swizzle, M=64, N=n_dim
+                const uint32_t id = make_idesc_tf32(64, n_dim, false, false);
+                for (int k = 0; k < 4; ++k)
+                    umma_tf32(tmem_base, make_smem_desc(base + k * 2048, 128, 256, 0), make_smem_desc(base + 65536 + k * 1024, 128, 256, 0), id, true);
+            }
+        }
+        const long long t1 = clock64();
+        umma_commit(&bar);
+        mbar_wait_hot(&bar, 0);
+        const long long t2 = clock64();
+        if (blockIdx.x == 0) {
+            out[0] = t1 - t0;
+            out[1] = t2 - t0;
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 0) tmem_dealloc(tmem_base, 128);
+}
+}  // namespace
+
+extern "C" int wx_tc_mma_bench(wx_ctx* ctx, int variant, int n_dim, int reps, long long* out, void* stream) {
+    WX_CHECK_ARG(ctx != nullptr && out != nullptr, "wx_tc_mma_bench: NULL argument");
+    WX_CUDA(cudaSetDevice(ctx->device));
+    const int smem = 97 * 1024;
+    WX_CUDA(cudaFuncSetAttribute(tc_mma_bench_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    tc_mma_bench_kernel<<<ctx->num_sms, 128, smem, (cudaStream_t)stream>>>(variant, n_dim, reps, out);
+    WX_LAUNCH_CHECK(ctx);
+    return WX_OK;
+}

@@ -37,7 +37,8 @@ constexpr int WORKERS = NGROUPS * TILE;          // 256 row-worker threads
 constexpr int TC_THREADS = WORKERS + 64;         // + producer warp + MMA warp
 constexpr int PRODUCER_WARP = WORKERS / 32, MMA_WARP = WORKERS / 32 + 1;
 constexpr int STAGES = 3;
-constexpr int MAXF_TC = 29;                      // F + 3 columns must fit the 32-column operand tile
+constexpr int MAXF_TC = 29;                      // F feature columns + 3 fixed columns fill the 32-column operand tile
+constexpr int COL_ONE = 29, COL_DL0 = 30, COL_DL1 = 31;   // fixed positions: selects on them are compile-time
 constexpr int TMEM_COLS = 512;                   // D1 x2 [0,128) | G [128,160) | dW2 sums of group g [256+128g, 384+128g)
 constexpr int TM_G = 128, TM_ACC = 256;
 
@@ -75,8 +76,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_step_kernel(const GridArgs a
     const int P = 64 * F + 194;
     const int OFF_B1 = 64 * F, OFF_W2 = 64 * F + 64, OFF_B2 = 64 * F + 192;
     const int slab_stride = (P + 1 + 3) & ~3;
-    const int K1 = ((F + 1) + 7) & ~7;            // GEMM1 K extent
-    const int N2 = ((F + 3) + 7) & ~7;            // GEMM2 N extent
+    constexpr int K1 = 32;                        // GEMM1 K extent: features [0,F) | zeros | 1 at column 29 (| dl at 30,31: zero weights)
+    constexpr int N2 = 32;                        // GEMM2 N extent
     const bool raw_cols = a.loader != wxk::LOAD_ROWMAJOR;
     const int64_t ntiles = (a.batch + TILE - 1) / TILE;
     const int64_t my_tiles = (ntiles - blockIdx.x + gridDim.x - 1) / gridDim.x;     // >= 1 by construction of the grid
@@ -113,7 +114,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_step_kernel(const GridArgs a
 #pragma unroll
             for (int e = 0; e < 4; ++e) {
                 const int c = c4 * 4 + e;
-                const float v = c < F ? a.params[n * F + c] : (c == F ? a.params[OFF_B1 + n] : 0.0f);
+                const float v = c < F ? a.params[n * F + c] : (c == COL_ONE ? a.params[OFF_B1 + n] : 0.0f);
                 split_tf32(v, hi[e], lo[e]);
             }
             const uint32_t off = sw128_offset(n, c4 * 4);
@@ -184,51 +185,85 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_step_kernel(const GridArgs a
         }
     } else if (warp == MMA_WARP) {
         // ================= MMA issuer =================
-        if (lane == 0) {
+        {
+            // The WHOLE warp runs this code and one elected lane issues each MMA: operands stay warp-uniform (uniform
+            // registers, no per-instruction conversion) -- 3x faster issue than a lone thread (profiles/: 84 -> 24 cycles
+            // per MMA).  One base descriptor per operand/term; a k-step only adds a constant to the start-address field.
             const uint32_t id1 = make_idesc_tf32(128, 64, false, false);
             const uint32_t id2 = make_idesc_tf32(64, N2, true, true);
-            const uint32_t xk[2] = {smem_u32(s.xk_hi), smem_u32(s.xk_lo)};
-            const uint32_t wk[2] = {smem_u32(s.w_hi), smem_u32(s.w_lo)};
-            const uint32_t am[2] = {smem_u32(s.a_hi), smem_u32(s.a_lo)};
-            const uint32_t xm[2] = {smem_u32(s.xm_hi), smem_u32(s.xm_lo)};
-            auto gemm2 = [&](bool first) {
+            const uint64_t xk_d[2] = {make_smem_desc(smem_u32(s.xk_hi), 16, 1024), make_smem_desc(smem_u32(s.xk_lo), 16, 1024)};
+            const uint64_t wk_d[2] = {make_smem_desc(smem_u32(s.w_hi), 16, 1024), make_smem_desc(smem_u32(s.w_lo), 16, 1024)};
+            const uint64_t am_d[2] = {make_smem_desc(smem_u32(s.a_hi), 512, 1024, LAYOUT_SW128_B32),
+                                      make_smem_desc(smem_u32(s.a_lo), 512, 1024, LAYOUT_SW128_B32)};
+            const uint64_t xm_d[2] = {make_smem_desc(smem_u32(s.xm_hi), 512, 512, LAYOUT_SW128_B32),
+                                      make_smem_desc(smem_u32(s.xm_lo), 512, 512, LAYOUT_SW128_B32)};
+            const int k1steps = K1 / 8;
+            auto gemm1 = [&](uint32_t d1) {
                 // small terms first: hi*lo, lo*hi, then hi*hi
-                bool acc = !first;
+                bool acc = false;
 #pragma unroll
                 for (int term = 0; term < 3; ++term) {
-                    const uint32_t ab = am[term == 1 ? 1 : 0], bb = xm[term == 0 ? 1 : 0];
-                    for (int k = 0; k < TILE / 8; ++k) {
-                        umma_tf32(g_base, make_smem_desc(ab + k * 2048, 512, 1024, LAYOUT_SW128_B32),
-                                  make_smem_desc(bb + k * 1024, 512, 512, LAYOUT_SW128_B32), id2, acc);
+                    const uint64_t ad = xk_d[term == 1 ? 1 : 0], bd = wk_d[term == 0 ? 1 : 0];
+#pragma unroll 4
+                    for (int k = 0; k < k1steps; ++k) {
+                        umma_tf32_warp(d1, ad + uint64_t(k * 2), bd + uint64_t(k * 2), id1, acc);       // +32 B per k-step
                         acc = true;
                     }
                 }
             };
-            for (int64_t i = 0; i < my_tiles; ++i) {
-                if (!mbar_wait(&s.xk_ready, uint32_t(i & 1))) s.err = 3;
-                tc_fence_after();
-                const uint32_t d1 = d1_base + uint32_t(i & 1) * 64;
-                bool acc = false;
+            auto gemm2 = [&](bool first) {
+                bool acc = !first;
 #pragma unroll
                 for (int term = 0; term < 3; ++term) {
-                    const uint32_t ab = xk[term == 1 ? 1 : 0], bb = wk[term == 0 ? 1 : 0];
-                    for (int k = 0; k < K1 / 8; ++k) {
-                        umma_tf32(d1, make_smem_desc(ab + k * 32, 16, 1024), make_smem_desc(bb + k * 32, 16, 1024), id1, acc);
+                    const uint64_t ad = am_d[term == 1 ? 1 : 0], bd = xm_d[term == 0 ? 1 : 0];
+#pragma unroll
+                    for (int k = 0; k < TILE / 8; ++k) {
+                        umma_tf32_warp(g_base, ad + uint64_t(k * 128), bd + uint64_t(k * 64), id2, acc);  // +2048 B / +1024 B
                         acc = true;
                     }
                 }
-                umma_commit(&s.d1_full[i & 1]);
+            };
+            const bool mt = a.dbg != nullptr && lane == 0;
+            long long mph[6] = {0, 0, 0, 0, 0, 0};
+            long long mk = mt ? clock64() : 0;
+#define WX_MPH(k)                               \
+    do {                                        \
+        if (mt) {                               \
+            const long long now__ = clock64();  \
+            mph[k] += now__ - mk;               \
+            mk = now__;                         \
+        }                                       \
+    } while (0)
+            for (int64_t i = 0; i < my_tiles; ++i) {
+                if (!mbar_wait_hot(&s.xk_ready, uint32_t(i & 1))) s.err = 3;
+                tc_fence_after();
+                WX_MPH(0);
+                gemm1(d1_base + uint32_t(i & 1) * 64);
+                umma_commit_warp(&s.d1_full[i & 1]);
+                WX_MPH(1);
+                if (mt && (i & 7) == 3) {          // sampled: how long does GEMM1 take to complete once issued?
+                    mbar_wait_hot(&s.d1_full[i & 1], uint32_t((i >> 1) & 1));
+                    WX_MPH(4);
+                }
                 if (i > 0) {
-                    if (!mbar_wait(&s.a2_ready, uint32_t((i - 1) & 1))) s.err = 4;
+                    if (!mbar_wait_hot(&s.a2_ready, uint32_t((i - 1) & 1))) s.err = 4;
                     tc_fence_after();
+                    WX_MPH(2);
                     gemm2(i - 1 == 0);
-                    umma_commit(&s.a2_free);
+                    umma_commit_warp(&s.a2_free);
+                    WX_MPH(3);
+                    if (mt && (i & 7) == 5) {      // sampled: GEMM2 completion latency
+                        mbar_wait_hot(&s.a2_free, uint32_t((i - 1) & 1));
+                        WX_MPH(5);
+                    }
                 }
             }
-            if (!mbar_wait(&s.a2_ready, uint32_t((my_tiles - 1) & 1))) s.err = 4;
+            if (mt)
+                for (int k = 0; k < 6; ++k) a.dbg[1184 * 4 + 148 * 16 + blockIdx.x * 8 + k] = mph[k];
+            if (!mbar_wait_hot(&s.a2_ready, uint32_t((my_tiles - 1) & 1))) s.err = 4;
             tc_fence_after();
             gemm2(my_tiles - 1 == 0);
-            umma_commit(&s.a2_free);
+            umma_commit_warp(&s.a2_free);
         }
     } else {
         // ================= row workers: group 0 = warps 0-3, group 1 = warps 4-7 =================
@@ -271,31 +306,41 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_step_kernel(const GridArgs a
             const int64_t tile = blockIdx.x + i * gridDim.x;
             if (!mbar_wait(&s.land_full[st], uint32_t((i / STAGES) & 1))) s.err = 5;
             const bool valid = r < tile_rows(tile);
-            float* lx = s.land_x[st];
+            float* lx = s.land_x[st] + (raw_cols ? r : r * F);     // element c of this row at lx[c * cstride]
+            const int cstride = raw_cols ? TILE : 1;
 #pragma unroll 1
-            for (int c4 = 0; c4 < 8; ++c4) {
-                float hi[4], lo[4];
+            for (int c8 = 0; c8 < 4; ++c8) {
+                float t[8];
 #pragma unroll
-                for (int e = 0; e < 4; ++e) {
-                    const int c = c4 * 4 + e;
-                    float v = 0.0f;
-                    if (valid && c < F) {
-                        if (!raw_cols) {
-                            v = lx[r * F + c];
-                        } else {
-                            const float xr = lx[c * TILE + r];
-                            v = __double2float_rn((double(xr) - s.mean[c]) * s.rstd[c]);
+                for (int e = 0; e < 8; ++e) {                       // unconditional (clamped) loads: all eight in flight
+                    const int c = c8 * 8 + e;
+                    t[e] = lx[(c < F ? c : F - 1) * cstride];
+                }
+                if (raw_cols) {
+#pragma unroll
+                    for (int e = 0; e < 8; ++e) {
+                        const int c = c8 * 8 + e;
+                        if (c < F) {
+                            const float xr = t[e];
+                            float v = __double2float_rn((double(xr) - s.mean[c]) * s.rstd[c]);
                             if (xr != xr) v = (a.impute == WX_IMPUTE_MEAN) ? 0.0f : __int_as_float(0x7fc00000);
-                            lx[c * TILE + r] = v;
+                            t[e] = v;
+                            lx[c * cstride] = v;                    // second use in phase B
                         }
-                    } else if (valid && c == F) {
-                        v = 1.0f;
                     }
+                }
+                float hi[8], lo[8];
+#pragma unroll
+                for (int e = 0; e < 8; ++e) {
+                    const int c = c8 * 8 + e;
+                    const float v = !valid ? 0.0f : (c == COL_ONE ? 1.0f : (c < COL_ONE && c < F ? t[e] : 0.0f));
                     split_tf32(v, hi[e], lo[e]);
                 }
-                const uint32_t off = sw128_offset(r, c4 * 4);
-                st4(s.xk_hi, off, hi[0], hi[1], hi[2], hi[3]);
-                st4(s.xk_lo, off, lo[0], lo[1], lo[2], lo[3]);
+                const uint32_t off0 = sw128_offset(r, c8 * 8), off1 = sw128_offset(r, c8 * 8 + 4);
+                st4(s.xk_hi, off0, hi[0], hi[1], hi[2], hi[3]);
+                st4(s.xk_hi, off1, hi[4], hi[5], hi[6], hi[7]);
+                st4(s.xk_lo, off0, lo[0], lo[1], lo[2], lo[3]);
+                st4(s.xk_lo, off1, lo[4], lo[5], lo[6], lo[7]);
             }
             fence_proxy_async();
             mbar_arrive(&s.xk_ready);
@@ -371,23 +416,59 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_step_kernel(const GridArgs a
                 gb2_1 += dl1;
             }
             WX_TPH(2);
+            // ---- phase B (still off the critical path: touches registers and TMEM only) ----
+            // dW2 sums (TMEM read-modify-write) and dh for all 64 units, kept in registers until the GEMM2 operand
+            // buffers are free.  ds is folded into the dlogits: (dl*ds)*zg == dl*(zg*ds) up to one rounding.
+            float dhv[64];
+            {
+                const float dl0s = dl0 * ds, dl1s = dl1 * ds;
+#pragma unroll
+                for (int cc = 0; cc < 4; ++cc) {
+                    float z[16], g0[16], g1[16];
+                    tmem_ld16(d1 + cc * 16, z);
+                    tmem_ld16(acc_base + cc * 16, g0);
+                    tmem_ld16(acc_base + 64 + cc * 16, g1);
+                    const uint32_t gb = uint32_t(gate >> (cc * 16)) & 0xffffu;
+                    float w0[16], w1[16];
+#pragma unroll
+                    for (int q4 = 0; q4 < 4; ++q4) {
+                        const float4 u = ld4(&s.w2[cc * 16 + q4 * 4]), t = ld4(&s.w2[64 + cc * 16 + q4 * 4]);
+                        w0[q4 * 4] = u.x; w0[q4 * 4 + 1] = u.y; w0[q4 * 4 + 2] = u.z; w0[q4 * 4 + 3] = u.w;
+                        w1[q4 * 4] = t.x; w1[q4 * 4 + 1] = t.y; w1[q4 * 4 + 2] = t.z; w1[q4 * 4 + 3] = t.w;
+                    }
+                    tmem_ld_wait();
+#pragma unroll
+                    for (int q = 0; q < 16; ++q) {
+                        const bool on = (gb >> q) & 1u;                    // unit active: z > 0 (or NaN) and kept
+                        const float zg = on ? z[q] : 0.0f;
+                        g0[q] = fmaf(dl0s, zg, g0[q]);
+                        g1[q] = fmaf(dl1s, zg, g1[q]);
+                        dhv[cc * 16 + q] = on ? fmaf(dl1s, w1[q], dl0s * w0[q]) : 0.0f;
+                    }
+                    tmem_st16(acc_base + cc * 16, g0);
+                    tmem_st16(acc_base + 64 + cc * 16, g1);
+                }
+            }
             // ---- GEMM2 operands may be rewritten once the previous tile's GEMM2 has drained ----
             if (i > 0 && !mbar_wait(&s.a2_free, uint32_t((i - 1) & 1))) s.err = 7;
             WX_TPH(3);
             // Xaug row (MN-major): features, 1, dl0, dl1
             {
-                const float* lx = s.land_x[st];
+                const float* lx = s.land_x[st] + (raw_cols ? r : r * F);
+                const int cstride = raw_cols ? TILE : 1;
 #pragma unroll 1
                 for (int g8 = 0; g8 < 4; ++g8) {
-                    float hi[8], lo[8];
+                    float t[8], hi[8], lo[8];
 #pragma unroll
                     for (int e = 0; e < 8; ++e) {
                         const int c = g8 * 8 + e;
-                        float v = 0.0f;
-                        if (valid) {
-                            if (c < F) v = raw_cols ? lx[c * TILE + r] : lx[r * F + c];
-                            else v = c == F ? 1.0f : (c == F + 1 ? dl0 : (c == F + 2 ? dl1 : 0.0f));
-                        }
+                        t[e] = lx[(c < F ? c : F - 1) * cstride];
+                    }
+#pragma unroll
+                    for (int e = 0; e < 8; ++e) {
+                        const int c = g8 * 8 + e;
+                        const float v = !valid ? 0.0f
+                                               : (c == COL_ONE ? 1.0f : (c == COL_DL0 ? dl0 : (c == COL_DL1 ? dl1 : (c < F ? t[e] : 0.0f))));
                         split_tf32(v, hi[e], lo[e]);
                     }
                     const uint32_t off = mn32_offset(g8 * 8, r, 512, 512);
@@ -398,42 +479,17 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_step_kernel(const GridArgs a
                 }
             }
             WX_TPH(4);
-            // ---- phase B: dW2 sums (TMEM read-modify-write), dh -> GEMM2 A operand ----
-#pragma unroll 1
-            for (int cc = 0; cc < 4; ++cc) {
-                float z[16], g0[16], g1[16];
-                tmem_ld16(d1 + cc * 16, z);
-                tmem_ld16(acc_base + cc * 16, g0);
-                tmem_ld16(acc_base + 64 + cc * 16, g1);
-                const uint32_t kb = uint32_t(keep >> (cc * 16)) & 0xffffu;
-                const uint32_t gb = uint32_t(gate >> (cc * 16)) & 0xffffu;
-                tmem_ld_wait();
+            // ---- critical section (serialised between the two groups by a2_free): operand stores only ----
 #pragma unroll
-                for (int g8 = 0; g8 < 2; ++g8) {
-                    float hi[8], lo[8];
-                    const float4 u0 = ld4(&s.w2[cc * 16 + g8 * 8]), u1 = ld4(&s.w2[cc * 16 + g8 * 8 + 4]);
-                    const float4 t0 = ld4(&s.w2[64 + cc * 16 + g8 * 8]), t1 = ld4(&s.w2[64 + cc * 16 + g8 * 8 + 4]);
-                    const float w0[8] = {u0.x, u0.y, u0.z, u0.w, u1.x, u1.y, u1.z, u1.w};
-                    const float w1[8] = {t0.x, t0.y, t0.z, t0.w, t1.x, t1.y, t1.z, t1.w};
+            for (int g8 = 0; g8 < 8; ++g8) {
+                float hi[8], lo[8];
 #pragma unroll
-                    for (int e = 0; e < 8; ++e) {
-                        const int q = g8 * 8 + e;
-                        const float h = (z[q] <= 0.0f) ? 0.0f : z[q];
-                        const float av = h * (((kb >> q) & 1u) ? ds : 0.0f);
-                        g0[q] = fmaf(dl0, av, g0[q]);
-                        g1[q] = fmaf(dl1, av, g1[q]);
-                        const float t = fmaf(dl1, w1[e], dl0 * w0[e]);
-                        const float dh = ((gb >> q) & 1u) ? t * ds : 0.0f;
-                        split_tf32(dh, hi[e], lo[e]);
-                    }
-                    const uint32_t off = mn32_offset(cc * 16 + g8 * 8, r, 512, 1024);
-                    st4(s.a_hi, off, hi[0], hi[1], hi[2], hi[3]);
-                    st4(s.a_hi, off + 16, hi[4], hi[5], hi[6], hi[7]);
-                    st4(s.a_lo, off, lo[0], lo[1], lo[2], lo[3]);
-                    st4(s.a_lo, off + 16, lo[4], lo[5], lo[6], lo[7]);
-                }
-                tmem_st16(acc_base + cc * 16, g0);
-                tmem_st16(acc_base + 64 + cc * 16, g1);
+                for (int e = 0; e < 8; ++e) split_tf32(dhv[g8 * 8 + e], hi[e], lo[e]);
+                const uint32_t off = mn32_offset(g8 * 8, r, 512, 1024);
+                st4(s.a_hi, off, hi[0], hi[1], hi[2], hi[3]);
+                st4(s.a_hi, off + 16, hi[4], hi[5], hi[6], hi[7]);
+                st4(s.a_lo, off, lo[0], lo[1], lo[2], lo[3]);
+                st4(s.a_lo, off + 16, lo[4], lo[5], lo[6], lo[7]);
             }
             tmem_st_wait();
             fence_proxy_async();
@@ -460,7 +516,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_step_kernel(const GridArgs a
                     for (int q = 0; q < 16; ++q) {
                         const int n = c0 + q;
                         if (n < F) s.slab[m * F + n] = v[q];             // dW1[m][n]
-                        else if (n == F) s.slab[OFF_B1 + m] = v[q];      // db1[m]
+                        else if (n == COL_ONE) s.slab[OFF_B1 + m] = v[q];  // db1[m]
                     }
                 }
             }
@@ -520,19 +576,40 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_step_kernel(const GridArgs a
     __threadfence();
     if (a.tail == wxk::TAIL_ADAM && tid == 0) s.adam = wxk::adam_scalars(a.desc, a.state[0] + 1);
     __syncthreads();
+    // Deterministic two-level sum of the CTA slabs: work item (float4 group g, segment q of the CTA range) -> partial in
+    // shared memory (the operand tiles are dead now), then the SEG partials of a group are added in segment order.
     const unsigned nparts = gridDim.x;
-    for (int i = tid; i < P + 1; i += TC_THREADS) {
-        const float* q = a.part + i;
-        unsigned b = 0;
-        float sum = 0.0f;
-        for (; b + 8 <= nparts; b += 8) {
-            float t[8];
+    constexpr int SEG = 4;
+    const int ng = slab_stride / 4;
+    float4* psum = reinterpret_cast<float4*>(s.xk_hi);            // [SEG][ng] float4 <= 4 * 561 * 16 B = 36 KB (xk_hi + xk_lo)
+    const unsigned per = (nparts + SEG - 1) / SEG;
+    for (int item = tid; item < ng * SEG; item += TC_THREADS) {
+        const int g = item % ng, q = item / ng;
+        const unsigned b0 = q * per, b1 = (b0 + per < nparts) ? b0 + per : nparts;
+        const float4* src = reinterpret_cast<const float4*>(a.part) + g;
+        float4 acc = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+        unsigned b = b0;
+        for (; b + 8 <= b1; b += 8) {
+            float4 t[8];
 #pragma unroll
-            for (int u = 0; u < 8; ++u) t[u] = __ldcg(q + size_t(b + u) * slab_stride);
+            for (int u = 0; u < 8; ++u) t[u] = __ldcg(src + size_t(b + u) * ng);
 #pragma unroll
-            for (int u = 0; u < 8; ++u) sum += t[u];
+            for (int u = 0; u < 8; ++u) {
+                acc.x += t[u].x; acc.y += t[u].y; acc.z += t[u].z; acc.w += t[u].w;
+            }
         }
-        for (; b < nparts; ++b) sum += __ldcg(q + size_t(b) * slab_stride);
+        for (; b < b1; ++b) {
+            const float4 t = __ldcg(src + size_t(b) * ng);
+            acc.x += t.x; acc.y += t.y; acc.z += t.z; acc.w += t.w;
+        }
+        psum[q * ng + g] = acc;
+    }
+    __syncthreads();
+    for (int i = tid; i < P + 1; i += TC_THREADS) {
+        const float* ps = reinterpret_cast<const float*>(psum);
+        float sum = 0.0f;
+#pragma unroll
+        for (int q = 0; q < SEG; ++q) sum += ps[(q * ng) * 4 + i];
         if (i == P) sum *= a.scale;
         if (a.tail == wxk::TAIL_GRADS) {
             a.out[i] = sum;

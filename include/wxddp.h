@@ -92,6 +92,10 @@ int wx_debug_cta_times(wx_ctx* ctx, long long* device_buf);
 int wx_tc_selftest(wx_ctx* ctx, const float* x, const float* w, const float* dh, int terms, float* z, float* g,
                    int* status, void* stream);
 
+/* Developer aid: cycles for `reps` x 4 tcgen05.mma (kind::tf32) of one operand layout (variant 0..3, see
+ * csrc/tc_selftest.cu); out = device int64[2] = { issue cycles, issue + completion cycles } of CTA 0. */
+int wx_tc_mma_bench(wx_ctx* ctx, int variant, int n_dim, int reps, long long* out, void* stream);
+
 /* ---- K1: preprocessing (jobs/preprocess.py) ------------------------------------------------ */
 
 /* Label encode: labels_out[i] = 1 iff string i is valid and equals "rain" exactly, else 0.

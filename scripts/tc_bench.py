@@ -25,11 +25,14 @@ if os.environ.get("CTA_TIMES"):
     print("ctas", len(d), "main us min/med/max %.1f %.1f %.1f" % (loop.min(), np.median(loop), loop.max()), "exit max %.1f" % ex.max(),
           "slowest", [(int(i), int(d[i, 0]), round(float(loop[i]), 1)) for i in np.argsort(loop)[-4:]])
 if os.environ.get("CTA_TIMES"):
-    dbg2 = torch.zeros(1184 * 4 + 148 * 2 * 8, dtype=torch.int64, device="cuda")
+    dbg2 = torch.zeros(1184 * 4 + 148 * 2 * 8 + 148 * 8, dtype=torch.int64, device="cuda")
     c.lib.wx_debug_cta_times(c._h, dbg2.data_ptr())
     fn(p, m, v, st, x, y, loss, row0=0, batch=B, dropout=mode, seed=3); torch.cuda.synchronize()
-    ph = dbg2[1184 * 4:].cpu().numpy().reshape(148, 2, 8)
+    ph = dbg2[1184 * 4:1184 * 4 + 148 * 16].cpu().numpy().reshape(148, 2, 8)
+    mm = dbg2[1184 * 4 + 148 * 16:].cpu().numpy().reshape(148, 8)
     names = ["wait_d1", "rng+y", "phaseA+softmax", "wait_a2free", "xm_row", "phaseB", "wait_xk+convert", "loop_gap"]
     tiles = (B // 128) / 148
     for g in range(2):
         print("group", g, {n: int(ph[:, g, k].mean() / (tiles / 2)) for k, n in enumerate(names)}, "cycles per tile (avg over CTAs)")
+    print("mma thread cycles/tile:", {n: int(mm[:, k].mean() / tiles) for k, n in enumerate(["wait_xk", "issue_g1", "wait_a2ready", "issue_g2"])},
+          "sampled completion latency: g1", int(mm[:, 4].mean() / (tiles / 8)), "g2", int(mm[:, 5].mean() / (tiles / 8)))
