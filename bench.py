@@ -222,6 +222,9 @@ def main() -> int:
     step_raw = ctx.tc_train_step_raw if use_tc else ctx.train_step_raw
     kernel_name = ("tc_step_kernel (tcgen05 tf32x3, wx_tc_train_step_raw)" if use_tc
                    else "mlp_grid_kernel<F,TRAIN,RAW_F32> (FFMA, wx_train_step_raw)")
+    grad_fn = ctx.mlp_grad
+    if world > 1 and args.kernel != "ffma" and ctx.tc_ok_rowmajor(feats, y, 0) and (B * f) % 4 == 0:
+        grad_fn = ctx.tc_mlp_grad
 
     def one_step():
         s = step_no[0]
@@ -232,8 +235,8 @@ def main() -> int:
         else:
             # DDP: local sums pre-scaled by 1/(W*B), SUM across ranks (what torch's reducer does, :136),
             # loss scalar rides in the same bucket (element P), then Adam
-            ctx.mlp_grad(params, feats, y, row0=row0, batch=B, dropout=wxddp.DROPOUT_PHILOX, seed=42 + 1000 * rank,
-                         step=s, scale=1.0 / (world * B), out=grads)
+            grad_fn(params, feats, y, row0=row0, batch=B, dropout=wxddp.DROPOUT_PHILOX, seed=42 + 1000 * rank,
+                    step=s, scale=1.0 / (world * B), out=grads)
             dist.all_reduce(grads)
             ctx.adam_step(params, grads, m, v, s + 1, n=P)
         step_no[0] = s + 1
@@ -305,9 +308,13 @@ def main() -> int:
     kernel_s = (ms / 1e3) / args.steps                          # one step-kernel launch per step on 1 GPU
     achieved = B * bytes_per_row / kernel_s / 1e9
     flops_per_row = 2 * (2 * f * 64 + 3 * 64 * 2)
+    # dram__bytes_read.sum + dram__bytes_write.sum per launch from the ncu --set full capture of this exact workload
+    # (profiles/README.md: 92.46 MB + 2.5 MB); any other workload has no capture -> null
+    traffic = 94.96e6 if (world == 1 and use_tc and f == 20 and B == (1 << 20)) else None
     roof = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-            "traffic": None, "kernel": kernel_name if world == 1
-            else "mlp_grid_kernel<F,TRAIN,ROWMAJOR> (wx_mlp_grad) + NCCL all-reduce + adam_kernel",
+            "traffic": traffic, "kernel": kernel_name if world == 1
+            else ("tc_step_kernel (wx_tc_mlp_grad)" if grad_fn == ctx.tc_mlp_grad else "mlp_grid_kernel<F,TRAIN,ROWMAJOR> (wx_mlp_grad)")
+            + " + NCCL all-reduce + adam_kernel",
             "peak_source": peak_src, "algorithmic_bytes_per_row": bytes_per_row,
             "fp32_pipe": {"achieved_tflops": B * flops_per_row / kernel_s / 1e12, "peak_tflops": 74.4,
                           "frac": B * flops_per_row / kernel_s / 1e12 / 74.4,

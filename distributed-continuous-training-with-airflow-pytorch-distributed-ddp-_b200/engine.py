@@ -89,9 +89,15 @@ class StepEngine:
             self.steps_done += 1
             return self.loss
         b = batch if batch is not None else (row_idx.numel() if row_idx is not None else x.shape[0] - row0)
-        self.ctx.mlp_grad(self.params, x, y, row_idx=row_idx, row0=row0, batch=b, dropout=dropout, keep_mask=keep_mask,
-                          seed=self._dropout_seed(), step=self.steps_done, scale=1.0 / (self.world * b),
-                          out=self.bucket)
+        mask_ok = keep_mask is None or keep_mask.data_ptr() % 16 == 0
+        if self.use_tc and b >= 128 and mask_ok and self.ctx.tc_ok_rowmajor(x, y, row0, row_idx):
+            self.ctx.tc_mlp_grad(self.params, x, y, row0=row0, batch=b, dropout=dropout, keep_mask=keep_mask,
+                                 seed=self._dropout_seed(), step=self.steps_done, scale=1.0 / (self.world * b),
+                                 out=self.bucket)
+        else:
+            self.ctx.mlp_grad(self.params, x, y, row_idx=row_idx, row0=row0, batch=b, dropout=dropout,
+                              keep_mask=keep_mask, seed=self._dropout_seed(), step=self.steps_done,
+                              scale=1.0 / (self.world * b), out=self.bucket)
         self.dist.all_reduce(self.bucket)                                    # C2 + C3 in one bucket
         self.steps_done += 1
         self.ctx.adam_step(self.params, self.bucket, self.m, self.v, self.steps_done, n=self.P)
