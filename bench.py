@@ -226,12 +226,22 @@ def main() -> int:
     if world > 1 and args.kernel != "ffma" and ctx.tc_ok_rowmajor(feats, y, 0) and (B * f) % 4 == 0:
         grad_fn = ctx.tc_mlp_grad
 
+    fused_ddp = False
+    if world > 1 and use_tc:
+        # DDP exchange inside the step kernel: every rank maps every rank's inbox (CUDA IPC) once
+        handles = [None] * world
+        dist.all_gather_object(handles, ctx.peer_export())
+        ctx.peer_connect(rank, world, handles)
+        dist.barrier()
+        fused_ddp = True
+        kernel_name = "tc_step_kernel (tcgen05 tf32x3) with in-kernel [P+1] all-reduce over NVLink peer memory"
+
     def one_step():
         s = step_no[0]
         row0 = (s % n_windows) * B
-        if world == 1:
+        if world == 1 or fused_ddp:
             step_raw(params, m, v, state, cols, stats, y, loss, row0=row0, batch=B,
-                     impute=wxddp.IMPUTE_MEAN, dropout=wxddp.DROPOUT_PHILOX, seed=42)
+                     impute=wxddp.IMPUTE_MEAN, dropout=wxddp.DROPOUT_PHILOX, seed=42 + 1000 * rank)
         else:
             # DDP: local sums pre-scaled by 1/(W*B), SUM across ranks (what torch's reducer does, :136),
             # loss scalar rides in the same bucket (element P), then Adam
@@ -267,7 +277,7 @@ def main() -> int:
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms = float(t.item())
-    final_loss = float(loss.item()) if world == 1 else float(grads[P].item())
+    final_loss = float(loss.item()) if (world == 1 or fused_ddp) else float(grads[P].item())
 
     # ---- e2e: public API with HOST buffers; H2D of the step's raw rows + labels and D2H of the loss inside ----
     e2e = None
@@ -275,6 +285,8 @@ def main() -> int:
         from wxddp.engine import StepEngine
         eng = StepEngine(f, device=device, world=world, rank=rank, process_group=dist if world > 1 else None)
         eng.set_stats(stats)
+        if world > 1:
+            eng.connect_peers()
         n_host = 4
         host_cols = [torch.empty(f, B, dtype=torch.float32).pin_memory() for _ in range(n_host)]
         host_y = [torch.empty(B, dtype=torch.int64).pin_memory() for _ in range(n_host)]
@@ -305,14 +317,14 @@ def main() -> int:
     value = args.steps * B * world / (ms / 1e3)
     peak, peak_src = read_peaks()
     bytes_per_row = 4 * f + 8                                   # fp32 features + int64 label
-    kernel_s = (ms / 1e3) / args.steps                          # one step-kernel launch per step on 1 GPU
+    kernel_s = (ms / 1e3) / args.steps                          # one step-kernel launch per step and GPU
     achieved = B * bytes_per_row / kernel_s / 1e9
     flops_per_row = 2 * (2 * f * 64 + 3 * 64 * 2)
     # dram__bytes_read.sum + dram__bytes_write.sum per launch from the ncu --set full capture of this exact workload
     # (profiles/README.md: 92.46 MB + 2.5 MB); any other workload has no capture -> null
     traffic = 94.96e6 if (world == 1 and use_tc and f == 20 and B == (1 << 20)) else None
     roof = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-            "traffic": traffic, "kernel": kernel_name if world == 1
+            "traffic": traffic, "kernel": kernel_name if (world == 1 or fused_ddp)
             else ("tc_step_kernel (wx_tc_mlp_grad)" if grad_fn == ctx.tc_mlp_grad else "mlp_grid_kernel<F,TRAIN,ROWMAJOR> (wx_mlp_grad)")
             + " + NCCL all-reduce + adam_kernel",
             "peak_source": peak_src, "algorithmic_bytes_per_row": bytes_per_row,

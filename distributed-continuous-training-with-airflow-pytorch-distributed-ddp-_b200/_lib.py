@@ -38,6 +38,8 @@ SIGNATURES = {
     "wx_n_params": (_i64, [_vp]),
     "wx_num_sms": (_int, [_vp]),
     "wx_launch_count": (_i64, [_vp]),
+    "wx_peer_export": (_int, [_vp, _vp]),
+    "wx_peer_connect": (_int, [_vp, _int, _int, _vp]),
     "wx_debug_cta_times": (_int, [_vp, _vp]),
     "wx_tc_selftest": (_int, [_vp, _vp, _vp, _vp, _int, _vp, _vp, _vp, _vp]),
     "wx_tc_mma_bench": (_int, [_vp, _int, _int, _int, _vp, _vp]),

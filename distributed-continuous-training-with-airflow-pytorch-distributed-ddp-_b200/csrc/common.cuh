@@ -6,6 +6,7 @@
 #include <stdio.h>
 
 #include "wxddp.h"
+#include "peer.cuh"
 
 #define WX_WARP 32
 
@@ -27,6 +28,9 @@ struct wx_ctx {
     size_t scratch_bytes;
     int64_t launches;
     long long* debug_times;   // optional device buffer [grid][4]: smid, t_start, t_loop_end, t_exit (globaltimer ns)
+    unsigned char* inbox;     // this rank's peer inbox (wx_peer_export), NULL until exported
+    wxpeer::PeerArgs peer;    // world <= 1 until wx_peer_connect
+    void* peer_mapped[wxpeer::MAXW];   // cudaIpcOpenMemHandle results to close at destroy
 };
 
 void wx_set_error(const char* fmt, ...);

@@ -46,6 +46,9 @@ int wx_create(int device, const wx_model_desc* desc, wx_ctx** out) {
     c->scratch_bytes = WX_SCRATCH_BYTES;
     c->launches = 0;
     c->debug_times = nullptr;
+    c->inbox = nullptr;
+    memset(&c->peer, 0, sizeof(c->peer));
+    memset(c->peer_mapped, 0, sizeof(c->peer_mapped));
     cudaError_t e = cudaMalloc(&c->scratch, c->scratch_bytes);
     if (e != cudaSuccess) {
         wx_set_error("wx_create: cudaMalloc(%zu) failed: %s", c->scratch_bytes, cudaGetErrorString(e));
@@ -66,6 +69,9 @@ int wx_create(int device, const wx_model_desc* desc, wx_ctx** out) {
 int wx_destroy(wx_ctx* ctx) {
     if (!ctx) return WX_OK;
     cudaSetDevice(ctx->device);
+    for (int q = 0; q < wxpeer::MAXW; ++q)
+        if (ctx->peer_mapped[q]) cudaIpcCloseMemHandle(ctx->peer_mapped[q]);
+    if (ctx->inbox) cudaFree(ctx->inbox);
     cudaFree(ctx->scratch);
     delete ctx;
     return WX_OK;
@@ -74,6 +80,47 @@ int wx_destroy(wx_ctx* ctx) {
 int64_t wx_n_params(const wx_ctx* ctx) { return ctx ? ctx->n_params : -1; }
 int wx_num_sms(const wx_ctx* ctx) { return ctx ? ctx->num_sms : -1; }
 int64_t wx_launch_count(const wx_ctx* ctx) { return ctx ? ctx->launches : -1; }
+
+int wx_peer_export(wx_ctx* ctx, void* handle_out) {
+    WX_CHECK_ARG(ctx != nullptr && handle_out != nullptr, "wx_peer_export: NULL argument");
+    WX_CUDA(cudaSetDevice(ctx->device));
+    if (ctx->inbox == nullptr) {
+        WX_CUDA(cudaMalloc(&ctx->inbox, wxpeer::INBOX_BYTES));
+        WX_CUDA(cudaMemset(ctx->inbox, 0, wxpeer::INBOX_BYTES));
+        WX_CUDA(cudaDeviceSynchronize());
+    }
+    cudaIpcMemHandle_t h;
+    WX_CUDA(cudaIpcGetMemHandle(&h, ctx->inbox));
+    static_assert(sizeof(h) == 64, "CUDA IPC handle is 64 bytes");
+    memcpy(handle_out, &h, sizeof(h));
+    return WX_OK;
+}
+
+int wx_peer_connect(wx_ctx* ctx, int rank, int world, const void* handles) {
+    WX_CHECK_ARG(ctx != nullptr && handles != nullptr, "wx_peer_connect: NULL argument");
+    WX_CHECK_ARG(world >= 1 && world <= wxpeer::MAXW && rank >= 0 && rank < world, "wx_peer_connect: rank=%d world=%d (max %d)",
+                 rank, world, wxpeer::MAXW);
+    WX_CHECK_ARG(ctx->inbox != nullptr, "wx_peer_connect: call wx_peer_export first");
+    WX_CUDA(cudaSetDevice(ctx->device));
+    wxpeer::PeerArgs pa;
+    memset(&pa, 0, sizeof(pa));
+    pa.world = world;
+    pa.rank = rank;
+    for (int q = 0; q < world; ++q) {
+        if (q == rank) {
+            pa.inbox[q] = ctx->inbox;
+            continue;
+        }
+        cudaIpcMemHandle_t h;
+        memcpy(&h, static_cast<const unsigned char*>(handles) + size_t(q) * 64, 64);
+        void* p = nullptr;
+        WX_CUDA(cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
+        ctx->peer_mapped[q] = p;
+        pa.inbox[q] = static_cast<unsigned char*>(p);
+    }
+    ctx->peer = pa;
+    return WX_OK;
+}
 
 int wx_debug_cta_times(wx_ctx* ctx, long long* device_buf) {
     if (!ctx) return WX_EINVAL;

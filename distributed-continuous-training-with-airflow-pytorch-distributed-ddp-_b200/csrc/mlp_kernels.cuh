@@ -49,6 +49,7 @@ struct GridArgs {
     double* eval_out;       // MODE_EVAL: [2]
     long long* dbg;         // optional per-CTA timestamps (wx_debug_cta_times)
     float* probs_out;       // MODE_PREDICT
+    wxpeer::PeerArgs peer;  // world > 1: cross-rank sum inside the tail (TAIL_ADAM only)
 };
 
 // smem bytes per warp for the staging buffers of a loader

@@ -611,6 +611,16 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_step_kernel(const GridArgs a
 #pragma unroll
         for (int q = 0; q < SEG; ++q) sum += ps[(q * ng) * 4 + i];
         if (i == P) sum *= a.scale;
+        s.slab[i] = sum;                                    // this rank's [P+1] bucket
+    }
+    __syncthreads();
+    if (a.peer.world > 1 && a.tail == wxk::TAIL_ADAM) {
+        // DDP exchange inside the kernel: one-shot all-reduce over NVLink peer memory (csrc/peer.cuh)
+        if (!wxpeer::allreduce_cta(s.slab, P + 1, a.peer, uint64_t(a.state[0]) + 1, tid, TC_THREADS) && tid == 0)
+            atomicExch(err_out, 20);
+    }
+    for (int i = tid; i < P + 1; i += TC_THREADS) {
+        const float sum = s.slab[i];
         if (a.tail == wxk::TAIL_GRADS) {
             a.out[i] = sum;
         } else if (i < P) {
@@ -668,6 +678,10 @@ int tc_launch(wx_ctx* ctx, GridArgs& a, cudaStream_t st, const char* who) {
     a.ticket = reinterpret_cast<unsigned int*>(ctx->scratch) + 1;
     a.desc = ctx->desc;
     a.dbg = ctx->debug_times;
+    if (a.tail == wxk::TAIL_ADAM && ctx->peer.world > 1) {
+        a.peer = ctx->peer;
+        a.scale = a.scale / float(ctx->peer.world);          // mean over W*B rows (what DDP's averaged gradients give)
+    }
     int* err = reinterpret_cast<int*>(ctx->scratch) + 8;       // word 8 of the ticket block: sticky protocol-error code
     tc_step_kernel<<<(unsigned)grid, TC_THREADS, smem, st>>>(a, f, err);
     WX_LAUNCH_CHECK(ctx);

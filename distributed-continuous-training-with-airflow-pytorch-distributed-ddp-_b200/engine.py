@@ -50,8 +50,21 @@ class StepEngine:
         self.stats = None
         self._stage = None
         self._loss_host = torch.zeros(1).pin_memory() if torch.cuda.is_available() else torch.zeros(1)
+        self.peers = False
         if world > 1:
             self.dist.broadcast(self.params, src=0)                          # C1: DDP's initial parameter broadcast
+
+    def connect_peers(self) -> None:
+        """Exchange CUDA IPC handles of the per-rank inboxes so the fused tensor-core steps can all-reduce the [P+1]
+        bucket inside the kernel (NVLink peer stores) instead of mlp_grad -> NCCL -> adam (one launch per step)."""
+        if self.world == 1:
+            return
+        mine = self.ctx.peer_export()
+        handles = [None] * self.world
+        self.dist.all_gather_object(handles, mine)
+        self.ctx.peer_connect(self.rank, self.world, handles)
+        self.dist.barrier()
+        self.peers = True
 
     # ---- statistics ------------------------------------------------------------------------------
     def set_stats(self, stats: torch.Tensor) -> None:
@@ -90,6 +103,12 @@ class StepEngine:
             return self.loss
         b = batch if batch is not None else (row_idx.numel() if row_idx is not None else x.shape[0] - row0)
         mask_ok = keep_mask is None or keep_mask.data_ptr() % 16 == 0
+        if self.peers and self.use_tc and mask_ok and self.ctx.tc_ok_rowmajor(x, y, row0, row_idx):
+            # fused: forward + backward + cross-rank sum over NVLink peer memory + Adam in ONE launch
+            self.ctx.tc_train_step(self.params, self.m, self.v, self.state, x, y, self.loss, row0=row0, batch=b,
+                                   dropout=dropout, keep_mask=keep_mask, seed=self._dropout_seed())
+            self.steps_done += 1
+            return self.loss
         if self.use_tc and b >= 128 and mask_ok and self.ctx.tc_ok_rowmajor(x, y, row0, row_idx):
             self.ctx.tc_mlp_grad(self.params, x, y, row0=row0, batch=b, dropout=dropout, keep_mask=keep_mask,
                                  seed=self._dropout_seed(), step=self.steps_done, scale=1.0 / (self.world * b),
@@ -119,6 +138,13 @@ class StepEngine:
             return self.loss
         n = cols[0].numel()
         b = batch if batch is not None else n - row0
+        mask_ok = keep_mask is None or keep_mask.data_ptr() % 16 == 0
+        if self.peers and self.use_tc and mask_ok and self.ctx.tc_ok_raw(cols, y, row0):
+            self.ctx.tc_train_step_raw(self.params, self.m, self.v, self.state, cols, self.stats, y, self.loss, row0=row0,
+                                       batch=b, impute=impute, dropout=dropout, keep_mask=keep_mask,
+                                       seed=self._dropout_seed())
+            self.steps_done += 1
+            return self.loss
         feats, _ = self.ctx.normalize_pack([c[row0:row0 + b] for c in cols], self.stats, impute=impute,
                                            want_nullmask=False)
         return self.step(feats, y[row0:row0 + b].contiguous(), dropout=dropout, keep_mask=keep_mask)

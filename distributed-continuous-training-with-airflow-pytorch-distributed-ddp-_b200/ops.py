@@ -40,6 +40,7 @@ class Context:
         h = C.c_void_p()
         check(self.lib.wx_create(dev.index or 0, C.byref(desc), C.byref(h)))
         self._h = h
+        self.peer_world = 1
 
     # -- bookkeeping ---------------------------------------------------------------------------
     def close(self) -> None:
@@ -221,6 +222,22 @@ class Context:
             self._chk(keep_mask, torch.int64, "keep_mask", batch)
         check(self.lib.wx_tc_train_step_raw(self._h, _p(params), _p(m), _p(v), _p(state), cp, _p(stats), impute, _p(y),
                                             row0, batch, dropout, _p(keep_mask), seed, _p(loss_out), self._stream()))
+
+    # -- multi-GPU: in-kernel gradient exchange over NVLink peer memory ---------------------------------
+    def peer_export(self) -> bytes:
+        """This rank's inbox as a 64-byte CUDA IPC handle (allocates the inbox on first use)."""
+        h = (C.c_ubyte * 64)()
+        check(self.lib.wx_peer_export(self._h, h))
+        return bytes(h)
+
+    def peer_connect(self, rank: int, world: int, handles: list[bytes]) -> None:
+        """Map every rank's inbox; afterwards tc_train_step / tc_train_step_raw all-reduce inside the kernel."""
+        blob = b"".join(handles)
+        if len(blob) != 64 * world:
+            raise WxError("peer_connect needs one 64-byte handle per rank")
+        buf = (C.c_ubyte * len(blob)).from_buffer_copy(blob)
+        check(self.lib.wx_peer_connect(self._h, rank, world, buf))
+        self.peer_world = world
 
     # -- kernel choice --------------------------------------------------------------------------------
     TC_MAX_FEATURES = 29

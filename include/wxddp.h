@@ -81,6 +81,16 @@ int wx_num_sms(const wx_ctx* ctx);
 /* Number of kernels this context has launched since creation (bench.py's gpu_launches claim). */
 int64_t wx_launch_count(const wx_ctx* ctx);
 
+/* ---- multi-GPU: gradient exchange inside the step kernel ------------------------------------------------ */
+/* Replaces DDP's bucket all-reduce and the sync_dist loss reduce (train_lightning_ddp.py:70,:136) for the fused
+ * tensor-core steps: after wx_peer_connect, wx_tc_train_step / wx_tc_train_step_raw sum the [P+1] bucket over all
+ * ranks INSIDE the kernel's tail (stores into every rank's inbox over NVLink peer memory, flag per rank, ordered sum)
+ * and scale by 1/(world*batch).  One process per GPU on one node; every rank must launch the same step.
+ *   wx_peer_export : allocates this rank's inbox (cudaMalloc, once) and writes its 64-byte CUDA IPC handle to handle_out (host).
+ *   wx_peer_connect: handles = host [world][64] bytes gathered from all ranks (any transport, e.g. torch.distributed). */
+int wx_peer_export(wx_ctx* ctx, void* handle_out);
+int wx_peer_connect(wx_ctx* ctx, int rank, int world, const void* handles);
+
 /* Developer aid, not part of the reference-facing surface: when device_buf (int64 [grid][4]) is non-NULL the step
  * kernels record per CTA { smid, t_start, t_main_loop_end, t_exit } in globaltimer ns.  NULL switches it off. */
 int wx_debug_cta_times(wx_ctx* ctx, long long* device_buf);

@@ -72,3 +72,59 @@ def test_ddp_on_gpus_matches_gloo_ddp_oracle(world):
         np.testing.assert_allclose(g[3], r[3], rtol=1e-6)
         np.testing.assert_allclose(g[4], r[4], rtol=2e-3, atol=2e-5)
     np.testing.assert_array_equal(got[0][4], got[1][4])                   # replicas stay bit-identical
+
+
+def _peer_worker(rank, world, port, q):
+    """Fused in-kernel exchange (NVLink peer memory) vs the NCCL bucket path, same data, same dropout bits."""
+    import torch.distributed as dist
+
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    torch.cuda.set_device(rank)
+    dev = torch.device("cuda", rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+    import wxddp
+    from wxddp.engine import StepEngine
+
+    f, b, steps = 20, 4096 + 128 * rank, 6        # per-rank batches of different size are fine for the exchange itself
+    b = 4096
+    g = torch.Generator().manual_seed(100 + rank)
+    x = torch.randn(steps * b, f, generator=g).to(dev); y = (torch.rand(steps * b, generator=g) < 0.3).long().to(dev)
+    torch.manual_seed(5)
+    res = {}
+    for name, use_peers in (("nccl", False), ("peer", True)):
+        torch.manual_seed(5)
+        eng = StepEngine(f, device=dev, world=world, rank=rank, process_group=dist)
+        if use_peers:
+            eng.connect_peers()
+        losses = []
+        for s in range(steps):
+            l = eng.step(x, y, row0=s * b, batch=b, dropout=wxddp.DROPOUT_PHILOX)
+            losses.append(float(l.item()))
+        torch.cuda.synchronize()
+        res[name] = (losses, eng.params.cpu().numpy(), eng.ctx.tc_status(), int(eng.state[0].item()) if use_peers else steps)
+        dist.barrier()
+    q.put((rank, res))
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world", [2])
+def test_in_kernel_peer_allreduce_matches_nccl_bucket_path(world):
+    _need(world)
+    import torch.multiprocessing as mp
+
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_peer_worker, args=(r, world, 29691, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    out = sorted([q.get(timeout=600) for _ in range(world)], key=lambda t: t[0])
+    for p in procs:
+        p.join(timeout=120)
+        assert p.exitcode == 0
+    for rank, res in out:
+        assert res["peer"][2] == 0 and res["peer"][3] == 6
+        np.testing.assert_allclose(res["peer"][0], res["nccl"][0], rtol=1e-5)              # rank-mean train_loss per step
+        np.testing.assert_allclose(res["peer"][1], res["nccl"][1], rtol=1e-4, atol=1e-6)   # parameters after 6 Adam steps
+    np.testing.assert_array_equal(out[0][1]["peer"][1], out[1][1]["peer"][1])              # replicas bit-identical
+    np.testing.assert_allclose(out[0][1]["peer"][0], out[1][1]["peer"][0], rtol=0, atol=0)
