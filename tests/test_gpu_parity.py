@@ -179,6 +179,75 @@ def test_normalize_pack_bit_exact_given_stats(wx, f, n, dtype, impute):
         assert cnt2 == cnt and idx2.cpu().numpy().tolist() == ref_idx[:3].tolist()
 
 
+@pytest.mark.parametrize("dtype", [torch.float32, torch.float64])
+def test_normalize_pack_exact_rounding_at_scale(wx, dtype):
+    """The kernel multiplies by 1/std and only divides when the fp32 rounding could differ: over 25M cells (a few of
+    which sit next to a rounding midpoint) the result must still be float32((x - mean) / std) evaluated in IEEE float64."""
+    f, n = 8, 3_145_728 + 17
+    gen = torch.Generator(device="cuda").manual_seed(5)
+    raw = (torch.randn(f, n, device="cuda", generator=gen, dtype=torch.float64) * 7.3 + 19.1).to(dtype)
+    raw[:, ::1013] = float("nan")
+    raw[3, 5:2000:7] = raw[3, 4]                      # repeated values
+    c = ctx_for(wx, f)
+    cols = [raw[j] for j in range(f)]
+    stats = c.col_stats(cols)
+    stats[3, 1] = raw[3, 4].double()                  # mean equal to a value that occurs: exact zeros in the output
+    feats, nm = c.normalize_pack(cols, stats, impute=0)
+    want = ((raw.double() - stats[:, 1:2]) / stats[:, 3:4]).float().t().contiguous()
+    assert torch.equal(torch.isnan(feats), torch.isnan(want))
+    assert torch.equal(torch.nan_to_num(feats).view(torch.int32), torch.nan_to_num(want).view(torch.int32))
+    assert (feats[5:2000:7, 3] == 0).all()
+    # same table through columns that are only element-aligned (direct-load kernels instead of the TMA ring / 16-byte loads)
+    pad = torch.empty(f, n + 1, device="cuda", dtype=dtype)
+    pad[:, 1:] = raw
+    cols_u = [pad[j, 1:] for j in range(f)]
+    assert cols_u[0].data_ptr() % 16 != 0
+    feats_u, nm_u = c.normalize_pack(cols_u, stats, impute=0)
+    assert torch.equal(torch.nan_to_num(feats_u).view(torch.int32), torch.nan_to_num(feats).view(torch.int32))
+    assert torch.equal(nm_u, nm)
+    st_u = c.col_stats(cols_u).cpu().numpy()
+    st_a = c.col_stats(cols).cpu().numpy()
+    np.testing.assert_array_equal(st_u[:, 0], st_a[:, 0])
+    np.testing.assert_allclose(st_u[:, 1], st_a[:, 1], rtol=1e-13)
+    np.testing.assert_allclose(st_u[:, 3], st_a[:, 3], rtol=1e-12)
+
+
+def test_normalize_pack_extreme_statistics(wx):
+    """std / mean far outside the comfortable range: subnormal fp32 results, overflow to inf, a std whose reciprocal is
+    not representable -- all must equal the float64 divide."""
+    f, n = 4, 1024
+    rng = np.random.default_rng(11)
+    raw = np.stack([rng.normal(0, 1, n), rng.normal(0, 1e-30, n), rng.normal(0, 1e30, n), rng.normal(5, 1e-3, n)])
+    st = np.zeros((f, 4))
+    st[:, 0] = n
+    st[:, 1] = [0.0, 0.0, 0.0, 5.0]
+    st[:, 3] = [1e39, 1e-300, 1e-12, 3e300]          # tiny quotients, huge ones (inf in fp32), overflowing, underflowing
+    c = ctx_for(wx, f)
+    for dtype in (np.float64, np.float32):
+        r = raw.astype(dtype)
+        feats, _ = c.normalize_pack([dev(r[j]) for j in range(f)], dev(st), impute=0)
+        with np.errstate(over="ignore", under="ignore"):
+            want = ((r.astype(np.float64) - st[:, 1:2]) / st[:, 3:4]).astype(np.float32).T
+        np.testing.assert_array_equal(feats.cpu().numpy().view(np.uint32), want.view(np.uint32))
+
+
+def test_col_stats_trend_and_outliers(wx):
+    """The pivoted-sum statistics keep full accuracy on a column with a trend, a far-off level and a single outlier."""
+    n = 1_000_003
+    rng = np.random.default_rng(3)
+    cols_np = np.stack([np.arange(n, dtype=np.float64) * 1e-3 + rng.normal(0, 1e-2, n),          # trend
+                        1e9 + rng.normal(0, 1.0, n),                                             # far-off level
+                        np.where(np.arange(n) == 17, 1e12, rng.normal(0, 1.0, n)),               # one outlier first tile
+                        np.concatenate([np.zeros(n // 2), 1e6 + rng.normal(0, 1, n - n // 2)])]) # level jump
+    c = ctx_for(wx, 4)
+    got = c.col_stats([dev(cols_np[j]) for j in range(4)]).cpu().numpy()
+    for j in range(4):
+        cnt, m, s = preprocess_ref.column_stats(cols_np[j])
+        assert got[j, 0] == cnt
+        np.testing.assert_allclose(got[j, 1], m, rtol=1e-13)
+        np.testing.assert_allclose(got[j, 3], s, rtol=1e-11)
+
+
 def test_normalize_with_gpu_stats_within_one_ulp(wx):
     f, n = 20, 145_460
     t = synth.synth_table(1234, n, f, null_rate=0.0, const_col=f - 1)
