@@ -294,11 +294,18 @@ def main() -> int:
             host_cols[i].copy_(raw[:, i * B:(i + 1) * B])
             host_y[i].copy_(y[i * B:(i + 1) * B])
         for i in range(3):
-            eng.step_host(host_cols[i % n_host], host_y[i % n_host])
+            eng.submit_host(host_cols[i % n_host], host_y[i % n_host])
+        eng.drain()
         barrier()
         t0 = time.perf_counter()
+        n_read = 0
         for i in range(args.steps):
-            last = eng.step_host(host_cols[i % n_host], host_y[i % n_host])
+            # H2D of batch i overlaps the kernel of batch i-1; every step's loss is read back (one call late)
+            r = eng.submit_host(host_cols[i % n_host], host_y[i % n_host])
+            n_read += r is not None
+        last = eng.drain()
+        n_read += 1
+        assert n_read == args.steps
         barrier()
         dt = time.perf_counter() - t0
         tt = torch.tensor([dt], dtype=torch.float64, device=device)
@@ -307,7 +314,7 @@ def main() -> int:
         dt = float(tt.item())
         e2e = {"value": args.steps * B * world / dt, "unit": UNIT, "h2d_bytes_per_step": B * (4 * f + 8),
                "d2h_bytes_per_step": 4, "ms_per_step": 1e3 * dt / args.steps, "last_loss": last,
-               "api": "wxddp.engine.StepEngine.step_host(pinned raw columns, labels) -> loss"}
+               "api": "wxddp.engine.StepEngine.submit_host(pinned raw columns, labels) -> loss of the previous step; drain() for the last (H2D of batch i overlaps the kernel of batch i-1)"}
 
     if rank != 0:
         if world > 1:

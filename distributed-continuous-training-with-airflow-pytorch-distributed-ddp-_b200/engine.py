@@ -164,6 +164,54 @@ class StepEngine:
         torch.cuda.current_stream(self.device).synchronize()
         return float(self._loss_host.item())
 
+    # ---- pipelined host path --------------------------------------------------------------------------
+    def submit_host(self, cols_host: torch.Tensor, y_host: torch.Tensor):
+        """Pipelined form of `step_host`: the H2D copy of THIS batch runs on a copy stream while the previous step's
+        kernel runs on the compute stream (two staging slots, event-ordered), and the loss comes back one call late --
+        the return value is the loss of the previously submitted step (None on the first call); `drain()` returns the
+        last one.  Same arithmetic and step order as `step_host`; host buffers should be pinned and must stay untouched
+        until the next call returns."""
+        f, b = cols_host.shape
+        if getattr(self, "_pipe", None) is None or self._pipe["b"] != b:
+            self._pipe = {
+                "b": b, "k": 0, "copy": torch.cuda.Stream(device=self.device),
+                "cols": [torch.empty(f, b, dtype=torch.float32, device=self.device) for _ in range(2)],
+                "y": [torch.empty(b, dtype=torch.int64, device=self.device) for _ in range(2)],
+                "ready": [torch.cuda.Event() for _ in range(2)], "free": [torch.cuda.Event() for _ in range(2)],
+                "done": [torch.cuda.Event() for _ in range(2)],
+                "loss": [torch.zeros(1).pin_memory() for _ in range(2)], "pending": None,
+            }
+        p = self._pipe
+        slot = p["k"] & 1
+        compute = torch.cuda.current_stream(self.device)
+        with torch.cuda.stream(p["copy"]):
+            if p["k"] >= 2:
+                p["copy"].wait_event(p["free"][slot])        # the step that last read this slot has finished
+            p["cols"][slot].copy_(cols_host, non_blocking=True)
+            p["y"][slot].copy_(y_host, non_blocking=True)
+            p["ready"][slot].record(p["copy"])
+        compute.wait_event(p["ready"][slot])
+        dc = p["cols"][slot]
+        loss = self.step_raw([dc[j] for j in range(f)], p["y"][slot], row0=0, batch=b)
+        p["free"][slot].record(compute)
+        p["loss"][slot].copy_(loss.reshape(1), non_blocking=True)
+        p["done"][slot].record(compute)
+        prev, p["pending"] = p["pending"], slot
+        p["k"] += 1
+        if prev is None:
+            return None
+        p["done"][prev].synchronize()
+        return float(p["loss"][prev].item())
+
+    def drain(self):
+        """Loss of the last `submit_host` call (waits for it); None if nothing is pending."""
+        p = getattr(self, "_pipe", None)
+        if p is None or p["pending"] is None:
+            return None
+        slot, p["pending"] = p["pending"], None
+        p["done"][slot].synchronize()
+        return float(p["loss"][slot].item())
+
     def evaluate(self, x, y, *, row_idx=None, row0: int = 0, batch: int | None = None):
         """validation pass (:73-85) over this rank's rows -> (val_loss, val_acc) as rank-weighted means (C4)."""
         out = self.ctx.mlp_eval(self.params, x, y, row_idx=row_idx, row0=row0, batch=batch)

@@ -166,3 +166,42 @@ def test_etl_front_end_matches_oracle_and_feeds_the_trainer():
         np.testing.assert_array_equal(ds.labels.numpy(), want["labels"])
     finally:
         shutil.rmtree(tmp)
+
+
+def test_host_buffer_steps_sync_and_pipelined_agree():
+    """StepEngine.step_host (synchronous) and submit_host/drain (H2D of batch i overlapped with the kernel of batch
+    i-1, loss one call late) run the same arithmetic in the same order as step_raw on device-resident columns."""
+    from wxddp.engine import StepEngine
+
+    f, b, n_steps = 20, 4096, 7
+    t = synth.synth_table(21, b * n_steps, f, null_rate=0.01)
+    raw = torch.from_numpy(t["raw"].astype(np.float32))
+    y = torch.from_numpy(preprocess_ref.label_encode(t["labels"]).astype(np.int64))
+    torch.manual_seed(42)
+    p0 = None
+    engines = []
+    for _ in range(3):
+        e = StepEngine(f, device=0, params=p0)
+        p0 = e.params.cpu() if p0 is None else p0
+        engines.append(e)
+    dev_cols = [raw[j].cuda() for j in range(f)]
+    stats = engines[0].fit_stats(dev_cols)
+    for e in engines[1:]:
+        e.set_stats(stats)
+    host = [(raw[:, i * b:(i + 1) * b].contiguous().pin_memory(), y[i * b:(i + 1) * b].contiguous().pin_memory())
+            for i in range(n_steps)]
+    yd = y.cuda()
+    ref = [float(engines[0].step_raw(dev_cols, yd, row0=i * b, batch=b).item()) for i in range(n_steps)]
+    sync = [engines[1].step_host(c, l) for c, l in host]
+    piped = []
+    for c, l in host:
+        r = engines[2].submit_host(c, l)
+        if r is not None:
+            piped.append(r)
+    piped.append(engines[2].drain())
+    assert engines[2].drain() is None
+    assert sync == piped and len(piped) == n_steps
+    assert torch.equal(engines[1].params, engines[2].params)
+    # device-resident windows of one big table vs per-batch staging buffers: same rows, same kernel
+    np.testing.assert_allclose(sync, ref, rtol=1e-6)
+    np.testing.assert_allclose(engines[1].params.cpu().numpy(), engines[0].params.cpu().numpy(), rtol=1e-5, atol=1e-7)
