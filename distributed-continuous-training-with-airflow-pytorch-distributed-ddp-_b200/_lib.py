@@ -19,6 +19,12 @@ class ModelDesc(C.Structure):
                 ("beta2", C.c_double), ("eps", C.c_double)]
 
 
+class WideDesc(C.Structure):
+    _fields_ = [("n_features", C.c_int32), ("hidden", C.c_int32), ("n_hidden", C.c_int32), ("classes", C.c_int32),
+                ("dropout_p", C.c_float), ("lr", C.c_double), ("beta1", C.c_double), ("beta2", C.c_double),
+                ("eps", C.c_double)]
+
+
 class WxError(RuntimeError):
     pass
 
@@ -63,6 +69,14 @@ SIGNATURES = {
                                     _vp, _vp]),
     "wx_mlp_eval": (_int, [_vp, _vp, _vp, _vp, _vp, _i64, _i64, _vp, _vp]),
     "wx_mlp_predict": (_int, [_vp, _vp, _vp, _i64, _vp, _vp]),
+    "wx_wide_n_params": (_i64, [C.POINTER(WideDesc)]),
+    "wx_wide_workspace_bytes": (_i64, [C.POINTER(WideDesc), _i64]),
+    "wx_wide_cast_weights": (_int, [_vp, C.POINTER(WideDesc), _vp, _vp, _vp]),
+    "wx_wide_forward": (_int, [_vp, C.POINTER(WideDesc), _vp, _vp, _vp, _vp, _i64, _int, _u64, _u64, C.c_float, _vp,
+                               _vp]),
+    "wx_wide_backward_layer": (_int, [_vp, C.POINTER(WideDesc), _vp, _i64, _int, _int, _vp, _vp]),
+    "wx_wide_adam": (_int, [_vp, C.POINTER(WideDesc), _vp, _vp, _vp, _vp, _i64, _vp, _vp]),
+    "wx_wide_gemm": (_int, [_vp, _int, _int, _vp, _i64, _vp, _i64, _i64, _i64, _i64, _vp, _vp, _vp]),
 }
 
 _lib = None

@@ -1,0 +1,652 @@
+// Wide tabular MLP (F -> H -> ... -> H -> 2, H a multiple of 256; BASELINE.json configs[3]: 4 layers, hidden 4096) on the
+// bf16 tcgen05 GEMM of wide_gemm.cuh.  Same layer pattern as the reference's net (Linear, ReLU, Dropout(p) per hidden
+// layer, Linear head, CE loss, Adam -- /root/reference/jobs/train_lightning_ddp.py:57-62,:69,:88), widened; the reference
+// has no such model, so the oracle for this path is oracle/wide_ref.py (torch fp32 with bf16 rounding at the same points).
+//
+// Data flow of one step (all device pointers caller-owned; `ws` is one caller-allocated workspace):
+//   x fp32 [B,F] --cast/pad--> X0 bf16 [B,64]
+//   H_l = drop(relu(H_{l-1} W_l^T + b_l))            GEMM, EPI_FWD      l = 1..L   (bf16 activations, fp32 accumulate)
+//   logits = H_L W_o^T + b_o ; loss ; dlogits         wide_head_kernel   (fp32, warp per row)
+//   dZ_L = (dlogits W_o) * gate(H_L) ; dW_o partials  wide_head_bwd_kernel
+//   for l = L..1:  dW_l = dZ_l^T H_{l-1}              GEMM, EPI_DW (both operands read MN-major, fp32 out)
+//                  db_l = colsum(dZ_l)                 wide_colsum_kernel + wide_reduce_kernel
+//                  dZ_{l-1} = (dZ_l W_l) * gate(H_{l-1})   GEMM, EPI_DX (W read MN-major)
+//   Adam on the fp32 master parameters, re-emitting the bf16 copies of the hidden weights in the same pass.
+#include "wide_gemm.cuh"
+
+#include <math.h>
+
+namespace {
+
+using namespace wxwide;
+
+struct AdamS {
+    float w_lerp, beta2, one_m_beta2, neg_step, bc2_sqrt, eps;
+};
+
+__device__ __forceinline__ void adam_one(float& p, float g, float& m, float& v, const AdamS& a) {
+    // torch.optim.Adam single-tensor op order (same as wxk::adam_apply)
+    m = fmaf(a.w_lerp, g - m, m);
+    v = v * a.beta2;
+    v = v + (a.one_m_beta2 * g) * g;
+    const float denom = sqrtf(v) / a.bc2_sqrt + a.eps;
+    p = p + (a.neg_step * m) / denom;
+}
+
+constexpr int KPAD = 64;          // the first layer's contraction length, zero padded (F <= 64)
+constexpr int COLSUM_SLABS = 64;
+constexpr int HEAD_SLABS = 64;
+
+struct Layout {
+    int64_t P;                    // number of fp32 parameters
+    int64_t off_w[8], off_b[8];   // parameter offsets of hidden layer l = 1..L (index l), head at index L+1
+    size_t wb[8];                 // workspace byte offsets: bf16 weights of hidden layer l
+    size_t x0, h[8], dz[2], dlog, part, dw1tmp, total;
+};
+
+size_t align_up(size_t v) { return (v + 1023) & ~size_t(1023); }
+
+int make_layout(const wx_wide_desc* d, int64_t batch, Layout* L) {
+    const int64_t F = d->n_features, H = d->hidden, C = d->classes;
+    const int nl = d->n_hidden;
+    int64_t off = 0;
+    for (int l = 1; l <= nl; ++l) {
+        const int64_t in = (l == 1) ? F : H;
+        L->off_w[l] = off;
+        off += H * in;
+        L->off_b[l] = off;
+        off += H;
+    }
+    L->off_w[nl + 1] = off;
+    off += C * H;
+    L->off_b[nl + 1] = off;
+    off += C;
+    L->P = off;
+    size_t w = 0;
+    for (int l = 1; l <= nl; ++l) {
+        L->wb[l] = w;
+        w = align_up(w + size_t(H) * ((l == 1) ? KPAD : H) * 2);
+    }
+    L->x0 = w;
+    w = align_up(w + size_t(batch) * KPAD * 2);
+    for (int l = 1; l <= nl; ++l) {
+        L->h[l] = w;
+        w = align_up(w + size_t(batch) * H * 2);
+    }
+    for (int i = 0; i < 2; ++i) {
+        L->dz[i] = w;
+        w = align_up(w + size_t(batch) * H * 2);
+    }
+    L->dlog = w;
+    w = align_up(w + size_t(batch) * 2 * 4);
+    L->part = w;   // partial sums: max(colsum: SLABS x H, head: SLABS x (2H), head rows: grid x 4)
+    w = align_up(w + size_t(HEAD_SLABS) * 2 * H * 4 + size_t(4096) * 4 * 4);
+    L->dw1tmp = w;
+    w = align_up(w + size_t(H) * KPAD * 4);
+    L->total = w;
+    return 0;
+}
+
+int check_desc(const wx_wide_desc* d, const char* who) {
+    WX_CHECK_ARG(d != nullptr, "%s: desc is NULL", who);
+    WX_CHECK_ARG(d->n_features >= 1 && d->n_features <= KPAD, "%s: n_features=%d outside 1..64", who, d->n_features);
+    WX_CHECK_ARG(d->hidden >= 256 && d->hidden % 256 == 0 && d->hidden <= 16384, "%s: hidden=%d must be a multiple of 256 in 256..16384",
+                 who, d->hidden);
+    WX_CHECK_ARG(d->n_hidden >= 1 && d->n_hidden <= 6, "%s: n_hidden=%d outside 1..6", who, d->n_hidden);
+    WX_CHECK_ARG(d->classes == 2, "%s: classes=%d, only 2 is supported (train_lightning_ddp.py:61)", who, d->classes);
+    WX_CHECK_ARG(d->dropout_p >= 0.0f && d->dropout_p < 1.0f, "%s: dropout_p=%f outside [0,1)", who, d->dropout_p);
+    return WX_OK;
+}
+
+// ------------------------------------------------------------------------------------------------------------------
+// small kernels
+// ------------------------------------------------------------------------------------------------------------------
+// fp32 [rows, in] -> bf16 [rows, pad] (zero padded); used for x and for the first layer's weights
+__global__ void __launch_bounds__(256) cast_pad_kernel(const float* __restrict__ src, int64_t rows, int in, int pad,
+                                                      __nv_bfloat16* __restrict__ dst) {
+    const int64_t total = rows * pad;
+    for (int64_t i = int64_t(blockIdx.x) * blockDim.x + threadIdx.x; i < total; i += int64_t(gridDim.x) * blockDim.x) {
+        const int64_t r = i / pad;
+        const int c = int(i - r * pad);
+        dst[i] = __float2bfloat16_rn(c < in ? src[r * in + c] : 0.0f);
+    }
+}
+
+__global__ void __launch_bounds__(256) cast_kernel(const float* __restrict__ src, int64_t n, __nv_bfloat16* __restrict__ dst) {
+    const int64_t n4 = n >> 2;
+    for (int64_t i = int64_t(blockIdx.x) * blockDim.x + threadIdx.x; i < n4; i += int64_t(gridDim.x) * blockDim.x) {
+        const float4 v = reinterpret_cast<const float4*>(src)[i];
+        uint2 o;
+        o.x = pack_bf16(v.x, v.y);
+        o.y = pack_bf16(v.z, v.w);
+        reinterpret_cast<uint2*>(dst)[i] = o;
+    }
+}
+
+__device__ __forceinline__ void unpack8(const uint4& u, float (&f)[8]) {
+    const uint32_t w[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        f[2 * i] = __uint_as_float(w[i] << 16);
+        f[2 * i + 1] = __uint_as_float(w[i] & 0xFFFF0000u);
+    }
+}
+
+// head forward + loss: one warp per row.  logits = h . W_o^T + b_o (fp32), CE, dlogits = (softmax - onehot) * scale.
+// Per-CTA partial (loss*scale, sum dl0, sum dl1) -> part[blockIdx][4]; reduced in order by wide_reduce_kernel.
+__global__ void __launch_bounds__(256) wide_head_kernel(const __nv_bfloat16* __restrict__ h, int64_t batch, int H,
+                                                       const float* __restrict__ w_o, const float* __restrict__ b_o,
+                                                       const int64_t* __restrict__ y, float scale,
+                                                       float* __restrict__ dlog, float* __restrict__ part) {
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    float acc_loss = 0.0f, acc0 = 0.0f, acc1 = 0.0f;
+    for (int64_t row = int64_t(blockIdx.x) * 8 + warp; row < batch; row += int64_t(gridDim.x) * 8) {
+        const uint4* hp = reinterpret_cast<const uint4*>(h + row * H);
+        float s0 = 0.0f, s1 = 0.0f;
+        for (int c8 = lane; c8 < H / 8; c8 += 32) {
+            float f[8];
+            unpack8(__ldg(hp + c8), f);
+            const float4* w0 = reinterpret_cast<const float4*>(w_o + c8 * 8);
+            const float4* w1 = reinterpret_cast<const float4*>(w_o + H + c8 * 8);
+            const float4 a0 = __ldg(w0), a1 = __ldg(w0 + 1), c0 = __ldg(w1), c1 = __ldg(w1 + 1);
+            s0 = fmaf(f[0], a0.x, s0); s0 = fmaf(f[1], a0.y, s0); s0 = fmaf(f[2], a0.z, s0); s0 = fmaf(f[3], a0.w, s0);
+            s0 = fmaf(f[4], a1.x, s0); s0 = fmaf(f[5], a1.y, s0); s0 = fmaf(f[6], a1.z, s0); s0 = fmaf(f[7], a1.w, s0);
+            s1 = fmaf(f[0], c0.x, s1); s1 = fmaf(f[1], c0.y, s1); s1 = fmaf(f[2], c0.z, s1); s1 = fmaf(f[3], c0.w, s1);
+            s1 = fmaf(f[4], c1.x, s1); s1 = fmaf(f[5], c1.y, s1); s1 = fmaf(f[6], c1.z, s1); s1 = fmaf(f[7], c1.w, s1);
+        }
+        s0 = warp_sum(s0) + b_o[0];
+        s1 = warp_sum(s1) + b_o[1];
+        if (lane == 0) {
+            const float mx = fmaxf(s0, s1);
+            const float e0 = expf(s0 - mx), e1 = expf(s1 - mx);
+            const float lse = mx + logf(e0 + e1);
+            const int64_t lab = y[row];
+            const float inv = 1.0f / (e0 + e1);
+            const float d0 = (e0 * inv - (lab == 0 ? 1.0f : 0.0f)) * scale;
+            const float d1 = (e1 * inv - (lab == 1 ? 1.0f : 0.0f)) * scale;
+            dlog[row * 2] = d0;
+            dlog[row * 2 + 1] = d1;
+            acc_loss += (lse - (lab == 0 ? s0 : s1)) * scale;
+            acc0 += d0;
+            acc1 += d1;
+        }
+    }
+    __shared__ float sh[8][3];
+    if (lane == 0) {
+        sh[warp][0] = acc_loss;
+        sh[warp][1] = acc0;
+        sh[warp][2] = acc1;
+    }
+    __syncthreads();
+    if (threadIdx.x < 3) {
+        float t = 0.0f;
+        for (int w = 0; w < 8; ++w) t += sh[w][threadIdx.x];
+        part[blockIdx.x * 4 + threadIdx.x] = t;
+    }
+    if (threadIdx.x == 3) part[blockIdx.x * 4 + 3] = 0.0f;
+}
+
+// head backward: dZ_L[r][c] = (dl0[r] W_o[0][c] + dl1[r] W_o[1][c]) * gate(H_L[r][c]) as bf16, and per-slab partial sums
+// of dW_o[k][c] = sum_r dl_k[r] H_L[r][c].  Thread = 8 columns, CTA = 2048 columns, grid.y = row slabs.
+__global__ void __launch_bounds__(256) wide_head_bwd_kernel(const __nv_bfloat16* __restrict__ h, int64_t batch, int H,
+                                                           const float* __restrict__ w_o, const float* __restrict__ dlog,
+                                                           float inv_keep, __nv_bfloat16* __restrict__ dz,
+                                                           float* __restrict__ part) {
+    const int c8 = blockIdx.x * 256 + threadIdx.x;          // 8-column group
+    if (c8 * 8 >= H) return;
+    const int64_t rows_per = (batch + gridDim.y - 1) / gridDim.y;
+    const int64_t r0 = int64_t(blockIdx.y) * rows_per, r1 = (r0 + rows_per < batch) ? r0 + rows_per : batch;
+    float w0[8], w1[8], a0[8], a1[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        w0[i] = __ldg(w_o + c8 * 8 + i);
+        w1[i] = __ldg(w_o + H + c8 * 8 + i);
+        a0[i] = 0.0f;
+        a1[i] = 0.0f;
+    }
+    for (int64_t r = r0; r < r1; ++r) {
+        const float2 dl = __ldg(reinterpret_cast<const float2*>(dlog) + r);
+        const uint4 hv = __ldg(reinterpret_cast<const uint4*>(h + r * H) + c8);
+        float f[8], o[8];
+        unpack8(hv, f);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            a0[i] = fmaf(dl.x, f[i], a0[i]);
+            a1[i] = fmaf(dl.y, f[i], a1[i]);
+            const float dh = fmaf(dl.x, w0[i], dl.y * w1[i]);
+            o[i] = f[i] > 0.0f ? dh * inv_keep : 0.0f;
+        }
+        uint4 ov;
+        ov.x = pack_bf16(o[0], o[1]);
+        ov.y = pack_bf16(o[2], o[3]);
+        ov.z = pack_bf16(o[4], o[5]);
+        ov.w = pack_bf16(o[6], o[7]);
+        reinterpret_cast<uint4*>(dz + r * H)[c8] = ov;
+    }
+    float* p = part + size_t(blockIdx.y) * 2 * H;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        p[c8 * 8 + i] = a0[i];
+        p[H + c8 * 8 + i] = a1[i];
+    }
+}
+
+// per-slab column sums of a bf16 [batch, H] matrix (bias gradients)
+__global__ void __launch_bounds__(256) wide_colsum_kernel(const __nv_bfloat16* __restrict__ dz, int64_t batch, int H,
+                                                         float* __restrict__ part) {
+    const int c8 = blockIdx.x * 256 + threadIdx.x;
+    if (c8 * 8 >= H) return;
+    const int64_t rows_per = (batch + gridDim.y - 1) / gridDim.y;
+    const int64_t r0 = int64_t(blockIdx.y) * rows_per, r1 = (r0 + rows_per < batch) ? r0 + rows_per : batch;
+    float a[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    for (int64_t r = r0; r < r1; ++r) {
+        float f[8];
+        unpack8(__ldg(reinterpret_cast<const uint4*>(dz + r * H) + c8), f);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) a[i] += f[i];
+    }
+    float* p = part + size_t(blockIdx.y) * H;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) p[c8 * 8 + i] = a[i];
+}
+
+// out[i] = sum over parts (in order) of part[p * stride + i]
+__global__ void __launch_bounds__(256) wide_reduce_kernel(const float* __restrict__ part, int n_parts, int64_t stride,
+                                                         int64_t n, float* __restrict__ out) {
+    const int64_t i = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    float t = 0.0f;
+    for (int p = 0; p < n_parts; ++p) t += part[size_t(p) * stride + i];
+    out[i] = t;
+}
+
+// head partials [n_parts][4] = (loss, db0, db1, -) -> grads[off_b_out .. +2] and grads[P]
+__global__ void wide_head_finish_kernel(const float* __restrict__ part, int n_parts, float* __restrict__ db_out,
+                                        float* __restrict__ loss_out) {
+    const int t = threadIdx.x;
+    if (t >= 3) return;
+    float s = 0.0f;
+    for (int p = 0; p < n_parts; ++p) s += part[p * 4 + t];
+    if (t == 0) *loss_out = s;
+    else db_out[t - 1] = s;
+}
+
+// [H, 64] fp32 -> [H, F] fp32 (first layer's weight gradient without the padding columns)
+__global__ void __launch_bounds__(256) unpad_kernel(const float* __restrict__ src, int64_t rows, int in, int pad,
+                                                   float* __restrict__ dst) {
+    const int64_t total = rows * in;
+    for (int64_t i = int64_t(blockIdx.x) * blockDim.x + threadIdx.x; i < total; i += int64_t(gridDim.x) * blockDim.x) {
+        const int64_t r = i / in;
+        dst[i] = src[r * pad + (i - r * in)];
+    }
+}
+
+// Adam over one parameter tensor; optionally re-emits its bf16 copy ([rows, pad] with `in` valid columns per row).
+__global__ void __launch_bounds__(256) wide_adam_kernel(float* __restrict__ p, const float* __restrict__ g,
+                                                       float* __restrict__ m, float* __restrict__ v, int64_t n, AdamS a,
+                                                       __nv_bfloat16* __restrict__ wb, int in, int pad) {
+    const int64_t stride = int64_t(gridDim.x) * blockDim.x;
+    const int64_t t0 = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (in == pad && (n & 3) == 0) {
+        const int64_t n4 = n >> 2;
+        for (int64_t i = t0; i < n4; i += stride) {
+            float4 pp = reinterpret_cast<float4*>(p)[i], mm = reinterpret_cast<float4*>(m)[i],
+                   vv = reinterpret_cast<float4*>(v)[i];
+            const float4 gg = __ldg(reinterpret_cast<const float4*>(g) + i);
+            adam_one(pp.x, gg.x, mm.x, vv.x, a);
+            adam_one(pp.y, gg.y, mm.y, vv.y, a);
+            adam_one(pp.z, gg.z, mm.z, vv.z, a);
+            adam_one(pp.w, gg.w, mm.w, vv.w, a);
+            reinterpret_cast<float4*>(p)[i] = pp;
+            reinterpret_cast<float4*>(m)[i] = mm;
+            reinterpret_cast<float4*>(v)[i] = vv;
+            if (wb != nullptr) {
+                uint2 o;
+                o.x = pack_bf16(pp.x, pp.y);
+                o.y = pack_bf16(pp.z, pp.w);
+                reinterpret_cast<uint2*>(wb)[i] = o;
+            }
+        }
+    } else {
+        for (int64_t i = t0; i < n; i += stride) {
+            float pp = p[i], mm = m[i], vv = v[i];
+            adam_one(pp, g[i], mm, vv, a);
+            p[i] = pp;
+            m[i] = mm;
+            v[i] = vv;
+            if (wb != nullptr) {
+                const int64_t r = i / in;
+                wb[r * pad + (i - r * in)] = __float2bfloat16_rn(pp);
+            }
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------------------------
+// tensor maps and GEMM launches
+// ------------------------------------------------------------------------------------------------------------------
+typedef CUresult (*encode_fn_t)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+encode_fn_t get_encode() {
+    static encode_fn_t fn = nullptr;
+    if (fn == nullptr) {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+            q == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<encode_fn_t>(p);
+    }
+    return fn;
+}
+
+// bf16 row-major [rows, cols] (pitch in elements); box = 64 columns x box_rows rows, 128-byte swizzle
+int make_map(CUtensorMap* tm, const void* base, int64_t rows, int64_t cols, int64_t pitch, int box_rows) {
+    encode_fn_t enc = get_encode();
+    if (enc == nullptr) {
+        wx_set_error("cuTensorMapEncodeTiled is not available from this driver");
+        return WX_ECUDA;
+    }
+    const cuuint64_t dims[2] = {cuuint64_t(cols), cuuint64_t(rows)};
+    const cuuint64_t strides[1] = {cuuint64_t(pitch) * 2};
+    const cuuint32_t box[2] = {64u, cuuint32_t(box_rows)};
+    const cuuint32_t estr[2] = {1u, 1u};
+    const CUresult r = enc(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
+                           CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                           CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        wx_set_error("cuTensorMapEncodeTiled failed with CUresult %d (base %p, %lld x %lld, pitch %lld)", int(r), base,
+                     (long long)rows, (long long)cols, (long long)pitch);
+        return WX_ECUDA;
+    }
+    return WX_OK;
+}
+
+template <bool A_K, bool B_K, int EPI>
+int launch_gemm_t(wx_ctx* ctx, const CUtensorMap& ta, const CUtensorMap& tb, const GemmArgs& g, cudaStream_t st) {
+    static bool attr_set[64] = {};
+    if (!attr_set[ctx->device & 63]) {
+        WX_CUDA(cudaFuncSetAttribute(wide_gemm_kernel<A_K, B_K, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     int(GEMM_SMEM)));
+        attr_set[ctx->device & 63] = true;
+    }
+    const int64_t tiles = ((g.M + BM - 1) / BM) * ((g.N + BN - 1) / BN);
+    const int grid = int(tiles < ctx->num_sms ? tiles : ctx->num_sms);
+    wide_gemm_kernel<A_K, B_K, EPI><<<grid, GEMM_THREADS, GEMM_SMEM, st>>>(ta, tb, g);
+    WX_LAUNCH_CHECK(ctx);
+    return WX_OK;
+}
+
+// D[M,N] = op(A) op(B): a_k / b_k say whether the operand is stored [M|N, K] (true) or [K, M|N] (false), row-major bf16.
+int launch_gemm(wx_ctx* ctx, bool a_k, bool b_k, int epi, const void* A, int64_t lda, const void* B, int64_t ldb,
+                GemmArgs g, cudaStream_t st) {
+    CUtensorMap ta, tb;
+    int rc;
+    if (a_k) rc = make_map(&ta, A, g.M, g.K, lda, BM);
+    else rc = make_map(&ta, A, g.K, g.M, lda, 64);
+    if (rc != WX_OK) return rc;
+    if (b_k) rc = make_map(&tb, B, g.N, g.K, ldb, BN);
+    else rc = make_map(&tb, B, g.K, g.N, ldb, 64);
+    if (rc != WX_OK) return rc;
+    g.err = reinterpret_cast<int*>(ctx->scratch) + 8;   // sticky status word (wx_tc_last_status)
+    if (a_k && b_k) {
+        if (epi == EPI_FWD) return launch_gemm_t<true, true, EPI_FWD>(ctx, ta, tb, g, st);
+        if (epi == EPI_PLAIN) return launch_gemm_t<true, true, EPI_PLAIN>(ctx, ta, tb, g, st);
+    } else if (a_k && !b_k) {
+        if (epi == EPI_DX) return launch_gemm_t<true, false, EPI_DX>(ctx, ta, tb, g, st);
+        if (epi == EPI_PLAIN) return launch_gemm_t<true, false, EPI_PLAIN>(ctx, ta, tb, g, st);
+    } else if (!a_k && !b_k) {
+        if (epi == EPI_DW) return launch_gemm_t<false, false, EPI_DW>(ctx, ta, tb, g, st);
+        if (epi == EPI_PLAIN) return launch_gemm_t<false, false, EPI_PLAIN>(ctx, ta, tb, g, st);
+    }
+    wx_set_error("wide gemm: unsupported layout/epilogue combination (a_k=%d b_k=%d epi=%d)", int(a_k), int(b_k), epi);
+    return WX_EINVAL;
+}
+
+AdamS adam_consts(const wx_wide_desc* d, int64_t step) {
+    AdamS a;
+    const double bc1 = 1.0 - pow(d->beta1, double(step)), bc2 = 1.0 - pow(d->beta2, double(step));
+    a.w_lerp = float(1.0 - d->beta1);
+    a.beta2 = float(d->beta2);
+    a.one_m_beta2 = float(1.0 - d->beta2);
+    a.neg_step = float(-(d->lr / bc1));
+    a.bc2_sqrt = float(sqrt(bc2));
+    a.eps = float(d->eps);
+    return a;
+}
+
+int grid_for(const wx_ctx* ctx, int64_t n, int per_thread = 1) {
+    int64_t b = (n / per_thread + 255) / 256;
+    const int64_t cap = int64_t(ctx->num_sms) * 8;
+    if (b > cap) b = cap;
+    if (b < 1) b = 1;
+    return int(b);
+}
+
+}  // namespace
+
+extern "C" {
+
+int64_t wx_wide_n_params(const wx_wide_desc* desc) {
+    if (check_desc(desc, "wx_wide_n_params") != WX_OK) return -1;
+    Layout L;
+    make_layout(desc, 128, &L);
+    return L.P;
+}
+
+int64_t wx_wide_workspace_bytes(const wx_wide_desc* desc, int64_t batch) {
+    if (check_desc(desc, "wx_wide_workspace_bytes") != WX_OK) return -1;
+    if (batch < 128 || batch % 128 != 0) {
+        wx_set_error("wx_wide_workspace_bytes: batch=%lld must be a positive multiple of 128", (long long)batch);
+        return -1;
+    }
+    Layout L;
+    make_layout(desc, batch, &L);
+    return int64_t(L.total);
+}
+
+/* Self-test / building block: D[M,N] (fp32, pitch N) = op(A) op(B) (+ bias), bf16 operands, fp32 accumulate. */
+int wx_wide_gemm(wx_ctx* ctx, int a_kmajor, int b_kmajor, const void* A, int64_t lda, const void* B, int64_t ldb,
+                 int64_t M, int64_t N, int64_t K, const float* bias, float* out, void* stream) {
+    WX_CHECK_ARG(ctx && A && B && out, "wx_wide_gemm: NULL argument");
+    WX_CHECK_ARG(M >= 1 && N >= 16 && N % 16 == 0 && K >= 64 && K % 64 == 0, "wx_wide_gemm: need N %% 16 == 0, K %% 64 == 0");
+    WX_CHECK_ARG((reinterpret_cast<uintptr_t>(A) | reinterpret_cast<uintptr_t>(B) | reinterpret_cast<uintptr_t>(out)) % 16 == 0 &&
+                     lda % 8 == 0 && ldb % 8 == 0,
+                 "wx_wide_gemm: operands must be 16-byte aligned with pitches that are multiples of 8 elements");
+    WX_CUDA(cudaSetDevice(ctx->device));
+    GemmArgs g = {};
+    g.M = M; g.N = N; g.K = K;
+    g.out = out; g.ldo = N; g.bias = bias;
+    g.inv_keep = 1.0f; g.keep_thresh16 = 65536u;
+    return launch_gemm(ctx, a_kmajor != 0, b_kmajor != 0, EPI_PLAIN, A, lda, B, ldb, g, (cudaStream_t)stream);
+}
+
+int wx_wide_cast_weights(wx_ctx* ctx, const wx_wide_desc* desc, const float* params, void* ws, void* stream) {
+    WX_CHECK_ARG(ctx && params && ws, "wx_wide_cast_weights: NULL argument");
+    int rc = check_desc(desc, "wx_wide_cast_weights");
+    if (rc != WX_OK) return rc;
+    WX_CUDA(cudaSetDevice(ctx->device));
+    Layout L;
+    make_layout(desc, 128, &L);
+    cudaStream_t st = (cudaStream_t)stream;
+    unsigned char* w = static_cast<unsigned char*>(ws);
+    const int64_t H = desc->hidden;
+    cast_pad_kernel<<<grid_for(ctx, H * KPAD), 256, 0, st>>>(params + L.off_w[1], H, desc->n_features, KPAD,
+                                                            reinterpret_cast<__nv_bfloat16*>(w + L.wb[1]));
+    WX_LAUNCH_CHECK(ctx);
+    for (int l = 2; l <= desc->n_hidden; ++l) {
+        cast_kernel<<<grid_for(ctx, H * H, 4), 256, 0, st>>>(params + L.off_w[l], H * H,
+                                                           reinterpret_cast<__nv_bfloat16*>(w + L.wb[l]));
+        WX_LAUNCH_CHECK(ctx);
+    }
+    return WX_OK;
+}
+
+/* Forward through the loss, plus the head's gradients and dZ of the last hidden layer.
+ *   x      fp32 [batch, F] row-major, standardised (the output of wx_normalize_pack)
+ *   grads  fp32 [P+1]: receives dW_o, db_o and, at [P], sum_rows(CE) * grad_scale
+ *   grad_scale = 1 / (world * batch): gradients and loss come out pre-scaled for a SUM all-reduce (DDP, :136)
+ *   dropout_mode: WX_DROPOUT_OFF or WX_DROPOUT_PHILOX (keep <=> 16 Philox bits < round((1-p) * 65536);
+ *                 counter (row, col/8, layer, step), key seed -- oracle/wide_ref.py keep_mask) */
+int wx_wide_forward(wx_ctx* ctx, const wx_wide_desc* desc, const float* params, void* ws, const float* x,
+                    const int64_t* y, int64_t batch, int dropout_mode, uint64_t seed, uint64_t step, float grad_scale,
+                    float* grads, void* stream) {
+    WX_CHECK_ARG(ctx && params && ws && x && y && grads, "wx_wide_forward: NULL argument");
+    int rc = check_desc(desc, "wx_wide_forward");
+    if (rc != WX_OK) return rc;
+    WX_CHECK_ARG(batch >= 128 && batch % 128 == 0, "wx_wide_forward: batch=%lld must be a positive multiple of 128",
+                 (long long)batch);
+    WX_CHECK_ARG(dropout_mode == WX_DROPOUT_OFF || dropout_mode == WX_DROPOUT_PHILOX,
+                 "wx_wide_forward: dropout_mode=%d (OFF or PHILOX)", dropout_mode);
+    WX_CUDA(cudaSetDevice(ctx->device));
+    Layout L;
+    make_layout(desc, batch, &L);
+    cudaStream_t st = (cudaStream_t)stream;
+    unsigned char* w = static_cast<unsigned char*>(ws);
+    const int64_t H = desc->hidden;
+    const int nl = desc->n_hidden;
+    const bool drop = dropout_mode == WX_DROPOUT_PHILOX && desc->dropout_p > 0.0f;
+    const float keep_p = 1.0f - desc->dropout_p;
+    __nv_bfloat16* x0 = reinterpret_cast<__nv_bfloat16*>(w + L.x0);
+    cast_pad_kernel<<<grid_for(ctx, batch * KPAD), 256, 0, st>>>(x, batch, desc->n_features, KPAD, x0);
+    WX_LAUNCH_CHECK(ctx);
+    for (int l = 1; l <= nl; ++l) {
+        GemmArgs g = {};
+        g.M = batch; g.N = H; g.K = (l == 1) ? KPAD : H;
+        g.out = w + L.h[l]; g.ldo = H;
+        g.bias = params + L.off_b[l];
+        g.inv_keep = drop ? 1.0f / keep_p : 1.0f;
+        g.keep_thresh16 = drop ? uint32_t(lrintf(keep_p * 65536.0f)) : 65536u;
+        g.seed_lo = uint32_t(seed); g.seed_hi = uint32_t(seed >> 32);
+        g.step = uint32_t(step); g.layer = uint32_t(l);
+        const void* a = (l == 1) ? static_cast<const void*>(x0) : static_cast<const void*>(w + L.h[l - 1]);
+        rc = launch_gemm(ctx, true, true, EPI_FWD, a, g.K, w + L.wb[l], g.K, g, st);
+        if (rc != WX_OK) return rc;
+    }
+    const __nv_bfloat16* hl = reinterpret_cast<const __nv_bfloat16*>(w + L.h[nl]);
+    float* dlog = reinterpret_cast<float*>(w + L.dlog);
+    float* part = reinterpret_cast<float*>(w + L.part);
+    float* head_part = part + size_t(HEAD_SLABS) * 2 * H;       // [grid][4]
+    int hgrid = int((batch + 7) / 8);
+    if (hgrid > 4096) hgrid = 4096;
+    wide_head_kernel<<<hgrid, 256, 0, st>>>(hl, batch, int(H), params + L.off_w[nl + 1], params + L.off_b[nl + 1], y,
+                                           grad_scale, dlog, head_part);
+    WX_LAUNCH_CHECK(ctx);
+    wide_head_finish_kernel<<<1, 32, 0, st>>>(head_part, hgrid, grads + L.off_b[nl + 1], grads + L.P);
+    WX_LAUNCH_CHECK(ctx);
+    int slabs = int(batch / 128 < HEAD_SLABS ? batch / 128 : HEAD_SLABS);
+    dim3 bg((unsigned)((H / 8 + 255) / 256), (unsigned)slabs);
+    wide_head_bwd_kernel<<<bg, 256, 0, st>>>(hl, batch, int(H), params + L.off_w[nl + 1], dlog,
+                                            drop ? 1.0f / keep_p : 1.0f,
+                                            reinterpret_cast<__nv_bfloat16*>(w + L.dz[0]), part);
+    WX_LAUNCH_CHECK(ctx);
+    wide_reduce_kernel<<<int((2 * H + 255) / 256), 256, 0, st>>>(part, slabs, 2 * H, 2 * H, grads + L.off_w[nl + 1]);
+    WX_LAUNCH_CHECK(ctx);
+    return WX_OK;
+}
+
+/* Backward of hidden layer `layer` (call with layer = n_hidden, ..., 1 after wx_wide_forward): writes dW_layer and
+ * db_layer into grads and, for layer > 1, dZ of the layer below into the workspace. */
+int wx_wide_backward_layer(wx_ctx* ctx, const wx_wide_desc* desc, void* ws, int64_t batch, int layer, int dropout_mode,
+                           float* grads, void* stream) {
+    WX_CHECK_ARG(ctx && ws && grads, "wx_wide_backward_layer: NULL argument");
+    int rc = check_desc(desc, "wx_wide_backward_layer");
+    if (rc != WX_OK) return rc;
+    WX_CHECK_ARG(batch >= 128 && batch % 128 == 0, "wx_wide_backward_layer: batch=%lld must be a positive multiple of 128",
+                 (long long)batch);
+    const int nl = desc->n_hidden;
+    WX_CHECK_ARG(layer >= 1 && layer <= nl, "wx_wide_backward_layer: layer=%d outside 1..%d", layer, nl);
+    WX_CUDA(cudaSetDevice(ctx->device));
+    Layout L;
+    make_layout(desc, batch, &L);
+    cudaStream_t st = (cudaStream_t)stream;
+    unsigned char* w = static_cast<unsigned char*>(ws);
+    const int64_t H = desc->hidden;
+    const bool drop = dropout_mode == WX_DROPOUT_PHILOX && desc->dropout_p > 0.0f;
+    const void* dz = w + L.dz[(nl - layer) & 1];
+    void* dz_below = w + L.dz[(nl - layer + 1) & 1];
+    const void* h_below = (layer == 1) ? static_cast<const void*>(w + L.x0) : static_cast<const void*>(w + L.h[layer - 1]);
+    const int64_t in = (layer == 1) ? KPAD : H;
+    // dW = dZ^T H_below : A = dZ stored [batch, H] = [K, M], B = H_below stored [batch, in] = [K, N]
+    {
+        GemmArgs g = {};
+        g.M = H; g.N = in; g.K = batch;
+        g.inv_keep = 1.0f; g.keep_thresh16 = 65536u;
+        if (layer == 1) {
+            g.out = w + L.dw1tmp; g.ldo = KPAD;
+        } else {
+            g.out = grads + L.off_w[layer]; g.ldo = H;
+        }
+        rc = launch_gemm(ctx, false, false, EPI_DW, dz, H, h_below, in, g, st);
+        if (rc != WX_OK) return rc;
+        if (layer == 1) {
+            unpad_kernel<<<grid_for(ctx, H * desc->n_features), 256, 0, st>>>(
+                reinterpret_cast<const float*>(w + L.dw1tmp), H, desc->n_features, KPAD, grads + L.off_w[1]);
+            WX_LAUNCH_CHECK(ctx);
+        }
+    }
+    // db = column sums of dZ
+    {
+        float* part = reinterpret_cast<float*>(w + L.part);
+        int slabs = int(batch / 128 < COLSUM_SLABS ? batch / 128 : COLSUM_SLABS);
+        dim3 cg((unsigned)((H / 8 + 255) / 256), (unsigned)slabs);
+        wide_colsum_kernel<<<cg, 256, 0, st>>>(reinterpret_cast<const __nv_bfloat16*>(dz), batch, int(H), part);
+        WX_LAUNCH_CHECK(ctx);
+        wide_reduce_kernel<<<int((H + 255) / 256), 256, 0, st>>>(part, slabs, H, H, grads + L.off_b[layer]);
+        WX_LAUNCH_CHECK(ctx);
+    }
+    // dZ_below = (dZ W) * gate(H_below): A = dZ [batch, H] K-major, B = W stored [H(out), H(in)] = [K, N]
+    if (layer > 1) {
+        GemmArgs g = {};
+        g.M = batch; g.N = H; g.K = H;
+        g.out = dz_below; g.ldo = H;
+        g.gate = reinterpret_cast<const __nv_bfloat16*>(h_below); g.ldg = H;
+        g.inv_keep = drop ? 1.0f / (1.0f - desc->dropout_p) : 1.0f;
+        g.keep_thresh16 = 65536u;
+        rc = launch_gemm(ctx, true, false, EPI_DX, dz, H, w + L.wb[layer], H, g, st);
+        if (rc != WX_OK) return rc;
+    }
+    return WX_OK;
+}
+
+/* Adam (train_lightning_ddp.py:88 arithmetic) over all P parameters; the hidden layers' bf16 copies in the workspace are
+ * rewritten in the same pass.  step is 1-based. */
+int wx_wide_adam(wx_ctx* ctx, const wx_wide_desc* desc, float* params, const float* grads, float* m, float* v,
+                 int64_t step, void* ws, void* stream) {
+    WX_CHECK_ARG(ctx && params && grads && m && v && ws, "wx_wide_adam: NULL argument");
+    int rc = check_desc(desc, "wx_wide_adam");
+    if (rc != WX_OK) return rc;
+    WX_CHECK_ARG(step >= 1, "wx_wide_adam: step=%lld must be >= 1", (long long)step);
+    WX_CUDA(cudaSetDevice(ctx->device));
+    Layout L;
+    make_layout(desc, 128, &L);
+    cudaStream_t st = (cudaStream_t)stream;
+    unsigned char* w = static_cast<unsigned char*>(ws);
+    const AdamS a = adam_consts(desc, step);
+    const int64_t H = desc->hidden;
+    const int nl = desc->n_hidden;
+    for (int l = 1; l <= nl; ++l) {
+        const int64_t in = (l == 1) ? desc->n_features : H;
+        const int64_t nw = H * in;
+        wide_adam_kernel<<<grid_for(ctx, nw, 4), 256, 0, st>>>(params + L.off_w[l], grads + L.off_w[l], m + L.off_w[l],
+                                                             v + L.off_w[l], nw, a,
+                                                             reinterpret_cast<__nv_bfloat16*>(w + L.wb[l]), int(in),
+                                                             l == 1 ? KPAD : int(in));
+        WX_LAUNCH_CHECK(ctx);
+    }
+    // biases and the head: everything that is not a hidden weight, tensor by tensor (contiguous runs)
+    for (int l = 1; l <= nl + 1; ++l) {
+        const int64_t b0 = L.off_b[l], bn = (l <= nl) ? H : desc->classes;
+        wide_adam_kernel<<<grid_for(ctx, bn), 256, 0, st>>>(params + b0, grads + b0, m + b0, v + b0, bn, a, nullptr, 1, 1);
+        WX_LAUNCH_CHECK(ctx);
+    }
+    {
+        const int64_t w0 = L.off_w[nl + 1], wn = int64_t(desc->classes) * H;
+        wide_adam_kernel<<<grid_for(ctx, wn, 4), 256, 0, st>>>(params + w0, grads + w0, m + w0, v + w0, wn, a, nullptr, 1, 1);
+        WX_LAUNCH_CHECK(ctx);
+    }
+    return WX_OK;
+}
+
+}  // extern "C"

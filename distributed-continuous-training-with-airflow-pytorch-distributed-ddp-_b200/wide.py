@@ -1,0 +1,151 @@
+"""Wide tabular MLP (BASELINE.json configs[3]: 4 layers, hidden 4096) on the bf16 tcgen05 GEMMs of libwxddp.so.
+
+Same operator shape as the narrow StepEngine: one object per process / GPU holding flat fp32 parameters, Adam moments and
+the workspace; `step(x, y)` = forward, CE loss, backward, DDP gradient mean over ranks, Adam -- the loop Lightning runs
+around jobs/train_lightning_ddp.py:66-71,:88,:136, for a net of the same pattern (:57-62) widened.  The DDP exchange is
+bucketed by layer: the all-reduce of layer l's slice runs on a side stream while layer l-1's backward GEMMs run.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import torch
+
+from ._lib import DROPOUT_OFF, DROPOUT_PHILOX, ModelDesc, WideDesc, WxError, check, load
+
+
+class WideEngine:
+    def __init__(self, n_features: int, hidden: int = 4096, n_hidden: int = 3, *, max_batch: int, device=0, world: int = 1,
+                 rank: int = 0, process_group=None, params: torch.Tensor | None = None, seed: int = 42, lr: float = 0.01,
+                 dropout_p: float = 0.2):
+        if not torch.cuda.is_available():
+            raise WxError("wxddp needs a CUDA device (B200, sm_100a): there is no CPU fallback")
+        self.device = torch.device("cuda", device) if not isinstance(device, torch.device) else device
+        self.lib = load()
+        self.desc = WideDesc(n_features, hidden, n_hidden, 2, dropout_p, lr, 0.9, 0.999, 1e-8)
+        self.F, self.H, self.L = n_features, hidden, n_hidden
+        self.P = int(self.lib.wx_wide_n_params(C.byref(self.desc)))
+        if self.P < 0:
+            check(-1)
+        # a context of the narrow model carries the device, scratch and launch counter (wx_create is the only allocator)
+        h = C.c_void_p()
+        nd = ModelDesc(min(n_features, 32), 64, 2, 0.2, lr, 0.9, 0.999, 1e-8)
+        check(self.lib.wx_create(self.device.index, C.byref(nd), C.byref(h)))
+        self._h = h
+        self.max_batch = max_batch
+        nbytes = int(self.lib.wx_wide_workspace_bytes(C.byref(self.desc), max_batch))
+        if nbytes < 0:
+            check(-1)
+        self.ws = torch.empty(nbytes, dtype=torch.uint8, device=self.device)
+        self.world, self.rank, self.dist = world, rank, process_group
+        if world > 1 and process_group is None:
+            raise WxError("world > 1 needs an initialised torch.distributed (NCCL) handle")
+        if params is None:
+            from torch import nn
+            parts = []
+            for l in range(n_hidden + 1):
+                lin = nn.Linear(n_features if l == 0 else hidden, hidden if l < n_hidden else 2)
+                parts += [lin.weight.detach().reshape(-1), lin.bias.detach()]
+            params = torch.cat(parts)
+        if params.numel() != self.P:
+            raise WxError(f"params has {params.numel()} elements, the model has {self.P}")
+        self.params = params.detach().to(self.device, torch.float32).contiguous().clone()
+        if world > 1:
+            self.dist.broadcast(self.params, src=0)
+        self.m = torch.zeros(self.P, device=self.device)
+        self.v = torch.zeros(self.P, device=self.device)
+        self.grads = torch.zeros(self.P + 1, device=self.device)
+        self.seed, self.steps_done = seed, 0
+        self._side = torch.cuda.Stream(device=self.device) if world > 1 else None
+        # slices of the flat gradient per hidden layer (W_l, b_l contiguous), head last (+ the loss element)
+        self.slices, off = [], 0
+        for l in range(n_hidden):
+            n = hidden * (n_features if l == 0 else hidden) + hidden
+            self.slices.append((off, off + n))
+            off += n
+        self.head_slice = (off, self.P + 1)
+        self.cast_weights()
+
+    def __del__(self):
+        try:
+            if getattr(self, "_h", None):
+                self.lib.wx_destroy(self._h)
+                self._h = None
+        except Exception:
+            pass
+
+    def _stream(self):
+        return C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
+
+    @property
+    def launch_count(self) -> int:
+        return int(self.lib.wx_launch_count(self._h))
+
+    def status(self) -> int:
+        out = C.c_int(0)
+        check(self.lib.wx_tc_last_status(self._h, C.byref(out)))
+        return out.value
+
+    def cast_weights(self) -> None:
+        check(self.lib.wx_wide_cast_weights(self._h, C.byref(self.desc), self.params.data_ptr(), self.ws.data_ptr(),
+                                            self._stream()))
+
+    def _check_batch(self, x, y):
+        b = x.shape[0]
+        if x.dtype != torch.float32 or not x.is_contiguous() or x.shape[1] != self.F or x.device != self.device:
+            raise WxError("x must be a contiguous fp32 [batch, F] tensor on the engine's device")
+        if y.dtype != torch.int64 or y.shape[0] != b or y.device != self.device:
+            raise WxError("y must be int64 [batch] on the engine's device")
+        if b > self.max_batch:
+            raise WxError(f"batch {b} exceeds max_batch {self.max_batch}")
+        return b
+
+    def loss_and_grads(self, x, y, *, dropout: int = DROPOUT_PHILOX, step: int | None = None, grad_scale=None,
+                       overlap_reduce: bool = False) -> torch.Tensor:
+        """Forward + backward of one batch into self.grads ([P+1], loss at [P]); returns self.grads."""
+        b = self._check_batch(x, y)
+        step = self.steps_done if step is None else step
+        scale = 1.0 / (self.world * b) if grad_scale is None else grad_scale
+        st = self._stream()
+        d = C.byref(self.desc)
+        check(self.lib.wx_wide_forward(self._h, d, self.params.data_ptr(), self.ws.data_ptr(), x.data_ptr(), y.data_ptr(), b,
+                                       dropout, self.seed, step, scale, self.grads.data_ptr(), st))
+        main = torch.cuda.current_stream(self.device)
+        works = []
+
+        def reduce_slice(lo, hi):
+            ev = torch.cuda.Event()
+            ev.record(main)
+            self._side.wait_event(ev)
+            with torch.cuda.stream(self._side):
+                works.append(self.dist.all_reduce(self.grads[lo:hi], async_op=True))
+
+        if overlap_reduce:
+            reduce_slice(*self.head_slice)
+        for layer in range(self.L, 0, -1):
+            check(self.lib.wx_wide_backward_layer(self._h, d, self.ws.data_ptr(), b, layer, dropout, self.grads.data_ptr(), st))
+            if overlap_reduce:
+                reduce_slice(*self.slices[layer - 1])
+        if overlap_reduce:
+            for w in works:
+                w.wait()
+            main.wait_stream(self._side)
+        return self.grads
+
+    def step(self, x, y, *, dropout: int = DROPOUT_PHILOX) -> torch.Tensor:
+        """One optimizer step; returns the device scalar train_loss (rank mean)."""
+        self.loss_and_grads(x, y, dropout=dropout, overlap_reduce=self.world > 1)
+        self.steps_done += 1
+        check(self.lib.wx_wide_adam(self._h, C.byref(self.desc), self.params.data_ptr(), self.grads.data_ptr(),
+                                    self.m.data_ptr(), self.v.data_ptr(), self.steps_done, self.ws.data_ptr(), self._stream()))
+        return self.grads[self.P:self.P + 1]
+
+    def gemm(self, a: torch.Tensor, b: torch.Tensor, a_kmajor: bool, b_kmajor: bool, bias=None) -> torch.Tensor:
+        """Test hook for wx_wide_gemm: bf16 row-major operands, fp32 result [M, N]."""
+        m, k = (a.shape if a_kmajor else (a.shape[1], a.shape[0]))
+        n = b.shape[0] if b_kmajor else b.shape[1]
+        out = torch.empty(m, n, dtype=torch.float32, device=self.device)
+        check(self.lib.wx_wide_gemm(self._h, int(a_kmajor), int(b_kmajor), a.data_ptr(), a.stride(0), b.data_ptr(),
+                                    b.stride(0), m, n, k, bias.data_ptr() if bias is not None else None, out.data_ptr(),
+                                    self._stream()))
+        return out

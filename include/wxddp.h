@@ -234,6 +234,50 @@ int wx_mlp_eval(wx_ctx* ctx, const float* params, const float* x, const int64_t*
 int wx_mlp_predict(wx_ctx* ctx, const float* params, const float* x, int64_t n, float* probs_out,
                    void* stream);
 
+/* ---- wide tabular MLP on bf16 tcgen05 GEMMs (BASELINE.json configs[3]; SURVEY 8(b) "wx_wide_mlp_fwd/bwd") ----------
+ * No counterpart in the reference, whose only model is Linear(F,64)-ReLU-Dropout-Linear(64,2)
+ * (jobs/train_lightning_ddp.py:57-62).  Same layer pattern widened: n_hidden x [Linear, ReLU, Dropout(p)] then
+ * Linear(hidden, 2), CE loss (:69), Adam (:88).  Parameters are ONE flat fp32 vector in torch module order
+ * (W_1 [H,F], b_1 [H], W_2 [H,H], b_2 [H], ..., W_o [2,H], b_o [2]); gradients use the same layout plus one extra
+ * element [P] for the loss, so the DDP exchange (:136) is a SUM all-reduce of (slices of) one buffer.
+ * Hidden-layer products run in bf16 with fp32 accumulation (activations and dZ are stored as bf16); the head, the loss,
+ * bias gradients and Adam are fp32.  All buffers are caller-owned device memory; `ws` is a caller-allocated workspace of
+ * wx_wide_workspace_bytes() bytes (1024-byte aligned) that carries the bf16 weight copies between calls.
+ * Constraints: hidden % 256 == 0, n_features <= 64, classes == 2, batch % 128 == 0. */
+typedef struct wx_wide_desc {
+    int32_t n_features; /* F */
+    int32_t hidden;     /* H */
+    int32_t n_hidden;   /* number of hidden layers; "4 layers, hidden 4096" = 3 hidden + the head */
+    int32_t classes;    /* 2 */
+    float dropout_p;
+    double lr, beta1, beta2, eps;
+} wx_wide_desc;
+
+int64_t wx_wide_n_params(const wx_wide_desc* desc);                      /* P, or -1 (see wx_last_error) */
+int64_t wx_wide_workspace_bytes(const wx_wide_desc* desc, int64_t batch); /* bytes, or -1 */
+/* (Re)build the bf16 copies of the hidden weights inside ws from the fp32 parameters (once after init / load). */
+int wx_wide_cast_weights(wx_ctx* ctx, const wx_wide_desc* desc, const float* params, void* ws, void* stream);
+/* Forward + loss + head gradients: x fp32 [batch,F] row-major standardised features (wx_normalize_pack output),
+ * y int64 [batch].  grads fp32 [P+1] receives dW_o, db_o and, at [P], sum(CE) * grad_scale; grad_scale is normally
+ * 1/(world*batch).  dropout_mode: WX_DROPOUT_OFF or WX_DROPOUT_PHILOX (keep <=> 16 Philox4x32-10 bits <
+ * round((1-p)*65536); counter (row, col/8, layer, step), key = seed). */
+int wx_wide_forward(wx_ctx* ctx, const wx_wide_desc* desc, const float* params, void* ws, const float* x,
+                    const int64_t* y, int64_t batch, int dropout_mode, uint64_t seed, uint64_t step, float grad_scale,
+                    float* grads, void* stream);
+/* Backward of hidden layer `layer` = n_hidden, ..., 1 (in that order, after wx_wide_forward): dW_layer and db_layer into
+ * grads; the caller may start reducing that slice across ranks while the next layer's backward runs. */
+int wx_wide_backward_layer(wx_ctx* ctx, const wx_wide_desc* desc, void* ws, int64_t batch, int layer, int dropout_mode,
+                           float* grads, void* stream);
+/* Adam over all P parameters (step is 1-based), rewriting the bf16 weight copies in ws in the same pass. */
+int wx_wide_adam(wx_ctx* ctx, const wx_wide_desc* desc, float* params, const float* grads, float* m, float* v,
+                 int64_t step, void* ws, void* stream);
+/* The GEMM underneath, exposed for tests: out fp32 [M,N] = op(A) op(B) (+ bias[N]); A is [M,K] (a_kmajor) or [K,M],
+ * B is [N,K] (b_kmajor) or [K,N], row-major bf16 with pitches lda/ldb in elements.  N % 16 == 0, K % 64 == 0.
+ * Supported layout pairs: (1,1), (1,0), (0,0) -- the three the wide MLP uses. */
+int wx_wide_gemm(wx_ctx* ctx, int a_kmajor, int b_kmajor, const void* A, int64_t lda, const void* B, int64_t ldb,
+                 int64_t M, int64_t N, int64_t K, const float* bias, float* out, void* stream);
+
+
 #ifdef __cplusplus
 }
 #endif
