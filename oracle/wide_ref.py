@@ -66,7 +66,7 @@ def _r(t: torch.Tensor, on: bool) -> torch.Tensor:
 
 def loss_and_grads(flat: torch.Tensor, x: torch.Tensor, y: torch.Tensor, f: int, h: int, n_hidden: int, *,
                    p_drop: float = 0.2, dropout: bool = True, seed: int = 42, step: int = 0, grad_scale=None,
-                   emulate_bf16: bool = True, masks=None):
+                   emulate_bf16: bool = True, masks=None, intermediates: dict | None = None):
     """Manual forward/backward in the CUDA path's operation order.  Returns (loss*scale*B... see below, grads [P+1]).
 
     grads[P] = sum_rows(CE) * grad_scale, like the kernels' bucket (grad_scale defaults to 1/B -> mean loss)."""
@@ -98,11 +98,15 @@ def loss_and_grads(flat: torch.Tensor, x: torch.Tensor, y: torch.Tensor, f: int,
     g_layers[n_hidden][1].copy_(dlog.sum(0))
     grads[-1] = ce.sum() * scale
     dz = _r((dlog @ wo) * (hs[-1] > 0) * float(inv_keep), e)
+    if intermediates is not None:
+        intermediates.update(hs=hs, dlog=dlog, dz={n_hidden: dz})
     for l in range(n_hidden - 1, -1, -1):
         g_layers[l][0].copy_(dz.t() @ hs[l])
         g_layers[l][1].copy_(dz.sum(0))
         if l > 0:
             dz = _r((dz @ _r(layers[l][0], e)) * (hs[l] > 0) * float(inv_keep), e)
+            if intermediates is not None:
+                intermediates["dz"][l] = dz
     return grads
 
 

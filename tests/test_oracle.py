@@ -168,3 +168,56 @@ def test_sampler_restatement_matches_torch_distributed_sampler():
                 assert list(iter(smp)) == train_ref.epoch_indices(1003, epoch, rank, world)
             smp = DistributedSampler(ds, num_replicas=world, rank=rank, shuffle=False)
             assert list(iter(smp)) == train_ref.val_indices_for_rank(1003, rank, world)
+
+
+# ---------------------------------------------------------------------------------------------
+# wide-MLP oracle (oracle/wide_ref.py): pinned through the narrow model and through autograd
+# ---------------------------------------------------------------------------------------------
+def test_wide_oracle_reduces_to_the_reference_model():
+    """hidden=64, one hidden layer, no bf16 rounding: wide_ref IS the reference's net (train_lightning_ddp.py:57-69),
+    so it must reproduce train_ref (itself pinned by the golden vectors of the reference module)."""
+    import torch
+    from oracle import train_ref, wide_ref
+
+    f, b = 5, 96
+    torch.manual_seed(3)
+    flat = wide_ref.init_params(f, 64, 1)
+    assert flat.numel() == train_ref.n_params(f) == wide_ref.n_params(f, 64, 1)
+    x, y = torch.randn(b, f), (torch.rand(b) < 0.4).long()
+    mask = (torch.rand(b, 64) < 0.8)
+    loss, g = train_ref.loss_and_grads(flat, f, x, y, mask.float())
+    got = wide_ref.loss_and_grads(flat, x, y, f, 64, 1, dropout=True, emulate_bf16=False, masks=[mask])
+    np.testing.assert_allclose(float(got[-1]), float(loss), rtol=1e-6)
+    np.testing.assert_allclose(got[:-1].numpy(), g.numpy(), rtol=2e-5, atol=1e-8)
+
+
+def test_wide_oracle_manual_backward_matches_autograd():
+    import torch
+    from oracle import wide_ref
+
+    f, h, nl, b = 20, 128, 3, 64
+    torch.manual_seed(5)
+    flat = wide_ref.init_params(f, h, nl)
+    x, y = torch.randn(b, f), (torch.rand(b) < 0.3).long()
+    masks = [torch.from_numpy(wide_ref.keep_mask(42, 7, l + 1, b, h, 0.2)) for l in range(nl)]
+    got = wide_ref.loss_and_grads(flat, x, y, f, h, nl, dropout=True, seed=42, step=7, emulate_bf16=False)
+    want = wide_ref.torch_autograd_grads(flat, x, y, f, h, nl, masks)
+    np.testing.assert_allclose(got.numpy(), want.numpy(), rtol=2e-4, atol=1e-8)
+    # the bf16-rounded variant stays close to fp32 (this is the tolerance the CUDA path is held to against fp32)
+    e = wide_ref.loss_and_grads(flat, x, y, f, h, nl, dropout=True, seed=42, step=7, emulate_bf16=True)
+    assert abs(float(e[-1]) - float(want[-1])) < 2e-2 * abs(float(want[-1]))
+    cos = float(torch.dot(e[:-1], want[:-1]) / (e[:-1].norm() * want[:-1].norm()))
+    assert cos > 0.999
+
+
+def test_wide_keep_mask_contract():
+    from oracle import philox_ref, wide_ref
+
+    m = wide_ref.keep_mask(42, 3, 2, 64, 256, 0.2)
+    assert m.shape == (64, 256) and abs(m.mean() - 0.8) < 0.01
+    # element (row 5, col 19): counter (5, 19 // 8, layer, step); e = 3 -> word 1, high half
+    w = philox_ref.philox4x32_10(np.uint32(5), np.uint32(2), np.uint32(2), np.uint32(3), 42, 0)
+    bits = (int(w[1]) >> 16) & 0xFFFF
+    assert bool(m[5, 19]) == (bits < 52429)
+    assert not np.array_equal(m, wide_ref.keep_mask(42, 4, 2, 64, 256, 0.2))
+    assert wide_ref.keep_mask(42, 3, 2, 8, 64, 0.0).all()
