@@ -153,6 +153,159 @@ def workload_config(args, rows_per_gpu: int) -> dict:
             "parallelism": f"dp{args.gpus}"}
 
 
+def read_tensor_peak():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        with open(path) as fh:
+            d = json.load(fh)
+        if "bf16_tflops_sustained" in d:
+            return float(d["bf16_tflops_sustained"]), "measured (MEASURED_PEAKS.json bf16_tflops_sustained: step of back-to-back GEMMs)"
+    return 1416.4, "fallback (B200_PROFILING.md sustained cuBLAS bf16)"
+
+
+def wide_config(args, hidden: int, rows: int) -> dict:
+    return {"workload": f"wide tabular MLP {args.features}->{hidden}x3->2 (4 layers, hidden {hidden}; BASELINE.json "
+                        f"configs[3]), bf16 tcgen05 GEMMs with fp32 accumulate, fp32 head/loss/Adam: forward + CE + "
+                        f"backward + DDP mean + Adam per step; {rows} rows/step/GPU",
+            "features": args.features, "hidden": hidden, "layers": 4, "rows_per_step_per_gpu": rows,
+            "dropout": "philox p=0.2", "optimizer": "Adam lr=0.01 (fp32 master weights, bf16 copies re-emitted)",
+            "l2_policy": "working set per step (activations + weights, > 1 GB) is far larger than the 126 MB L2",
+            "parallelism": f"dp{args.gpus}"}
+
+
+def run_wide(args, rank: int, local_rank: int, world: int) -> int:
+    """BASELINE.json configs[3]: same JSON contract, tensor-pipe roofline."""
+    f, hidden, nl, B = args.features, args.wide_hidden, 3, args.wide_rows
+    weights = f * hidden + (nl - 1) * hidden * hidden + 2 * hidden
+    flops_per_row = 6.0 * weights - 2.0 * f * hidden            # SURVEY 8(d): no dX for the first layer
+    if args.impl == "reference":
+        if rank != 0:
+            return 0
+        from oracle import wide_ref
+        rows = min(B, 1024)
+        r = wide_ref.time_cpu_steps(f, hidden, nl, rows, max(1, min(args.steps, 6)), warmup=1)
+        line = {"impl": "reference", "metric": METRIC, "value": r["samples_per_sec"], "unit": UNIT, "n_gpus": args.gpus,
+                "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * r["seconds"] / max(1, min(args.steps, 6)),
+                "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+                "config": wide_config(args, hidden, B),
+                "cpu_baseline": {"value": r["samples_per_sec"], "unit": UNIT, "cores": r["cores"], "kind": "port",
+                                 "sample": f"{max(1, min(args.steps, 6))} steps x {rows} rows, torch fp32 nn.Sequential + "
+                                           f"autograd + torch.optim.Adam on the host cores ({r['seconds']:.1f} s)"},
+                "e2e": {"value": r["samples_per_sec"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+                "gpu_launches": 0}
+        print(json.dumps(line), flush=True)
+        return 0
+
+    import torch
+
+    from wxddp.wide import WideEngine
+
+    if args.warmup < 3:
+        args.warmup = 3
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a B200: wxddp has no CPU path (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local_rank)
+    device = torch.device("cuda", local_rank)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=device)
+    torch.manual_seed(42)
+    eng = WideEngine(f, hidden, nl, max_batch=B, device=device, world=world, rank=rank, process_group=dist,
+                     seed=42 + 1000 * rank)
+    n_win = 8
+    g = torch.Generator(device=device)
+    g.manual_seed(1234 + rank)
+    table = torch.randn(n_win * B, f, device=device, generator=g)           # standardised features (K1's output)
+    labels = (torch.rand(n_win * B, device=device, generator=g) < 0.3).to(torch.int64)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    step_no = [0]
+
+    def one_step():
+        w = step_no[0] % n_win
+        eng.step(table[w * B:(w + 1) * B], labels[w * B:(w + 1) * B])
+        step_no[0] += 1
+
+    for _ in range(args.warmup):
+        one_step()
+    barrier()
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    l0 = eng.launch_count
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    ev0.record()
+    for _ in range(args.steps):
+        one_step()
+    ev1.record()
+    barrier()
+    ms = ev0.elapsed_time(ev1)
+    launches = eng.launch_count - l0
+    clocks = sampler.stop() if rank == 0 else None
+    t = torch.tensor([ms], dtype=torch.float64, device=device)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t.item())
+    final_loss = float(eng.grads[eng.P].item())
+    status = eng.status()
+
+    e2e = None
+    if not args.no_e2e:
+        hx = [table[i * B:(i + 1) * B].cpu().pin_memory() for i in range(4)]
+        hy = [labels[i * B:(i + 1) * B].cpu().pin_memory() for i in range(4)]
+        for i in range(3):
+            eng.step_host(hx[i % 4], hy[i % 4])
+        barrier()
+        t0 = time.perf_counter()
+        for i in range(args.steps):
+            last = eng.step_host(hx[i % 4], hy[i % 4])
+        barrier()
+        dt = time.perf_counter() - t0
+        tt = torch.tensor([dt], dtype=torch.float64, device=device)
+        if world > 1:
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        dt = float(tt.item())
+        e2e = {"value": args.steps * B * world / dt, "unit": UNIT, "h2d_bytes_per_step": B * (4 * f + 8),
+               "d2h_bytes_per_step": 4, "ms_per_step": 1e3 * dt / args.steps, "last_loss": last,
+               "api": "wxddp.wide.WideEngine.step_host(pinned fp32 features, int64 labels) -> loss"}
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return 0
+    peak, peak_src = read_tensor_peak()
+    step_s = (ms / 1e3) / args.steps
+    achieved = B * flops_per_row / step_s / 1e12
+    roof = {"bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak,
+            "traffic": None, "kernel": "wide_gemm_kernel (tcgen05.mma kind::f16, 128x256x64 tiles, TMA 128B-swizzle "
+                                       "tensor maps, TMEM double buffer): 8 launches per step, ~90% of the step",
+            "peak_source": peak_src, "algorithmic_flops_per_row": flops_per_row,
+            "note": "achieved = algorithmic FLOPs of the whole step / step time, i.e. it charges the head, bias-gradient, "
+                    "cast and Adam kernels and the DDP exchange to the GEMMs"}
+    line = {"metric": METRIC, "value": args.steps * B * world / (ms / 1e3), "unit": UNIT, "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+            "config": wide_config(args, hidden, B), "roofline": roof, "clocks": clocks, "gpu_launches": int(launches),
+            "final_loss": final_loss, "kernel_status": status}
+    if e2e is not None:
+        line["e2e"] = e2e
+    if not args.no_cpu_baseline and world == 1:
+        from oracle import wide_ref
+        r = wide_ref.time_cpu_steps(f, hidden, nl, 1024, 4, warmup=1)
+        line["cpu_baseline"] = {"value": r["samples_per_sec"], "unit": UNIT, "cores": r["cores"], "kind": "port",
+                                "sample": f"4 steps x 1024 rows, torch fp32 nn.Sequential + autograd + torch.optim.Adam "
+                                          f"on the host cores ({r['seconds']:.1f} s)"}
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
 def main() -> int:
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -168,12 +321,19 @@ def main() -> int:
     ap.add_argument("--kernel", default="auto", choices=["auto", "tc", "ffma"], help="step kernel at N=1")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--workload", default="weather", choices=["weather", "wide"],
+                    help="weather = BASELINE.json configs[1] (default, the headline); wide = configs[3], the 4-layer "
+                         "hidden-4096 bf16 tcgen05 MLP")
+    ap.add_argument("--wide-rows", type=int, default=16384, help="rows/step/GPU of the wide workload")
+    ap.add_argument("--wide-hidden", type=int, default=4096)
     args = ap.parse_args()
 
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
 
+    if args.workload == "wide":
+        return run_wide(args, rank, local_rank, world)
     if args.impl == "reference":
         return run_reference(args, rank)
 

@@ -140,6 +140,21 @@ class WideEngine:
                                     self.m.data_ptr(), self.v.data_ptr(), self.steps_done, self.ws.data_ptr(), self._stream()))
         return self.grads[self.P:self.P + 1]
 
+    def step_host(self, x_host: torch.Tensor, y_host: torch.Tensor) -> float:
+        """End-to-end step from HOST buffers (pinned memory recommended): H2D of the fp32 [batch, F] features and int64
+        labels, the step, and a D2H read of the loss."""
+        b = x_host.shape[0]
+        if getattr(self, "_stage", None) is None or self._stage[0].shape[0] != b:
+            self._stage = (torch.empty(b, self.F, dtype=torch.float32, device=self.device),
+                           torch.empty(b, dtype=torch.int64, device=self.device), torch.zeros(1).pin_memory())
+        dx, dy, hl = self._stage
+        dx.copy_(x_host, non_blocking=True)
+        dy.copy_(y_host, non_blocking=True)
+        loss = self.step(dx, dy)
+        hl.copy_(loss, non_blocking=True)
+        torch.cuda.current_stream(self.device).synchronize()
+        return float(hl.item())
+
     def gemm(self, a: torch.Tensor, b: torch.Tensor, a_kmajor: bool, b_kmajor: bool, bias=None) -> torch.Tensor:
         """Test hook for wx_wide_gemm: bf16 row-major operands, fp32 result [M, N]."""
         m, k = (a.shape if a_kmajor else (a.shape[1], a.shape[0]))

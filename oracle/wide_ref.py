@@ -124,3 +124,35 @@ def torch_autograd_grads(flat: torch.Tensor, x: torch.Tensor, y: torch.Tensor, f
     loss = torch.nn.functional.cross_entropy(logits, y)
     loss.backward()
     return torch.cat([p.grad, loss.detach().view(1)])
+
+
+def time_cpu_steps(f: int, h: int, n_hidden: int, batch: int, steps: int, warmup: int = 1, threads: int | None = None):
+    """The same net as plain torch modules (nn.Sequential of Linear/ReLU/Dropout(0.2) + CE + torch.optim.Adam(lr=0.01),
+    the reference's recipe at train_lightning_ddp.py:57-62,:69,:88 widened) timed on the host cores, fp32."""
+    import time
+    from torch import nn
+    if threads:
+        torch.set_num_threads(threads)
+    torch.manual_seed(42)
+    mods, d = [], f
+    for _ in range(n_hidden):
+        mods += [nn.Linear(d, h), nn.ReLU(), nn.Dropout(0.2)]
+        d = h
+    mods.append(nn.Linear(d, 2))
+    net = nn.Sequential(*mods)
+    opt = torch.optim.Adam(net.parameters(), lr=0.01)
+    x = torch.randn(batch, f)
+    y = (torch.rand(batch) < 0.3).long()
+    def one():
+        opt.zero_grad(set_to_none=True)
+        loss = torch.nn.functional.cross_entropy(net(x), y)
+        loss.backward()
+        opt.step()
+        return float(loss.detach())
+    for _ in range(warmup):
+        one()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        last = one()
+    dt = time.perf_counter() - t0
+    return {"samples_per_sec": steps * batch / dt, "seconds": dt, "cores": torch.get_num_threads(), "last_loss": last}

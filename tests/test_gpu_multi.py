@@ -128,3 +128,59 @@ def test_in_kernel_peer_allreduce_matches_nccl_bucket_path(world):
         np.testing.assert_allclose(res["peer"][1], res["nccl"][1], rtol=1e-4, atol=1e-6)   # parameters after 6 Adam steps
     np.testing.assert_array_equal(out[0][1]["peer"][1], out[1][1]["peer"][1])              # replicas bit-identical
     np.testing.assert_allclose(out[0][1]["peer"][0], out[1][1]["peer"][0], rtol=0, atol=0)
+
+
+def _wide_worker(rank, world, port, q):
+    """Wide MLP under DDP: per-layer all-reduce overlapped with backward vs one all-reduce at the end; replicas equal;
+    the reduced gradient equals the oracle's gradient of the concatenated batch (dropout off: masks are per-rank)."""
+    import torch.distributed as dist
+
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    from wxddp.wide import WideEngine
+
+    f, h, nl, b = 20, 256, 2, 256
+    torch.manual_seed(42)
+    eng = WideEngine(f, h, nl, max_batch=b, device=rank, world=world, rank=rank, process_group=dist)
+    g = torch.Generator().manual_seed(100)
+    x_all = torch.randn(world * b, f, generator=g)
+    y_all = (torch.rand(world * b, generator=g) < 0.3).long()
+    x, y = x_all[rank * b:(rank + 1) * b].cuda(), y_all[rank * b:(rank + 1) * b].cuda()
+    p0 = eng.params.cpu().clone()
+    g_overlap = eng.loss_and_grads(x, y, dropout=0, overlap_reduce=True).clone()
+    g_local = eng.loss_and_grads(x, y, dropout=0, overlap_reduce=False).clone()
+    dist.all_reduce(g_local)
+    losses = [float(eng.step(x, y).item()) for _ in range(3)]
+    q.put((rank, p0.numpy(), g_overlap.cpu().numpy(), g_local.cpu().numpy(), losses, eng.params.cpu().numpy(),
+           x_all.numpy(), y_all.numpy(), eng.status()))
+    dist.destroy_process_group()
+
+
+def test_wide_ddp_overlapped_reduce():
+    _need(2)
+    import torch.multiprocessing as mp
+    from oracle import wide_ref
+
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_wide_worker, args=(r, 2, 29681, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = sorted([q.get(timeout=600) for _ in range(2)], key=lambda r: r[0])
+    for p in procs:
+        p.join(timeout=120)
+        assert p.exitcode == 0
+    (r0, r1) = res
+    assert r0[8] == 0 and r1[8] == 0
+    np.testing.assert_array_equal(r0[1], r1[1])                      # broadcast initial parameters
+    np.testing.assert_array_equal(r0[2], r0[3])                      # overlapped == reduce-at-the-end, bit for bit
+    np.testing.assert_array_equal(r0[2], r1[2])                      # every rank holds the same reduced bucket
+    np.testing.assert_array_equal(r0[5], r1[5])                      # replicas stay identical after 3 steps
+    assert r0[4] == r1[4]
+    want = wide_ref.loss_and_grads(torch.from_numpy(r0[1]), torch.from_numpy(r0[6]), torch.from_numpy(r0[7]), 20, 256, 2,
+                                   dropout=False)
+    got = torch.from_numpy(r0[2])
+    np.testing.assert_allclose(float(got[-1]), float(want[-1]), rtol=1e-4)
+    assert float((got[:-1] - want[:-1]).norm() / want[:-1].norm()) < 1e-3 + 1.5 / 512
