@@ -34,8 +34,9 @@ __device__ __forceinline__ void adam_one(float& p, float g, float& m, float& v, 
 }
 
 constexpr int KPAD = 64;          // the first layer's contraction length, zero padded (F <= 64)
-constexpr int COLSUM_SLABS = 64;
-constexpr int HEAD_SLABS = 64;
+constexpr int COLSUM_SLABS = 128;
+constexpr int HEAD_SLABS = 128;
+constexpr int MAX_SPLIT_K = 8;
 
 struct Layout {
     int64_t P;                    // number of fp32 parameters
@@ -82,7 +83,7 @@ int make_layout(const wx_wide_desc* d, int64_t batch, Layout* L) {
     L->part = w;   // partial sums: max(colsum: SLABS x H, head: SLABS x (2H), head rows: grid x 4)
     w = align_up(w + size_t(HEAD_SLABS) * 2 * H * 4 + size_t(4096) * 4 * 4);
     L->dw1tmp = w;
-    w = align_up(w + size_t(H) * KPAD * 4);
+    w = align_up(w + size_t(MAX_SPLIT_K) * H * KPAD * 4);
     L->total = w;
     return 0;
 }
@@ -204,24 +205,34 @@ __global__ void __launch_bounds__(256) wide_head_bwd_kernel(const __nv_bfloat16*
         a0[i] = 0.0f;
         a1[i] = 0.0f;
     }
-    for (int64_t r = r0; r < r1; ++r) {
-        const float2 dl = __ldg(reinterpret_cast<const float2*>(dlog) + r);
-        const uint4 hv = __ldg(reinterpret_cast<const uint4*>(h + r * H) + c8);
-        float f[8], o[8];
-        unpack8(hv, f);
+    for (int64_t rb = r0; rb < r1; rb += 4) {
+        float2 dl[4];
+        uint4 hv[4];
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
-            a0[i] = fmaf(dl.x, f[i], a0[i]);
-            a1[i] = fmaf(dl.y, f[i], a1[i]);
-            const float dh = fmaf(dl.x, w0[i], dl.y * w1[i]);
-            o[i] = f[i] > 0.0f ? dh * inv_keep : 0.0f;
+        for (int u = 0; u < 4; ++u) {                      // 4 independent rows in flight
+            const int64_t r = (rb + u < r1) ? rb + u : r1 - 1;
+            dl[u] = __ldg(reinterpret_cast<const float2*>(dlog) + r);
+            hv[u] = __ldg(reinterpret_cast<const uint4*>(h + r * H) + c8);
         }
-        uint4 ov;
-        ov.x = pack_bf16(o[0], o[1]);
-        ov.y = pack_bf16(o[2], o[3]);
-        ov.z = pack_bf16(o[4], o[5]);
-        ov.w = pack_bf16(o[6], o[7]);
-        reinterpret_cast<uint4*>(dz + r * H)[c8] = ov;
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            if (rb + u >= r1) break;
+            float f[8], o[8];
+            unpack8(hv[u], f);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                a0[i] = fmaf(dl[u].x, f[i], a0[i]);
+                a1[i] = fmaf(dl[u].y, f[i], a1[i]);
+                const float dh = fmaf(dl[u].x, w0[i], dl[u].y * w1[i]);
+                o[i] = f[i] > 0.0f ? dh * inv_keep : 0.0f;
+            }
+            uint4 ov;
+            ov.x = pack_bf16(o[0], o[1]);
+            ov.y = pack_bf16(o[2], o[3]);
+            ov.z = pack_bf16(o[4], o[5]);
+            ov.w = pack_bf16(o[6], o[7]);
+            reinterpret_cast<uint4*>(dz + (rb + u) * H)[c8] = ov;
+        }
     }
     float* p = part + size_t(blockIdx.y) * 2 * H;
 #pragma unroll
@@ -239,11 +250,21 @@ __global__ void __launch_bounds__(256) wide_colsum_kernel(const __nv_bfloat16* _
     const int64_t rows_per = (batch + gridDim.y - 1) / gridDim.y;
     const int64_t r0 = int64_t(blockIdx.y) * rows_per, r1 = (r0 + rows_per < batch) ? r0 + rows_per : batch;
     float a[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-    for (int64_t r = r0; r < r1; ++r) {
-        float f[8];
-        unpack8(__ldg(reinterpret_cast<const uint4*>(dz + r * H) + c8), f);
+    for (int64_t rb = r0; rb < r1; rb += 4) {
+        uint4 hv[4];
 #pragma unroll
-        for (int i = 0; i < 8; ++i) a[i] += f[i];
+        for (int u = 0; u < 4; ++u) {
+            const int64_t r = (rb + u < r1) ? rb + u : r1 - 1;
+            hv[u] = __ldg(reinterpret_cast<const uint4*>(dz + r * H) + c8);
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            if (rb + u >= r1) break;
+            float f[8];
+            unpack8(hv[u], f);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) a[i] += f[i];
+        }
     }
     float* p = part + size_t(blockIdx.y) * H;
 #pragma unroll
@@ -261,23 +282,39 @@ __global__ void __launch_bounds__(256) wide_reduce_kernel(const float* __restric
 }
 
 // head partials [n_parts][4] = (loss, db0, db1, -) -> grads[off_b_out .. +2] and grads[P]
-__global__ void wide_head_finish_kernel(const float* __restrict__ part, int n_parts, float* __restrict__ db_out,
-                                        float* __restrict__ loss_out) {
+__global__ void __launch_bounds__(256) wide_head_finish_kernel(const float* __restrict__ part, int n_parts,
+                                                              float* __restrict__ db_out, float* __restrict__ loss_out) {
+    __shared__ float sh[256][3];
     const int t = threadIdx.x;
-    if (t >= 3) return;
-    float s = 0.0f;
-    for (int p = 0; p < n_parts; ++p) s += part[p * 4 + t];
-    if (t == 0) *loss_out = s;
-    else db_out[t - 1] = s;
+    float s[3] = {0.0f, 0.0f, 0.0f};
+    for (int p = t; p < n_parts; p += 256) {               // fixed assignment + fixed tree: deterministic
+        const float4 v = __ldg(reinterpret_cast<const float4*>(part) + p);
+        s[0] += v.x; s[1] += v.y; s[2] += v.z;
+    }
+    sh[t][0] = s[0]; sh[t][1] = s[1]; sh[t][2] = s[2];
+    __syncthreads();
+    for (int o = 128; o > 0; o >>= 1) {
+        if (t < o) {
+            sh[t][0] += sh[t + o][0]; sh[t][1] += sh[t + o][1]; sh[t][2] += sh[t + o][2];
+        }
+        __syncthreads();
+    }
+    if (t == 0) {
+        *loss_out = sh[0][0];
+        db_out[0] = sh[0][1];
+        db_out[1] = sh[0][2];
+    }
 }
 
-// [H, 64] fp32 -> [H, F] fp32 (first layer's weight gradient without the padding columns)
+// [splits][H, 64] fp32 -> [H, F] fp32: sums the split-K slabs of the first layer's weight gradient and drops the padding
 __global__ void __launch_bounds__(256) unpad_kernel(const float* __restrict__ src, int64_t rows, int in, int pad,
-                                                   float* __restrict__ dst) {
+                                                   int splits, float* __restrict__ dst) {
     const int64_t total = rows * in;
     for (int64_t i = int64_t(blockIdx.x) * blockDim.x + threadIdx.x; i < total; i += int64_t(gridDim.x) * blockDim.x) {
         const int64_t r = i / in;
-        dst[i] = src[r * pad + (i - r * in)];
+        float t = 0.0f;
+        for (int s = 0; s < splits; ++s) t += src[(size_t(s) * rows + r) * pad + (i - r * in)];   // split-K slabs, in order
+        dst[i] = t;
     }
 }
 
@@ -341,20 +378,23 @@ encode_fn_t get_encode() {
     return fn;
 }
 
-// bf16 row-major [rows, cols] (pitch in elements); box = 64 columns x box_rows rows, 128-byte swizzle
-int make_map(CUtensorMap* tm, const void* base, int64_t rows, int64_t cols, int64_t pitch, int box_rows) {
+// bf16 row-major [rows, cols] (pitch in elements), 128-byte swizzle.
+//   K-major operand (mn_groups == 0): 2-D map, box = 64 columns x box_rows rows.
+//   MN-major operand: 3-D map (64 columns, all rows, cols/64 column groups), box = 64 x 64 x mn_groups -- one op drops
+//   mn_groups consecutive 8 KiB atoms (64 k-lines of 64 M|N elements) into shared memory.
+int make_map(CUtensorMap* tm, const void* base, int64_t rows, int64_t cols, int64_t pitch, int box_rows, int mn_groups = 0) {
     encode_fn_t enc = get_encode();
     if (enc == nullptr) {
         wx_set_error("cuTensorMapEncodeTiled is not available from this driver");
         return WX_ECUDA;
     }
-    const cuuint64_t dims[2] = {cuuint64_t(cols), cuuint64_t(rows)};
-    const cuuint64_t strides[1] = {cuuint64_t(pitch) * 2};
-    const cuuint32_t box[2] = {64u, cuuint32_t(box_rows)};
-    const cuuint32_t estr[2] = {1u, 1u};
-    const CUresult r = enc(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
-                           CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                           CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    const cuuint64_t dims[3] = {mn_groups ? 64u : cuuint64_t(cols), cuuint64_t(rows), cuuint64_t(cols / 64)};
+    const cuuint64_t strides[2] = {cuuint64_t(pitch) * 2, 128u};
+    const cuuint32_t box[3] = {64u, cuuint32_t(box_rows), cuuint32_t(mn_groups)};
+    const cuuint32_t estr[3] = {1u, 1u, 1u};
+    const CUresult r = enc(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, mn_groups ? 3 : 2, const_cast<void*>(base), dims, strides,
+                           box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                           CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) {
         wx_set_error("cuTensorMapEncodeTiled failed with CUresult %d (base %p, %lld x %lld, pitch %lld)", int(r), base,
                      (long long)rows, (long long)cols, (long long)pitch);
@@ -371,7 +411,7 @@ int launch_gemm_t(wx_ctx* ctx, const CUtensorMap& ta, const CUtensorMap& tb, con
                                      int(GEMM_SMEM)));
         attr_set[ctx->device & 63] = true;
     }
-    const int64_t tiles = ((g.M + BM - 1) / BM) * ((g.N + BN - 1) / BN);
+    const int64_t tiles = ((g.M + BM - 1) / BM) * ((g.N + BN - 1) / BN) * g.split_k;
     const int grid = int(tiles < ctx->num_sms ? tiles : ctx->num_sms);
     wide_gemm_kernel<A_K, B_K, EPI><<<grid, GEMM_THREADS, GEMM_SMEM, st>>>(ta, tb, g);
     WX_LAUNCH_CHECK(ctx);
@@ -384,12 +424,13 @@ int launch_gemm(wx_ctx* ctx, bool a_k, bool b_k, int epi, const void* A, int64_t
     CUtensorMap ta, tb;
     int rc;
     if (a_k) rc = make_map(&ta, A, g.M, g.K, lda, BM);
-    else rc = make_map(&ta, A, g.K, g.M, lda, 64);
+    else rc = make_map(&ta, A, g.K, g.M, lda, 64, BM / 64);
     if (rc != WX_OK) return rc;
     if (b_k) rc = make_map(&tb, B, g.N, g.K, ldb, BN);
-    else rc = make_map(&tb, B, g.K, g.N, ldb, 64);
+    else rc = make_map(&tb, B, g.K, g.N, ldb, 64, BN / 64);
     if (rc != WX_OK) return rc;
     g.err = reinterpret_cast<int*>(ctx->scratch) + 8;   // sticky status word (wx_tc_last_status)
+    if (g.split_k < 1) g.split_k = 1;
     if (a_k && b_k) {
         if (epi == EPI_FWD) return launch_gemm_t<true, true, EPI_FWD>(ctx, ta, tb, g, st);
         if (epi == EPI_PLAIN) return launch_gemm_t<true, true, EPI_PLAIN>(ctx, ta, tb, g, st);
@@ -454,6 +495,8 @@ int wx_wide_gemm(wx_ctx* ctx, int a_kmajor, int b_kmajor, const void* A, int64_t
     WX_CHECK_ARG((reinterpret_cast<uintptr_t>(A) | reinterpret_cast<uintptr_t>(B) | reinterpret_cast<uintptr_t>(out)) % 16 == 0 &&
                      lda % 8 == 0 && ldb % 8 == 0,
                  "wx_wide_gemm: operands must be 16-byte aligned with pitches that are multiples of 8 elements");
+    WX_CHECK_ARG((a_kmajor || M % 64 == 0) && (b_kmajor || N % 64 == 0),
+                 "wx_wide_gemm: an operand stored [K, M|N] needs M|N %% 64 == 0");
     WX_CUDA(cudaSetDevice(ctx->device));
     GemmArgs g = {};
     g.M = M; g.N = N; g.K = K;
@@ -533,7 +576,7 @@ int wx_wide_forward(wx_ctx* ctx, const wx_wide_desc* desc, const float* params, 
     wide_head_kernel<<<hgrid, 256, 0, st>>>(hl, batch, int(H), params + L.off_w[nl + 1], params + L.off_b[nl + 1], y,
                                            grad_scale, dlog, head_part);
     WX_LAUNCH_CHECK(ctx);
-    wide_head_finish_kernel<<<1, 32, 0, st>>>(head_part, hgrid, grads + L.off_b[nl + 1], grads + L.P);
+    wide_head_finish_kernel<<<1, 256, 0, st>>>(head_part, hgrid, grads + L.off_b[nl + 1], grads + L.P);
     WX_LAUNCH_CHECK(ctx);
     int slabs = int(batch / 128 < HEAD_SLABS ? batch / 128 : HEAD_SLABS);
     dim3 bg((unsigned)((H / 8 + 255) / 256), (unsigned)slabs);
@@ -573,7 +616,13 @@ int wx_wide_backward_layer(wx_ctx* ctx, const wx_wide_desc* desc, void* ws, int6
         GemmArgs g = {};
         g.M = H; g.N = in; g.K = batch;
         g.inv_keep = 1.0f; g.keep_thresh16 = 65536u;
+        int splits = 1;
         if (layer == 1) {
+            // 32 output tiles cannot fill 148 SMs: cut the batch into split-K ranges, one fp32 slab each (summed by unpad)
+            const int64_t tiles = ((H + BM - 1) / BM);
+            while (splits < MAX_SPLIT_K && tiles * splits * 2 <= ctx->num_sms && batch / 64 / (splits * 2) >= 4) splits *= 2;
+            g.split_k = splits;
+            g.split_stride = H * KPAD;
             g.out = w + L.dw1tmp; g.ldo = KPAD;
         } else {
             g.out = grads + L.off_w[layer]; g.ldo = H;
@@ -582,7 +631,7 @@ int wx_wide_backward_layer(wx_ctx* ctx, const wx_wide_desc* desc, void* ws, int6
         if (rc != WX_OK) return rc;
         if (layer == 1) {
             unpad_kernel<<<grid_for(ctx, H * desc->n_features), 256, 0, st>>>(
-                reinterpret_cast<const float*>(w + L.dw1tmp), H, desc->n_features, KPAD, grads + L.off_w[1]);
+                reinterpret_cast<const float*>(w + L.dw1tmp), H, desc->n_features, KPAD, splits, grads + L.off_w[1]);
             WX_LAUNCH_CHECK(ctx);
         }
     }

@@ -2,11 +2,14 @@
 // accumulation in TMEM.  Not in the reference (its model is 5->64->2, /root/reference/jobs/train_lightning_ddp.py:57-62);
 // this is the "wide-hidden config where the layers are real dense GEMMs" of the north star.
 //
-// One persistent CTA per SM, 192 threads, warp-specialised:
-//   warp 0      TMA producer: 2-D tensor-map loads (128B swizzle) of a 128 x 64 A block and a 256 x 64 B block per stage
-//   warp 1      MMA issuer: 4 x tcgen05.mma.kind::f16 (M128 N256 K16) per stage, tcgen05.commit frees the stage
-//   warps 2..5  epilogue: tcgen05.ld of the finished accumulator (TMEM is double-buffered: 2 x 256 columns, so the
-//               epilogue of tile i overlaps the main loop of tile i+1), fused pointwise work, global stores
+// One persistent CTA per SM, 352 threads, warp-specialised:
+//   warp 0      TMA producer for A, warp 1 TMA producer for B: tensor-map loads (128B swizzle) of a 128 x 64 A block and
+//               a 256 x 64 B block per stage, ONE bulk-tensor op per operand and stage (a 3-D map walks the 64-column
+//               atoms of an MN-major operand)
+//   warp 2      MMA issuer: 4 x tcgen05.mma.kind::f16 (M128 N256 K16) per stage, tcgen05.commit frees the stage
+//   warps 3..10 epilogue: tcgen05.ld of the finished accumulator (TMEM is double-buffered: 2 x 256 columns, so the
+//               epilogue of tile i overlaps the main loop of tile i+1), fused pointwise work, global stores; two warps
+//               per TMEM lane quarter, each taking half of the 256 columns
 // Operand layouts in global memory are all row-major; an operand whose contraction index is the row index (the W of the
 // dX product, both operands of the dW product) is read "MN-major": TMA boxes of 64 x 64 land as the canonical MN-major
 // 128B-swizzle atoms and the UMMA descriptor says so, so no transposed copies of activations or weights exist anywhere.
@@ -23,7 +26,8 @@ namespace wxwide {
 constexpr int BM = 128, BN = 256, BK = 64, STAGES = 4;
 constexpr int A_STAGE_BYTES = BM * BK * 2;   // 16 KiB
 constexpr int B_STAGE_BYTES = BN * BK * 2;   // 32 KiB
-constexpr int GEMM_THREADS = 192;
+constexpr int GEMM_THREADS = 352;
+constexpr int EPI_WARPS = 8;
 constexpr size_t GEMM_SMEM = size_t(STAGES) * (A_STAGE_BYTES + B_STAGE_BYTES) + 1024;   // + alignment slack
 
 enum Epilogue : int {
@@ -35,6 +39,8 @@ enum Epilogue : int {
 
 struct GemmArgs {
     int64_t M, N, K;          // output M x N, contraction length K (multiple of 64)
+    int split_k;              // >= 1: the contraction is cut into this many ranges, one output slab each (EPI_DW / PLAIN)
+    int64_t split_stride;     // elements between the output slabs of consecutive splits
     void* out;
     int64_t ldo;              // output row pitch in elements
     const float* bias;        // [N] or NULL
@@ -67,6 +73,14 @@ __device__ __forceinline__ void tma_load_2d(void* smem_dst, const CUtensorMap* t
     asm volatile(
         "cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
         ::"r"(wxtc::smem_u32(smem_dst)), "l"(tm), "r"(c0), "r"(c1), "r"(wxtc::smem_u32(bar))
+        : "memory");
+}
+
+__device__ __forceinline__ void tma_load_3d(void* smem_dst, const CUtensorMap* tm, int32_t c0, int32_t c1, int32_t c2,
+                                            uint64_t* bar) {
+    asm volatile(
+        "cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
+        ::"r"(wxtc::smem_u32(smem_dst)), "l"(tm), "r"(c0), "r"(c1), "r"(c2), "r"(wxtc::smem_u32(bar))
         : "memory");
 }
 
@@ -108,56 +122,58 @@ wide_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int64_t tiles_m = (g.M + BM - 1) / BM, tiles_n = (g.N + BN - 1) / BN;
-    const int64_t n_tiles = tiles_m * tiles_n;
-    const int kb_count = int(g.K / BK);
+    const int64_t mn_tiles = tiles_m * tiles_n;
+    const int64_t n_tiles = mn_tiles * g.split_k;
+    const int kb_total = int(g.K / BK);
+    const int kb_per = (kb_total + g.split_k - 1) / g.split_k;   // k-blocks per split (the last one may be shorter)
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < STAGES; ++s) {
-            wxtc::mbar_init(&full[s], 1);
+            wxtc::mbar_init(&full[s], 2);      // one arrive.expect_tx from each producer
             wxtc::mbar_init(&empty[s], 1);
         }
         for (int a = 0; a < 2; ++a) {
             wxtc::mbar_init(&tmem_full[a], 1);
-            wxtc::mbar_init(&tmem_empty[a], 4);
+            wxtc::mbar_init(&tmem_empty[a], EPI_WARPS);
         }
         wxtc::fence_mbar_init();
     }
-    if (warp == 0) wxtc::tmem_alloc(&tmem_base_s, 512);
+    if (warp == 2) wxtc::tmem_alloc(&tmem_base_s, 512);
     wxtc::tc_fence_before();
     __syncthreads();
     wxtc::tc_fence_after();
     const uint32_t tmem_base = tmem_base_s;
     bool ok = true;
 
-    if (warp == 0) {
-        // ================= TMA producer =================
+    if (warp < 2) {
+        // ================= TMA producers: warp 0 loads A, warp 1 loads B =================
         if (lane == 0) {
+            const bool is_a = warp == 0;
             uint32_t it = 0;   // running stage counter across tiles
             for (int64_t tile = blockIdx.x; tile < n_tiles && ok; tile += gridDim.x) {
-                const int32_t m0 = int32_t(tile / tiles_n) * BM, n0 = int32_t(tile % tiles_n) * BN;
-                for (int kb = 0; kb < kb_count; ++kb, ++it) {
+                const int64_t mn = tile % mn_tiles;
+                const int split = int(tile / mn_tiles);
+                const int32_t m0 = int32_t(mn / tiles_n) * BM, n0 = int32_t(mn % tiles_n) * BN;
+                const int kb0 = split * kb_per, kb1 = (kb0 + kb_per < kb_total) ? kb0 + kb_per : kb_total;
+                for (int kb = kb0; kb < kb1; ++kb, ++it) {
                     const int s = it % STAGES;
-                    if (it >= STAGES && !wxtc::mbar_wait(&empty[s], ((it / STAGES) - 1) & 1)) { ok = false; break; }
-                    wxtc::mbar_arrive_expect_tx(&full[s], A_STAGE_BYTES + B_STAGE_BYTES);
-                    unsigned char* a = sA + size_t(s) * A_STAGE_BYTES;
-                    unsigned char* b = sB + size_t(s) * B_STAGE_BYTES;
-                    if (A_K) {
-                        tma_load_2d(a, &tmA, kb * BK, m0, &full[s]);
+                    if (it >= STAGES && !wxtc::mbar_wait_hot(&empty[s], ((it / STAGES) - 1) & 1)) { ok = false; break; }
+                    if (is_a) {
+                        wxtc::mbar_arrive_expect_tx(&full[s], A_STAGE_BYTES);
+                        unsigned char* a = sA + size_t(s) * A_STAGE_BYTES;
+                        if (A_K) tma_load_2d(a, &tmA, kb * BK, m0, &full[s]);
+                        else tma_load_3d(a, &tmA, 0, kb * BK, m0 / 64, &full[s]);
                     } else {
-#pragma unroll
-                        for (int h = 0; h < BM / 64; ++h) tma_load_2d(a + h * 8192, &tmA, m0 + h * 64, kb * BK, &full[s]);
-                    }
-                    if (B_K) {
-                        tma_load_2d(b, &tmB, kb * BK, n0, &full[s]);
-                    } else {
-#pragma unroll
-                        for (int h = 0; h < BN / 64; ++h) tma_load_2d(b + h * 8192, &tmB, n0 + h * 64, kb * BK, &full[s]);
+                        wxtc::mbar_arrive_expect_tx(&full[s], B_STAGE_BYTES);
+                        unsigned char* b = sB + size_t(s) * B_STAGE_BYTES;
+                        if (B_K) tma_load_2d(b, &tmB, kb * BK, n0, &full[s]);
+                        else tma_load_3d(b, &tmB, 0, kb * BK, n0 / 64, &full[s]);
                     }
                 }
             }
             if (!ok) atomicExch(g.err, 201);
         }
-    } else if (warp == 1) {
+    } else if (warp == 2) {
         // ================= MMA issuer =================
         if (lane == 0) {
             constexpr uint32_t idesc = make_idesc_bf16(BM, BN, !A_K, !B_K);
@@ -167,7 +183,9 @@ wide_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                 if (local >= 2 && !wxtc::mbar_wait_hot(&tmem_empty[acc], ((local >> 1) - 1) & 1)) { ok = false; break; }
                 wxtc::tc_fence_after();
                 const uint32_t d_tmem = tmem_base + acc * BN;
-                for (int kb = 0; kb < kb_count; ++kb, ++it) {
+                const int split = int(tile / mn_tiles);
+                const int kb0 = split * kb_per, kb1 = (kb0 + kb_per < kb_total) ? kb0 + kb_per : kb_total;
+                for (int kb = kb0; kb < kb1; ++kb, ++it) {
                     const int s = it % STAGES;
                     if (!wxtc::mbar_wait_hot(&full[s], (it / STAGES) & 1)) { ok = false; break; }
                     wxtc::tc_fence_after();
@@ -181,7 +199,7 @@ wide_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                                                 : wxtc::make_smem_desc(a_addr + k * 2048, 8192, 1024);
                         const uint64_t bd = B_K ? wxtc::make_smem_desc(b_addr + k * 32, 16, 1024)
                                                 : wxtc::make_smem_desc(b_addr + k * 2048, 8192, 1024);
-                        umma_bf16(d_tmem, ad, bd, idesc, (kb | k) != 0);
+                        umma_bf16(d_tmem, ad, bd, idesc, ((kb - kb0) | k) != 0);
                     }
                     wxtc::umma_commit(&empty[s]);          // stage reusable once these MMAs have read it
                 }
@@ -191,12 +209,15 @@ wide_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             if (!ok) atomicExch(g.err, 202);
         }
     } else {
-        // ================= epilogue warps (TMEM lane quarter = warp % 4) =================
+        // ================= epilogue warps (TMEM lane quarter = warp % 4; column half = (warp - 3) / 4) =================
         const int q = warp & 3;
+        const int half = (warp - 3) >> 2;
         uint32_t local = 0;
         for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++local) {
             const uint32_t acc = local & 1;
-            const int64_t m0 = (tile / tiles_n) * BM, n0 = (tile % tiles_n) * BN;
+            const int64_t mn = tile % mn_tiles;
+            const int64_t m0 = (mn / tiles_n) * BM, n0 = (mn % tiles_n) * BN;
+            const int64_t out_off = (tile / mn_tiles) * g.split_stride;
             if (!wxtc::mbar_wait(&tmem_full[acc], (local >> 1) & 1)) {
                 if (lane == 0) atomicExch(g.err, 203);
                 break;
@@ -205,7 +226,7 @@ wide_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             const int64_t row = m0 + q * 32 + lane;
             const bool row_ok = row < g.M;
 #pragma unroll 1
-            for (int c = 0; c < BN / 16; ++c) {
+            for (int c = half * (BN / 32); c < (half + 1) * (BN / 32); ++c) {
                 float v[16];
                 wxtc::tmem_ld16(tmem_base + (uint32_t(q * 32) << 16) + acc * BN + c * 16, v);
                 wxtc::tmem_ld_wait();
@@ -261,7 +282,7 @@ wide_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                         reinterpret_cast<uint4*>(o)[0] = o0;
                         reinterpret_cast<uint4*>(o)[1] = o1;
                     } else {
-                        float* o = reinterpret_cast<float*>(g.out) + row * g.ldo + col0;
+                        float* o = reinterpret_cast<float*>(g.out) + out_off + row * g.ldo + col0;
 #pragma unroll
                         for (int i = 0; i < 4; ++i)
                             reinterpret_cast<float4*>(o)[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
@@ -276,7 +297,7 @@ wide_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     }
     wxtc::tc_fence_before();
     __syncthreads();
-    if (warp == 0) wxtc::tmem_dealloc(tmem_base, 512);
+    if (warp == 2) wxtc::tmem_dealloc(tmem_base, 512);
 }
 
 }  // namespace wxwide
