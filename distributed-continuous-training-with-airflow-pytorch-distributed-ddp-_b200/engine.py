@@ -127,6 +127,13 @@ class StepEngine:
         """One optimizer step straight from raw columns (standardisation fused into the step kernel)."""
         if self.stats is None:
             raise WxError("call fit_stats()/set_stats() before step_raw()")
+        if not hasattr(cols, "cp"):
+            # bind once per table: the same list object comes back every step of an epoch
+            cached = getattr(self, "_bound", None)
+            key = (len(cols), cols[0].data_ptr(), cols[-1].data_ptr())
+            if cached is None or cached[0] is not cols or cached[2] != key:
+                self._bound = (cols, self.ctx.bind_columns(cols), key)
+            cols = self._bound[1]
         if self.world == 1:
             mask_ok = keep_mask is None or keep_mask.data_ptr() % 16 == 0
             fn = self.ctx.train_step_raw
@@ -136,7 +143,7 @@ class StepEngine:
                impute=impute, dropout=dropout, keep_mask=keep_mask, seed=self._dropout_seed())
             self.steps_done += 1
             return self.loss
-        n = cols[0].numel()
+        n = cols.n
         b = batch if batch is not None else n - row0
         mask_ok = keep_mask is None or keep_mask.data_ptr() % 16 == 0
         if self.peers and self.use_tc and mask_ok and self.ctx.tc_ok_raw(cols, y, row0):
@@ -154,12 +161,13 @@ class StepEngine:
         recommended), the fused step, and a D2H read of the loss.  Returns the loss as a Python float."""
         f, b = cols_host.shape
         if self._stage is None or self._stage[0].shape[1] != b:
-            self._stage = (torch.empty(f, b, dtype=torch.float32, device=self.device),
-                           torch.empty(b, dtype=torch.int64, device=self.device))
-        dc, dy = self._stage
+            dc = torch.empty(f, b, dtype=torch.float32, device=self.device)
+            self._stage = (dc, torch.empty(b, dtype=torch.int64, device=self.device),
+                           self.ctx.bind_columns([dc[j] for j in range(f)]))
+        dc, dy, bound = self._stage
         dc.copy_(cols_host, non_blocking=True)
         dy.copy_(y_host, non_blocking=True)
-        loss = self.step_raw([dc[j] for j in range(f)], dy, row0=0, batch=b)
+        loss = self.step_raw(bound, dy, row0=0, batch=b)
         self._loss_host.copy_(loss.reshape(1), non_blocking=True)
         torch.cuda.current_stream(self.device).synchronize()
         return float(self._loss_host.item())
@@ -181,6 +189,7 @@ class StepEngine:
                 "done": [torch.cuda.Event() for _ in range(2)],
                 "loss": [torch.zeros(1).pin_memory() for _ in range(2)], "pending": None,
             }
+            self._pipe["bound"] = [self.ctx.bind_columns([c[j] for j in range(f)]) for c in self._pipe["cols"]]
         p = self._pipe
         slot = p["k"] & 1
         compute = torch.cuda.current_stream(self.device)
@@ -191,8 +200,7 @@ class StepEngine:
             p["y"][slot].copy_(y_host, non_blocking=True)
             p["ready"][slot].record(p["copy"])
         compute.wait_event(p["ready"][slot])
-        dc = p["cols"][slot]
-        loss = self.step_raw([dc[j] for j in range(f)], p["y"][slot], row0=0, batch=b)
+        loss = self.step_raw(p["bound"][slot], p["y"][slot], row0=0, batch=b)
         p["free"][slot].record(compute)
         p["loss"][slot].copy_(loss.reshape(1), non_blocking=True)
         p["done"][slot].record(compute)

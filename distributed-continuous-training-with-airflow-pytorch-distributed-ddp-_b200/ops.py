@@ -21,6 +21,23 @@ def _p(t: torch.Tensor | None) -> int | None:
     return None if t is None else t.data_ptr()
 
 
+class Columns:
+    """A table's columns bound once: the checked tensors, their device pointers as the HOST pointer array the C ABI takes,
+    dtype and length.  Passing this instead of a list of tensors to the raw-column calls skips the per-call validation and
+    pointer gathering (about 20 us of Python per step for 20 columns -- the whole step at small batch sizes)."""
+
+    def __init__(self, tensors, cp, vp, dt, n):
+        self.tensors, self.cp, self.vp, self.dt, self.n = list(tensors), cp, vp, dt, n
+        self.ptrs = [t.data_ptr() for t in self.tensors]
+        self.dtype = self.tensors[0].dtype
+
+    def __len__(self):
+        return len(self.tensors)
+
+    def __getitem__(self, j):
+        return self.tensors[j]
+
+
 class Context:
     """One per process / GPU (wx_ctx).  Owns scratch only; all tensors stay caller-owned."""
 
@@ -77,7 +94,18 @@ class Context:
         if numel is not None and t.numel() < numel:
             raise WxError(f"{name} has {t.numel()} elements, needs {numel}")
 
+    def bind_columns(self, cols, validity=None) -> Columns:
+        """Validate a table's columns once and keep the pointer array for repeated raw-column steps."""
+        if isinstance(cols, Columns):
+            return cols
+        cp, vp, dt, n = self._cols(cols, validity)
+        return Columns(cols, cp, vp, dt, n)
+
     def _cols(self, cols, validity):
+        if isinstance(cols, Columns):
+            if len(cols) != self.n_features:
+                raise WxError(f"expected {self.n_features} columns, got {len(cols)}")
+            return cols.cp, cols.vp, cols.dt, cols.n
         if len(cols) != self.n_features:
             raise WxError(f"expected {self.n_features} columns, got {len(cols)}")
         dt = cols[0].dtype
@@ -248,6 +276,12 @@ class Context:
                 and (x.data_ptr() + row0 * self.n_features * 4) % 16 == 0 and (y.data_ptr() + row0 * 8) % 16 == 0)
 
     def tc_ok_raw(self, cols, y, row0: int) -> bool:
+        if isinstance(cols, Columns):
+            if row0 % 4 or cols.dtype != torch.float32 or self.n_features > self.TC_MAX_FEATURES:
+                return False
+            if getattr(cols, "_al16", None) is None:
+                cols._al16 = all(p % 16 == 0 for p in cols.ptrs)
+            return cols._al16 and (y.data_ptr() + row0 * 8) % 16 == 0
         return (self.n_features <= self.TC_MAX_FEATURES and cols[0].dtype == torch.float32
                 and all((c.data_ptr() + row0 * 4) % 16 == 0 for c in cols) and (y.data_ptr() + row0 * 8) % 16 == 0)
 
