@@ -517,10 +517,54 @@ def main() -> int:
         line["cpu_reference_config"] = {"value": r4["samples_per_sec"], "unit": UNIT, "cores": 2,
                                         "sample": "1500 steps x 4 rows/rank x 2 ranks, 1 thread/rank, per-sample "
                                                   "__getitem__+collate (train_lightning_ddp.py:49,122)"}
+    if world == 1 and not args.no_cpu_baseline:
+        line["gpu_reference_config"] = reference_config_on_gpu(torch, wxddp, device)
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
     return 0
+
+
+def reference_config_on_gpu(torch, wxddp, device) -> dict:
+    """The reference's literal shape (configs[0]: 145,460 rows x 5 features, global batch 8 = 2 ranks x 4,
+    train_lightning_ddp.py:122 + docker-compose.yml:124) on ONE B200: sampler-ordered rows, 2048 optimizer steps per
+    launch of the resident small-step kernel (wx_train_steps_small).  Reported next to cpu_reference_config."""
+    f, n, batch = 5, 116_368, 8
+    ctx = wxddp.Context(f, device=device)
+    g = torch.Generator(device=device)
+    g.manual_seed(7)
+    x = torch.randn(n, f, device=device, generator=g)
+    y = (torch.rand(n, device=device, generator=g) < 0.13).to(torch.int64)
+    order = torch.randperm(n, device=device, generator=g)
+    torch.manual_seed(42)
+    from torch import nn
+    net = nn.Sequential(nn.Linear(f, 64), nn.ReLU(), nn.Dropout(0.2), nn.Linear(64, 2))
+    p = torch.cat([q.detach().reshape(-1) for q in net.parameters()]).to(device)
+    m, v = torch.zeros_like(p), torch.zeros_like(p)
+    state = torch.zeros(2, dtype=torch.int64, device=device)
+    per_launch = 2048
+    n_steps = n // batch
+    buf = torch.empty(per_launch, device=device)
+
+    def epoch():
+        s = 0
+        while s < n_steps:
+            k = min(per_launch, n_steps - s)
+            ctx.train_steps_small(p, m, v, state, x, y, buf, n_steps=k, batch=batch,
+                                  row_idx=order[s * batch:(s + k) * batch], dropout=wxddp.DROPOUT_PHILOX, seed=42)
+            s += k
+
+    epoch()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    epoch()
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1)
+    return {"value": n_steps * batch / (ms / 1e3), "unit": UNIT, "us_per_step": 1e3 * ms / n_steps,
+            "sample": f"one epoch: {n_steps} optimizer steps of {batch} sampler-ordered rows (F=5), {per_launch} steps per "
+                      f"launch of wx_train_steps_small, {ms:.1f} ms", "last_loss": float(buf[0].item())}
 
 
 if __name__ == "__main__":
