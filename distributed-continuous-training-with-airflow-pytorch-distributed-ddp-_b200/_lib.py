@@ -74,7 +74,8 @@ SIGNATURES = {
     "wx_wide_cast_weights": (_int, [_vp, C.POINTER(WideDesc), _vp, _vp, _vp]),
     "wx_wide_forward": (_int, [_vp, C.POINTER(WideDesc), _vp, _vp, _vp, _vp, _i64, _int, _u64, _u64, C.c_float, _vp,
                                _vp]),
-    "wx_wide_backward_layer": (_int, [_vp, C.POINTER(WideDesc), _vp, _i64, _int, _int, _vp, _vp]),
+    "wx_wide_backward_layer": (_int, [_vp, C.POINTER(WideDesc), _vp, _i64, _int, _int, _int, _vp, _vp]),
+    "wx_wide_adam_layer": (_int, [_vp, C.POINTER(WideDesc), _vp, _vp, _vp, _vp, _i64, _vp, _int, _vp]),
     "wx_wide_adam": (_int, [_vp, C.POINTER(WideDesc), _vp, _vp, _vp, _vp, _i64, _vp, _vp]),
     "wx_wide_gemm": (_int, [_vp, _int, _int, _vp, _i64, _vp, _i64, _i64, _i64, _i64, _vp, _vp, _vp]),
 }

@@ -592,7 +592,7 @@ int wx_wide_forward(wx_ctx* ctx, const wx_wide_desc* desc, const float* params, 
 /* Backward of hidden layer `layer` (call with layer = n_hidden, ..., 1 after wx_wide_forward): writes dW_layer and
  * db_layer into grads and, for layer > 1, dZ of the layer below into the workspace. */
 int wx_wide_backward_layer(wx_ctx* ctx, const wx_wide_desc* desc, void* ws, int64_t batch, int layer, int dropout_mode,
-                           float* grads, void* stream) {
+                           int parts, float* grads, void* stream) {
     WX_CHECK_ARG(ctx && ws && grads, "wx_wide_backward_layer: NULL argument");
     int rc = check_desc(desc, "wx_wide_backward_layer");
     if (rc != WX_OK) return rc;
@@ -600,6 +600,7 @@ int wx_wide_backward_layer(wx_ctx* ctx, const wx_wide_desc* desc, void* ws, int6
                  (long long)batch);
     const int nl = desc->n_hidden;
     WX_CHECK_ARG(layer >= 1 && layer <= nl, "wx_wide_backward_layer: layer=%d outside 1..%d", layer, nl);
+    WX_CHECK_ARG(parts >= 1 && parts <= 7, "wx_wide_backward_layer: parts=%d (bit 0 dW, bit 1 db, bit 2 dZ below)", parts);
     WX_CUDA(cudaSetDevice(ctx->device));
     Layout L;
     make_layout(desc, batch, &L);
@@ -612,7 +613,7 @@ int wx_wide_backward_layer(wx_ctx* ctx, const wx_wide_desc* desc, void* ws, int6
     const void* h_below = (layer == 1) ? static_cast<const void*>(w + L.x0) : static_cast<const void*>(w + L.h[layer - 1]);
     const int64_t in = (layer == 1) ? KPAD : H;
     // dW = dZ^T H_below : A = dZ stored [batch, H] = [K, M], B = H_below stored [batch, in] = [K, N]
-    {
+    if (parts & WX_WIDE_DW) {
         GemmArgs g = {};
         g.M = H; g.N = in; g.K = batch;
         g.inv_keep = 1.0f; g.keep_thresh16 = 65536u;
@@ -636,7 +637,7 @@ int wx_wide_backward_layer(wx_ctx* ctx, const wx_wide_desc* desc, void* ws, int6
         }
     }
     // db = column sums of dZ
-    {
+    if (parts & WX_WIDE_DB) {
         float* part = reinterpret_cast<float*>(w + L.part);
         int slabs = int(batch / 128 < COLSUM_SLABS ? batch / 128 : COLSUM_SLABS);
         dim3 cg((unsigned)((H / 8 + 255) / 256), (unsigned)slabs);
@@ -646,7 +647,7 @@ int wx_wide_backward_layer(wx_ctx* ctx, const wx_wide_desc* desc, void* ws, int6
         WX_LAUNCH_CHECK(ctx);
     }
     // dZ_below = (dZ W) * gate(H_below): A = dZ [batch, H] K-major, B = W stored [H(out), H(in)] = [K, N]
-    if (layer > 1) {
+    if (layer > 1 && (parts & WX_WIDE_DZ)) {
         GemmArgs g = {};
         g.M = batch; g.N = H; g.K = H;
         g.out = dz_below; g.ldo = H;
@@ -659,14 +660,16 @@ int wx_wide_backward_layer(wx_ctx* ctx, const wx_wide_desc* desc, void* ws, int6
     return WX_OK;
 }
 
-/* Adam (train_lightning_ddp.py:88 arithmetic) over all P parameters; the hidden layers' bf16 copies in the workspace are
- * rewritten in the same pass.  step is 1-based. */
-int wx_wide_adam(wx_ctx* ctx, const wx_wide_desc* desc, float* params, const float* grads, float* m, float* v,
-                 int64_t step, void* ws, void* stream) {
-    WX_CHECK_ARG(ctx && params && grads && m && v && ws, "wx_wide_adam: NULL argument");
-    int rc = check_desc(desc, "wx_wide_adam");
+/* Adam for one layer's tensors (layer = 1..n_hidden, n_hidden+1 = the head): lets the caller run the update of a layer
+ * on a side stream as soon as its gradient slice is final, under the backward GEMMs of the layers below. */
+int wx_wide_adam_layer(wx_ctx* ctx, const wx_wide_desc* desc, float* params, const float* grads, float* m, float* v,
+                       int64_t step, void* ws, int layer, void* stream) {
+    WX_CHECK_ARG(ctx && params && grads && m && v && ws, "wx_wide_adam_layer: NULL argument");
+    int rc = check_desc(desc, "wx_wide_adam_layer");
     if (rc != WX_OK) return rc;
-    WX_CHECK_ARG(step >= 1, "wx_wide_adam: step=%lld must be >= 1", (long long)step);
+    WX_CHECK_ARG(step >= 1, "wx_wide_adam_layer: step=%lld must be >= 1", (long long)step);
+    const int nl = desc->n_hidden;
+    WX_CHECK_ARG(layer >= 1 && layer <= nl + 1, "wx_wide_adam_layer: layer=%d outside 1..%d (%d = head)", layer, nl + 1, nl + 1);
     WX_CUDA(cudaSetDevice(ctx->device));
     Layout L;
     make_layout(desc, 128, &L);
@@ -674,26 +677,27 @@ int wx_wide_adam(wx_ctx* ctx, const wx_wide_desc* desc, float* params, const flo
     unsigned char* w = static_cast<unsigned char*>(ws);
     const AdamS a = adam_consts(desc, step);
     const int64_t H = desc->hidden;
-    const int nl = desc->n_hidden;
-    for (int l = 1; l <= nl; ++l) {
-        const int64_t in = (l == 1) ? desc->n_features : H;
-        const int64_t nw = H * in;
-        wide_adam_kernel<<<grid_for(ctx, nw, 4), 256, 0, st>>>(params + L.off_w[l], grads + L.off_w[l], m + L.off_w[l],
-                                                             v + L.off_w[l], nw, a,
-                                                             reinterpret_cast<__nv_bfloat16*>(w + L.wb[l]), int(in),
-                                                             l == 1 ? KPAD : int(in));
-        WX_LAUNCH_CHECK(ctx);
-    }
-    // biases and the head: everything that is not a hidden weight, tensor by tensor (contiguous runs)
-    for (int l = 1; l <= nl + 1; ++l) {
-        const int64_t b0 = L.off_b[l], bn = (l <= nl) ? H : desc->classes;
-        wide_adam_kernel<<<grid_for(ctx, bn), 256, 0, st>>>(params + b0, grads + b0, m + b0, v + b0, bn, a, nullptr, 1, 1);
-        WX_LAUNCH_CHECK(ctx);
-    }
-    {
-        const int64_t w0 = L.off_w[nl + 1], wn = int64_t(desc->classes) * H;
-        wide_adam_kernel<<<grid_for(ctx, wn, 4), 256, 0, st>>>(params + w0, grads + w0, m + w0, v + w0, wn, a, nullptr, 1, 1);
-        WX_LAUNCH_CHECK(ctx);
+    const int64_t in = (layer == 1) ? desc->n_features : H;
+    const int64_t rows = (layer <= nl) ? H : desc->classes;
+    const int64_t nw = rows * in, w0 = L.off_w[layer], b0 = L.off_b[layer];
+    __nv_bfloat16* wb = (layer <= nl) ? reinterpret_cast<__nv_bfloat16*>(w + L.wb[layer]) : nullptr;
+    wide_adam_kernel<<<grid_for(ctx, nw, 4), 256, 0, st>>>(params + w0, grads + w0, m + w0, v + w0, nw, a, wb,
+                                                         wb ? int(in) : 1, wb ? (layer == 1 ? KPAD : int(in)) : 1);
+    WX_LAUNCH_CHECK(ctx);
+    wide_adam_kernel<<<grid_for(ctx, rows), 256, 0, st>>>(params + b0, grads + b0, m + b0, v + b0, rows, a, nullptr, 1, 1);
+    WX_LAUNCH_CHECK(ctx);
+    return WX_OK;
+}
+
+/* Adam (train_lightning_ddp.py:88 arithmetic) over all P parameters; the hidden layers' bf16 copies in the workspace are
+ * rewritten in the same pass.  step is 1-based. */
+int wx_wide_adam(wx_ctx* ctx, const wx_wide_desc* desc, float* params, const float* grads, float* m, float* v,
+                 int64_t step, void* ws, void* stream) {
+    int rc = check_desc(desc, "wx_wide_adam");
+    if (rc != WX_OK) return rc;
+    for (int l = 1; l <= desc->n_hidden + 1; ++l) {
+        rc = wx_wide_adam_layer(ctx, desc, params, grads, m, v, step, ws, l, stream);
+        if (rc != WX_OK) return rc;
     }
     return WX_OK;
 }

@@ -102,42 +102,70 @@ class WideEngine:
 
     def loss_and_grads(self, x, y, *, dropout: int = DROPOUT_PHILOX, step: int | None = None, grad_scale=None,
                        overlap_reduce: bool = False) -> torch.Tensor:
-        """Forward + backward of one batch into self.grads ([P+1], loss at [P]); returns self.grads."""
+        """Forward + backward of one batch into self.grads ([P+1], loss at [P]); returns self.grads.  With
+        overlap_reduce the gradient slices are SUM-all-reduced across ranks on a side stream, layer by layer."""
+        self._run(x, y, dropout, step, grad_scale, reduce=overlap_reduce, adam_step=None)
+        return self.grads
+
+    def _run(self, x, y, dropout, step, grad_scale, *, reduce: bool, adam_step: int | None) -> None:
+        """The step's schedule.  Main stream: forward, head, then per layer dW and dZ-below GEMMs.  Side stream: bias
+        gradients (column sums of dZ_l, which only read dZ_l), the layer's all-reduce, and -- when adam_step is given --
+        that layer's Adam, all running under the GEMMs of the layers below.  Events keep three hazards in order:
+        dZ buffers ping-pong (the dZ product below may not overwrite a buffer the side stream still sums), Adam rewrites
+        the bf16 weights (only after the layer's own dZ product has read them), and the next step's forward needs all
+        of it (the streams join at the end)."""
         b = self._check_batch(x, y)
         step = self.steps_done if step is None else step
         scale = 1.0 / (self.world * b) if grad_scale is None else grad_scale
-        st = self._stream()
         d = C.byref(self.desc)
-        check(self.lib.wx_wide_forward(self._h, d, self.params.data_ptr(), self.ws.data_ptr(), x.data_ptr(), y.data_ptr(), b,
-                                       dropout, self.seed, step, scale, self.grads.data_ptr(), st))
+        lib, h, ws, g = self.lib, self._h, self.ws.data_ptr(), self.grads.data_ptr()
         main = torch.cuda.current_stream(self.device)
-        works = []
+        if getattr(self, "_aux", None) is None:
+            self._aux = torch.cuda.Stream(device=self.device)
+        side = self._aux
+        mst, sst = C.c_void_p(main.cuda_stream), C.c_void_p(side.cuda_stream)
 
-        def reduce_slice(lo, hi):
+        def after_main():
             ev = torch.cuda.Event()
             ev.record(main)
-            self._side.wait_event(ev)
-            with torch.cuda.stream(self._side):
-                works.append(self.dist.all_reduce(self.grads[lo:hi], async_op=True))
+            side.wait_event(ev)
 
-        if overlap_reduce:
-            reduce_slice(*self.head_slice)
+        def reduce_slice(lo, hi):
+            if reduce:                                         # DDP SUM of the slice, on the side stream
+                with torch.cuda.stream(side):
+                    self.dist.all_reduce(self.grads[lo:hi])
+
+        def adam(layer):
+            if adam_step is not None:
+                check(lib.wx_wide_adam_layer(h, d, self.params.data_ptr(), g, self.m.data_ptr(), self.v.data_ptr(),
+                                             adam_step, ws, layer, sst))
+
+        check(lib.wx_wide_forward(h, d, self.params.data_ptr(), ws, x.data_ptr(), y.data_ptr(), b, dropout, self.seed, step,
+                                  scale, g, mst))
+        after_main()                                           # dZ_L, head gradients and the loss are enqueued
+        reduce_slice(*self.head_slice)
+        adam(self.L + 1)
+        db_done = {}
         for layer in range(self.L, 0, -1):
-            check(self.lib.wx_wide_backward_layer(self._h, d, self.ws.data_ptr(), b, layer, dropout, self.grads.data_ptr(), st))
-            if overlap_reduce:
-                reduce_slice(*self.slices[layer - 1])
-        if overlap_reduce:
-            for w in works:
-                w.wait()
-            main.wait_stream(self._side)
-        return self.grads
+            # side: bias gradient of this layer (dZ_layer is ready: the side stream already waited for its producer)
+            check(lib.wx_wide_backward_layer(h, d, ws, b, layer, dropout, 2, g, sst))
+            db_done[layer] = torch.cuda.Event()
+            db_done[layer].record(side)
+            check(lib.wx_wide_backward_layer(h, d, ws, b, layer, dropout, 1, g, mst))          # dW
+            after_main()
+            reduce_slice(*self.slices[layer - 1])             # starts as soon as dW is final, under the dZ product
+            if layer > 1:
+                if layer + 1 in db_done:
+                    main.wait_event(db_done[layer + 1])       # dZ_{layer-1} reuses the buffer of dZ_{layer+1}
+                check(lib.wx_wide_backward_layer(h, d, ws, b, layer, dropout, 4, g, mst))      # dZ below
+                after_main()
+            adam(layer)                                        # rewrites the bf16 weights the dZ product has just read
+        main.wait_stream(side)
 
     def step(self, x, y, *, dropout: int = DROPOUT_PHILOX) -> torch.Tensor:
         """One optimizer step; returns the device scalar train_loss (rank mean)."""
-        self.loss_and_grads(x, y, dropout=dropout, overlap_reduce=self.world > 1)
+        self._run(x, y, dropout, None, None, reduce=self.world > 1, adam_step=self.steps_done + 1)
         self.steps_done += 1
-        check(self.lib.wx_wide_adam(self._h, C.byref(self.desc), self.params.data_ptr(), self.grads.data_ptr(),
-                                    self.m.data_ptr(), self.v.data_ptr(), self.steps_done, self.ws.data_ptr(), self._stream()))
         return self.grads[self.P:self.P + 1]
 
     def step_host(self, x_host: torch.Tensor, y_host: torch.Tensor) -> float:

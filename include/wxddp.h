@@ -265,12 +265,21 @@ int wx_wide_forward(wx_ctx* ctx, const wx_wide_desc* desc, const float* params, 
                     const int64_t* y, int64_t batch, int dropout_mode, uint64_t seed, uint64_t step, float grad_scale,
                     float* grads, void* stream);
 /* Backward of hidden layer `layer` = n_hidden, ..., 1 (in that order, after wx_wide_forward): dW_layer and db_layer into
- * grads; the caller may start reducing that slice across ranks while the next layer's backward runs. */
+ * grads; the caller may start reducing that slice across ranks while the next layer's backward runs.  `parts` selects
+ * which of the three pieces this call enqueues (WX_WIDE_ALL for everything), so db can go to a side stream: it only
+ * reads dZ of this layer, which stays valid until the dZ product of the layer BELOW the next one overwrites it. */
+#define WX_WIDE_DW 1 /* weight gradient of the layer */
+#define WX_WIDE_DB 2 /* bias gradient (column sums of dZ) */
+#define WX_WIDE_DZ 4 /* dZ of the layer below (skipped for layer 1) */
+#define WX_WIDE_ALL 7
 int wx_wide_backward_layer(wx_ctx* ctx, const wx_wide_desc* desc, void* ws, int64_t batch, int layer, int dropout_mode,
-                           float* grads, void* stream);
+                           int parts, float* grads, void* stream);
 /* Adam over all P parameters (step is 1-based), rewriting the bf16 weight copies in ws in the same pass. */
 int wx_wide_adam(wx_ctx* ctx, const wx_wide_desc* desc, float* params, const float* grads, float* m, float* v,
                  int64_t step, void* ws, void* stream);
+/* The same for one layer's tensors (layer 1..n_hidden, n_hidden+1 = head), e.g. on a side stream once that slice is final. */
+int wx_wide_adam_layer(wx_ctx* ctx, const wx_wide_desc* desc, float* params, const float* grads, float* m, float* v,
+                       int64_t step, void* ws, int layer, void* stream);
 /* The GEMM underneath, exposed for tests: out fp32 [M,N] = op(A) op(B) (+ bias[N]); A is [M,K] (a_kmajor) or [K,M],
  * B is [N,K] (b_kmajor) or [K,N], row-major bf16 with pitches lda/ldb in elements.  N % 16 == 0, K % 64 == 0.
  * Supported layout pairs: (1,1), (1,0), (0,0) -- the three the wide MLP uses. */
