@@ -140,7 +140,7 @@ __global__ void __launch_bounds__(256) wide_head_kernel(const __nv_bfloat16* __r
                                                        const int64_t* __restrict__ y, float scale,
                                                        float* __restrict__ dlog, float* __restrict__ part) {
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    float acc_loss = 0.0f, acc0 = 0.0f, acc1 = 0.0f;
+    float acc_loss = 0.0f, acc0 = 0.0f, acc1 = 0.0f, acc_ok = 0.0f;
     for (int64_t row = int64_t(blockIdx.x) * 8 + warp; row < batch; row += int64_t(gridDim.x) * 8) {
         const uint4* hp = reinterpret_cast<const uint4*>(h + row * H);
         float s0 = 0.0f, s1 = 0.0f;
@@ -165,26 +165,29 @@ __global__ void __launch_bounds__(256) wide_head_kernel(const __nv_bfloat16* __r
             const float inv = 1.0f / (e0 + e1);
             const float d0 = (e0 * inv - (lab == 0 ? 1.0f : 0.0f)) * scale;
             const float d1 = (e1 * inv - (lab == 1 ? 1.0f : 0.0f)) * scale;
-            dlog[row * 2] = d0;
-            dlog[row * 2 + 1] = d1;
+            if (dlog != nullptr) {
+                dlog[row * 2] = d0;
+                dlog[row * 2 + 1] = d1;
+            }
             acc_loss += (lse - (lab == 0 ? s0 : s1)) * scale;
+            acc_ok += (int64_t(s1 > s0) == lab) ? 1.0f : 0.0f;          // argmax, first index on ties (torch.argmax)
             acc0 += d0;
             acc1 += d1;
         }
     }
-    __shared__ float sh[8][3];
+    __shared__ float sh[8][4];
     if (lane == 0) {
         sh[warp][0] = acc_loss;
         sh[warp][1] = acc0;
         sh[warp][2] = acc1;
+        sh[warp][3] = acc_ok;
     }
     __syncthreads();
-    if (threadIdx.x < 3) {
+    if (threadIdx.x < 4) {
         float t = 0.0f;
         for (int w = 0; w < 8; ++w) t += sh[w][threadIdx.x];
         part[blockIdx.x * 4 + threadIdx.x] = t;
     }
-    if (threadIdx.x == 3) part[blockIdx.x * 4 + 3] = 0.0f;
 }
 
 // head backward: dZ_L[r][c] = (dl0[r] W_o[0][c] + dl1[r] W_o[1][c]) * gate(H_L[r][c]) as bf16, and per-slab partial sums
@@ -283,26 +286,31 @@ __global__ void __launch_bounds__(256) wide_reduce_kernel(const float* __restric
 
 // head partials [n_parts][4] = (loss, db0, db1, -) -> grads[off_b_out .. +2] and grads[P]
 __global__ void __launch_bounds__(256) wide_head_finish_kernel(const float* __restrict__ part, int n_parts,
-                                                              float* __restrict__ db_out, float* __restrict__ loss_out) {
-    __shared__ float sh[256][3];
+                                                              float* __restrict__ db_out, float* __restrict__ loss_out,
+                                                              float* __restrict__ correct_out) {
+    __shared__ float sh[256][4];
     const int t = threadIdx.x;
-    float s[3] = {0.0f, 0.0f, 0.0f};
+    float s[4] = {0.0f, 0.0f, 0.0f, 0.0f};
     for (int p = t; p < n_parts; p += 256) {               // fixed assignment + fixed tree: deterministic
         const float4 v = __ldg(reinterpret_cast<const float4*>(part) + p);
-        s[0] += v.x; s[1] += v.y; s[2] += v.z;
+        s[0] += v.x; s[1] += v.y; s[2] += v.z; s[3] += v.w;
     }
-    sh[t][0] = s[0]; sh[t][1] = s[1]; sh[t][2] = s[2];
+    sh[t][0] = s[0]; sh[t][1] = s[1]; sh[t][2] = s[2]; sh[t][3] = s[3];
     __syncthreads();
     for (int o = 128; o > 0; o >>= 1) {
         if (t < o) {
-            sh[t][0] += sh[t + o][0]; sh[t][1] += sh[t + o][1]; sh[t][2] += sh[t + o][2];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) sh[t][i] += sh[t + o][i];
         }
         __syncthreads();
     }
     if (t == 0) {
         *loss_out = sh[0][0];
-        db_out[0] = sh[0][1];
-        db_out[1] = sh[0][2];
+        if (db_out != nullptr) {
+            db_out[0] = sh[0][1];
+            db_out[1] = sh[0][2];
+        }
+        if (correct_out != nullptr) *correct_out = sh[0][3];
     }
 }
 
@@ -526,6 +534,38 @@ int wx_wide_cast_weights(wx_ctx* ctx, const wx_wide_desc* desc, const float* par
     return WX_OK;
 }
 
+}  // extern "C"
+
+namespace {
+
+// x -> X0 -> H_1 .. H_L (bf16) in the workspace: the hidden stack shared by the training forward and the validation pass
+int hidden_forward(wx_ctx* ctx, const wx_wide_desc* desc, const Layout& L, const float* params, unsigned char* w,
+                   const float* x, int64_t batch, bool drop, uint64_t seed, uint64_t step, cudaStream_t st) {
+    const int64_t H = desc->hidden;
+    const float keep_p = 1.0f - desc->dropout_p;
+    __nv_bfloat16* x0 = reinterpret_cast<__nv_bfloat16*>(w + L.x0);
+    cast_pad_kernel<<<grid_for(ctx, batch * KPAD), 256, 0, st>>>(x, batch, desc->n_features, KPAD, x0);
+    WX_LAUNCH_CHECK(ctx);
+    for (int l = 1; l <= desc->n_hidden; ++l) {
+        GemmArgs g = {};
+        g.M = batch; g.N = H; g.K = (l == 1) ? KPAD : H;
+        g.out = w + L.h[l]; g.ldo = H;
+        g.bias = params + L.off_b[l];
+        g.inv_keep = drop ? 1.0f / keep_p : 1.0f;
+        g.keep_thresh16 = drop ? uint32_t(lrintf(keep_p * 65536.0f)) : 65536u;
+        g.seed_lo = uint32_t(seed); g.seed_hi = uint32_t(seed >> 32);
+        g.step = uint32_t(step); g.layer = uint32_t(l);
+        const void* a = (l == 1) ? static_cast<const void*>(x0) : static_cast<const void*>(w + L.h[l - 1]);
+        const int rc = launch_gemm(ctx, true, true, EPI_FWD, a, g.K, w + L.wb[l], g.K, g, st);
+        if (rc != WX_OK) return rc;
+    }
+    return WX_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
 /* Forward through the loss, plus the head's gradients and dZ of the last hidden layer.
  *   x      fp32 [batch, F] row-major, standardised (the output of wx_normalize_pack)
  *   grads  fp32 [P+1]: receives dW_o, db_o and, at [P], sum_rows(CE) * grad_scale
@@ -551,22 +591,8 @@ int wx_wide_forward(wx_ctx* ctx, const wx_wide_desc* desc, const float* params, 
     const int nl = desc->n_hidden;
     const bool drop = dropout_mode == WX_DROPOUT_PHILOX && desc->dropout_p > 0.0f;
     const float keep_p = 1.0f - desc->dropout_p;
-    __nv_bfloat16* x0 = reinterpret_cast<__nv_bfloat16*>(w + L.x0);
-    cast_pad_kernel<<<grid_for(ctx, batch * KPAD), 256, 0, st>>>(x, batch, desc->n_features, KPAD, x0);
-    WX_LAUNCH_CHECK(ctx);
-    for (int l = 1; l <= nl; ++l) {
-        GemmArgs g = {};
-        g.M = batch; g.N = H; g.K = (l == 1) ? KPAD : H;
-        g.out = w + L.h[l]; g.ldo = H;
-        g.bias = params + L.off_b[l];
-        g.inv_keep = drop ? 1.0f / keep_p : 1.0f;
-        g.keep_thresh16 = drop ? uint32_t(lrintf(keep_p * 65536.0f)) : 65536u;
-        g.seed_lo = uint32_t(seed); g.seed_hi = uint32_t(seed >> 32);
-        g.step = uint32_t(step); g.layer = uint32_t(l);
-        const void* a = (l == 1) ? static_cast<const void*>(x0) : static_cast<const void*>(w + L.h[l - 1]);
-        rc = launch_gemm(ctx, true, true, EPI_FWD, a, g.K, w + L.wb[l], g.K, g, st);
-        if (rc != WX_OK) return rc;
-    }
+    rc = hidden_forward(ctx, desc, L, params, w, x, batch, drop, seed, step, st);
+    if (rc != WX_OK) return rc;
     const __nv_bfloat16* hl = reinterpret_cast<const __nv_bfloat16*>(w + L.h[nl]);
     float* dlog = reinterpret_cast<float*>(w + L.dlog);
     float* part = reinterpret_cast<float*>(w + L.part);
@@ -576,7 +602,7 @@ int wx_wide_forward(wx_ctx* ctx, const wx_wide_desc* desc, const float* params, 
     wide_head_kernel<<<hgrid, 256, 0, st>>>(hl, batch, int(H), params + L.off_w[nl + 1], params + L.off_b[nl + 1], y,
                                            grad_scale, dlog, head_part);
     WX_LAUNCH_CHECK(ctx);
-    wide_head_finish_kernel<<<1, 256, 0, st>>>(head_part, hgrid, grads + L.off_b[nl + 1], grads + L.P);
+    wide_head_finish_kernel<<<1, 256, 0, st>>>(head_part, hgrid, grads + L.off_b[nl + 1], grads + L.P, nullptr);
     WX_LAUNCH_CHECK(ctx);
     int slabs = int(batch / 128 < HEAD_SLABS ? batch / 128 : HEAD_SLABS);
     dim3 bg((unsigned)((H / 8 + 255) / 256), (unsigned)slabs);
@@ -699,6 +725,35 @@ int wx_wide_adam(wx_ctx* ctx, const wx_wide_desc* desc, float* params, const flo
         rc = wx_wide_adam_layer(ctx, desc, params, grads, m, v, step, ws, l, stream);
         if (rc != WX_OK) return rc;
     }
+    return WX_OK;
+}
+
+/* Validation pass (train_lightning_ddp.py:73-85 for the wide net): eval-mode forward (no dropout), out[0] = sum of the
+ * per-row cross-entropy, out[1] = number of rows whose argmax equals the label (fp32 device scalars). */
+int wx_wide_eval(wx_ctx* ctx, const wx_wide_desc* desc, const float* params, void* ws, const float* x, const int64_t* y,
+                 int64_t batch, float* out, void* stream) {
+    WX_CHECK_ARG(ctx && params && ws && x && y && out, "wx_wide_eval: NULL argument");
+    int rc = check_desc(desc, "wx_wide_eval");
+    if (rc != WX_OK) return rc;
+    WX_CHECK_ARG(batch >= 128 && batch % 128 == 0, "wx_wide_eval: batch=%lld must be a positive multiple of 128",
+                 (long long)batch);
+    WX_CUDA(cudaSetDevice(ctx->device));
+    Layout L;
+    make_layout(desc, batch, &L);
+    cudaStream_t st = (cudaStream_t)stream;
+    unsigned char* w = static_cast<unsigned char*>(ws);
+    const int nl = desc->n_hidden;
+    rc = hidden_forward(ctx, desc, L, params, w, x, batch, false, 0, 0, st);
+    if (rc != WX_OK) return rc;
+    float* part = reinterpret_cast<float*>(w + L.part);
+    float* head_part = part + size_t(HEAD_SLABS) * 2 * desc->hidden;
+    int hgrid = int((batch + 7) / 8);
+    if (hgrid > 4096) hgrid = 4096;
+    wide_head_kernel<<<hgrid, 256, 0, st>>>(reinterpret_cast<const __nv_bfloat16*>(w + L.h[nl]), batch, desc->hidden,
+                                           params + L.off_w[nl + 1], params + L.off_b[nl + 1], y, 1.0f, nullptr, head_part);
+    WX_LAUNCH_CHECK(ctx);
+    wide_head_finish_kernel<<<1, 256, 0, st>>>(head_part, hgrid, nullptr, out, out + 1);
+    WX_LAUNCH_CHECK(ctx);
     return WX_OK;
 }
 

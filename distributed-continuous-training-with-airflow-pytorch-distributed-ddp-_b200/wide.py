@@ -168,6 +168,18 @@ class WideEngine:
         self.steps_done += 1
         return self.grads[self.P:self.P + 1]
 
+    def evaluate(self, x, y):
+        """validation_step (:73-85) for this rank's rows: eval-mode forward -> (val_loss, val_acc), rank-weighted means."""
+        b = self._check_batch(x, y)
+        out = torch.zeros(2, device=self.device)
+        check(self.lib.wx_wide_eval(self._h, C.byref(self.desc), self.params.data_ptr(), self.ws.data_ptr(), x.data_ptr(),
+                                    y.data_ptr(), b, out.data_ptr(), self._stream()))
+        tot = torch.cat([out.double(), torch.tensor([float(b)], dtype=torch.float64, device=self.device)])
+        if self.world > 1:
+            self.dist.all_reduce(tot)
+        tot = tot.cpu()
+        return float(tot[0] / tot[2]), float(tot[1] / tot[2])
+
     def step_host(self, x_host: torch.Tensor, y_host: torch.Tensor) -> float:
         """End-to-end step from HOST buffers (pinned memory recommended): H2D of the fp32 [batch, F] features and int64
         labels, the step, and a D2H read of the loss."""

@@ -280,6 +280,10 @@ int wx_wide_adam(wx_ctx* ctx, const wx_wide_desc* desc, float* params, const flo
 /* The same for one layer's tensors (layer 1..n_hidden, n_hidden+1 = head), e.g. on a side stream once that slice is final. */
 int wx_wide_adam_layer(wx_ctx* ctx, const wx_wide_desc* desc, float* params, const float* grads, float* m, float* v,
                        int64_t step, void* ws, int layer, void* stream);
+/* Validation pass of the wide net (the :73-85 pattern): eval-mode forward, out[0] = sum of per-row CE, out[1] = number of
+ * rows whose argmax equals the label (fp32 device scalars; first index wins a tie, as torch.argmax). */
+int wx_wide_eval(wx_ctx* ctx, const wx_wide_desc* desc, const float* params, void* ws, const float* x, const int64_t* y,
+                 int64_t batch, float* out, void* stream);
 /* The GEMM underneath, exposed for tests: out fp32 [M,N] = op(A) op(B) (+ bias[N]); A is [M,K] (a_kmajor) or [K,M],
  * B is [N,K] (b_kmajor) or [K,N], row-major bf16 with pitches lda/ldb in elements.  N % 16 == 0, K % 64 == 0.
  * Supported layout pairs: (1,1), (1,0), (0,0) -- the three the wide MLP uses. */

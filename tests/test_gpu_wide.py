@@ -114,6 +114,25 @@ def test_adam_steps_track_oracle_and_refresh_bf16_weights():
     assert e.status() == 0
 
 
+def test_validation_pass_matches_fp32_reference(eng):
+    f, h, nl = eng.F, eng.H, eng.L
+    torch.manual_seed(77)
+    x = torch.randn(512, f)
+    y = (torch.rand(512) < 0.4).long()
+    loss, acc = eng.evaluate(x.cuda(), y.cuda())
+    layers = wide_ref.split(eng.params.cpu(), f, h, nl)
+    a = x
+    for l in range(nl):
+        a = torch.relu(a @ layers[l][0].t() + layers[l][1])
+    logits = a @ layers[nl][0].t() + layers[nl][1]
+    want_loss = float(torch.nn.functional.cross_entropy(logits, y))
+    margin = (logits[:, 1] - logits[:, 0]).abs()
+    want_acc = float((logits.argmax(1) == y).float().mean())
+    assert abs(loss - want_loss) < 2e-2 * want_loss
+    # rows whose two logits are closer than the bf16 noise may flip
+    assert abs(acc - want_acc) <= float((margin < 2e-2).float().mean()) + 1e-9
+
+
 def test_constraints_are_checked():
     from wxddp import WxError
     from wxddp.wide import WideEngine
