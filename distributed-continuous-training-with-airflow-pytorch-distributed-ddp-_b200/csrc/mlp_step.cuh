@@ -35,7 +35,8 @@ struct Dim {
 // Philox4x32-10 (Salmon et al., SC'11).  Dropout stream contract (WX_DROPOUT_PHILOX), one 64-bit keep mask per
 // batch position b (bit j = keep hidden unit j):
 //   key = (seed_lo, seed_hi); for q = 0..7: counter = (b_lo, b_hi, step_lo, (step_hi << 3) | q) -> words W[4q..4q+3];
-//   the 32 words form 16 digit planes U_d = W[2d] | W[2d+1] << 32 (d = 0 most significant): bit j of U_d is binary
+//   calls 0..3 serve hidden units 0..31, calls 4..7 units 32..63 (a thread that owns half a row needs only its four):
+//   the 32 words form 16 digit planes U_d = W[d] | W[16 + d] << 32 (d = 0 most significant): bit j of U_d is binary
 //   digit d of a 16-bit uniform u_j;  keep_j <=> u_j < 0xCCCD (= 52429, 52429/65536 = 0.80000305), evaluated for all
 //   64 units at once: lt = 0; for d = 15..0: lt = T_d ? (~U_d | lt) : (~U_d & lt), T = 0xCCCD MSB first.
 // ---------------------------------------------------------------------------------------------
@@ -71,12 +72,29 @@ __device__ __forceinline__ uint64_t philox_keep_mask(uint64_t b, uint2 key, uint
     for (int sub = 3; sub >= 0; --sub) {
         uint32_t w[8];
 #pragma unroll
-        for (int h = 0; h < 2; ++h) {
+        for (int h = 0; h < 2; ++h) {          // call sub: low halves of planes 4sub..4sub+3; call 4+sub: high halves
             const uint4 o = philox4x32_10(make_uint4(uint32_t(b), uint32_t(b >> 32), uint32_t(step),
-                                                     (uint32_t(step >> 32) << 3) | uint32_t(2 * sub + h)), key);
-            w[4 * h] = o.x; w[4 * h + 1] = o.y; w[4 * h + 2] = o.z; w[4 * h + 3] = o.w;
+                                                     (uint32_t(step >> 32) << 3) | uint32_t(4 * h + sub)), key);
+            w[h] = o.x; w[2 + h] = o.y; w[4 + h] = o.z; w[6 + h] = o.w;
         }
         lt = keep_digits4(lt, w, 4 * sub);
+    }
+    return lt;
+}
+
+// keep bits of units 32*half .. 32*half+31 of batch position b: the four Philox calls of that half
+__device__ __forceinline__ uint32_t philox_keep_half(uint64_t b, int half, uint2 key, uint64_t step) {
+    uint32_t lt = 0;
+#pragma unroll 1
+    for (int sub = 3; sub >= 0; --sub) {
+        const uint4 o = philox4x32_10(make_uint4(uint32_t(b), uint32_t(b >> 32), uint32_t(step),
+                                                 (uint32_t(step >> 32) << 3) | uint32_t(4 * half + sub)), key);
+        const uint32_t w[4] = {o.x, o.y, o.z, o.w};
+#pragma unroll
+        for (int k = 3; k >= 0; --k) {
+            const bool t = (PHILOX_KEEP_THRESH >> (15 - (4 * sub + k))) & 1u;
+            lt = t ? (~w[k] | lt) : (~w[k] & lt);
+        }
     }
     return lt;
 }
@@ -233,8 +251,8 @@ __device__ __forceinline__ uint32_t chunk_keep_bits(int mode, const ChunkMeta& c
     uint32_t w[8];
 #pragma unroll
     for (int h = 0; h < 2; ++h) {
-        const uint4 o = philox4x32_10(make_uint4(uint32_t(b), uint32_t(b >> 32), step_lo, (step_hi << 3) | uint32_t(2 * sub + h)), key);
-        w[4 * h] = o.x; w[4 * h + 1] = o.y; w[4 * h + 2] = o.z; w[4 * h + 3] = o.w;
+        const uint4 o = philox4x32_10(make_uint4(uint32_t(b), uint32_t(b >> 32), step_lo, (step_hi << 3) | uint32_t(4 * h + sub)), key);
+        w[h] = o.x; w[2 + h] = o.y; w[4 + h] = o.z; w[6 + h] = o.w;
     }
     uint64_t cur = 0;
 #pragma unroll

@@ -33,9 +33,9 @@ def philox4x32_10(c0, c1, c2, c3, k0, k1):
 def dropout_keep_mask(batch: int, seed: int, step: int) -> np.ndarray:
     """[batch, 64] bool keep mask the kernels use for (seed, step): batch position b, hidden unit j.
 
-    For q = 0..7: counter (b_lo, b_hi, step_lo, (step_hi << 3) | q) -> words W[4q..4q+3]; digit plane
-    U_d = W[2d] | W[2d+1] << 32 (d = 0 most significant); bit j of U_d is binary digit d of a 16-bit uniform u_j;
-    keep_j <=> u_j < 0xCCCD.
+    For q = 0..7: counter (b_lo, b_hi, step_lo, (step_hi << 3) | q) -> words W[4q..4q+3] (calls 0..3 serve units
+    0..31, calls 4..7 units 32..63); digit plane U_d = W[d] | W[16 + d] << 32 (d = 0 most significant); bit j of U_d
+    is binary digit d of a 16-bit uniform u_j; keep_j <=> u_j < 0xCCCD.
     """
     b = np.arange(batch, dtype=np.uint64)
     b_lo = (b & np.uint64(0xFFFFFFFF)).astype(np.uint32)
@@ -48,7 +48,7 @@ def dropout_keep_mask(batch: int, seed: int, step: int) -> np.ndarray:
             words[4 * q + i] = out[i]
     u = np.zeros((batch, 64), dtype=np.uint32)                      # the 16-bit uniform of every (row, unit)
     for d in range(16):
-        plane = words[2 * d].astype(np.uint64) | (words[2 * d + 1].astype(np.uint64) << np.uint64(32))
+        plane = words[d].astype(np.uint64) | (words[16 + d].astype(np.uint64) << np.uint64(32))
         bits = ((plane[:, None] >> np.arange(64, dtype=np.uint64)) & np.uint64(1)).astype(np.uint32)
         u |= bits << np.uint32(15 - d)
     return u < KEEP_THRESH
