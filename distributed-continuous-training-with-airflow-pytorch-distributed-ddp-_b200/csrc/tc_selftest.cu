@@ -34,6 +34,10 @@ __global__ void __launch_bounds__(128) tc_selftest_kernel(const float* __restric
     extern __shared__ __align__(1024) unsigned char raw[];
     SelfSmem& s = *reinterpret_cast<SelfSmem*>((reinterpret_cast<uintptr_t>(raw) + 1023) & ~uintptr_t(1023));
     const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
+    // terms 11..13: variant with ONE unswizzled X buffer (8 x 16-byte core matrices, column groups 128 B apart, 8-row
+    // groups 1024 B apart) read K-major by GEMM1 and MN-major by GEMM2
+    const bool shared_x = terms > 10;
+    if (shared_x) terms -= 10;
     if (t == 0) {
         mbar_init(&s.bar, 1);
         fence_mbar_init();
@@ -44,8 +48,14 @@ __global__ void __launch_bounds__(128) tc_selftest_kernel(const float* __restric
     for (int c = 0; c < 32; ++c) {
         float hi, lo;
         split_tf32(x[t * 32 + c], hi, lo);
-        store_sw(s.xhi, t, c, hi);
-        store_sw(s.xlo, t, c, lo);
+        if (shared_x) {
+            const uint32_t off = (t >> 3) * 1024 + (c >> 2) * 128 + (t & 7) * 16 + (c & 3) * 4;
+            *reinterpret_cast<float*>(reinterpret_cast<unsigned char*>(s.xhi) + off) = hi;
+            *reinterpret_cast<float*>(reinterpret_cast<unsigned char*>(s.xlo) + off) = lo;
+        } else {
+            store_sw(s.xhi, t, c, hi);
+            store_sw(s.xlo, t, c, lo);
+        }
         *reinterpret_cast<float*>(reinterpret_cast<unsigned char*>(s.xmhi) + mn32_offset(c, t, 512, 512)) = hi;
         *reinterpret_cast<float*>(reinterpret_cast<unsigned char*>(s.xmlo) + mn32_offset(c, t, 512, 512)) = lo;
         if (t < 64) {
@@ -77,7 +87,8 @@ __global__ void __launch_bounds__(128) tc_selftest_kernel(const float* __restric
         bool acc = false;
         for (int term = 3 - terms; term < 3; ++term) {
             for (int k = 0; k < 4; ++k) {
-                const uint64_t ad = make_smem_desc(smem_u32(at[term]) + k * 32, 16, 1024);
+                const uint64_t ad = shared_x ? make_smem_desc(smem_u32(at[term]) + k * 256, 128, 1024, 0)
+                                             : make_smem_desc(smem_u32(at[term]) + k * 32, 16, 1024);
                 const uint64_t bd = make_smem_desc(smem_u32(bt[term]) + k * 32, 16, 1024);
                 umma_tf32(d1, ad, bd, id1, acc);
                 acc = true;
@@ -86,12 +97,13 @@ __global__ void __launch_bounds__(128) tc_selftest_kernel(const float* __restric
         // ---- GEMM2: M=64, N=32, K=128 (16 k-steps of 8), operands MN-major ----
         const uint32_t id2 = make_idesc_tf32(64, 32, true, true);
         const float* a2[3] = {s.ahi, s.alo, s.ahi};
-        const float* b2[3] = {s.xmlo, s.xmhi, s.xmhi};
+        const float* b2[3] = {shared_x ? s.xlo : s.xmlo, shared_x ? s.xhi : s.xmhi, shared_x ? s.xhi : s.xmhi};
         acc = false;
         for (int term = 3 - terms; term < 3; ++term) {
             for (int k = 0; k < 16; ++k) {
                 const uint64_t ad = make_smem_desc(smem_u32(a2[term]) + k * 2048, 512, 1024, LAYOUT_SW128_B32);
-                const uint64_t bd = make_smem_desc(smem_u32(b2[term]) + k * 1024, 512, 512, LAYOUT_SW128_B32);
+                const uint64_t bd = shared_x ? make_smem_desc(smem_u32(b2[term]) + k * 1024, 1024, 128, 0)
+                                             : make_smem_desc(smem_u32(b2[term]) + k * 1024, 512, 512, LAYOUT_SW128_B32);
                 umma_tf32(d2, ad, bd, id2, acc);
                 acc = true;
             }
@@ -128,7 +140,7 @@ extern "C" int wx_tc_selftest(wx_ctx* ctx, const float* x, const float* w, const
                               int* status, void* stream) {
     WX_CHECK_ARG(ctx != nullptr, "wx_tc_selftest: ctx is NULL");
     WX_CHECK_ARG(x && w && dh && z && g && status, "wx_tc_selftest: NULL pointer");
-    WX_CHECK_ARG(terms >= 1 && terms <= 3, "wx_tc_selftest: terms=%d", terms);
+    WX_CHECK_ARG((terms >= 1 && terms <= 3) || (terms >= 11 && terms <= 13), "wx_tc_selftest: terms=%d", terms);
     WX_CUDA(cudaSetDevice(ctx->device));
     const int smem = int(sizeof(SelfSmem)) + 1024;
     WX_CUDA(cudaFuncSetAttribute(tc_selftest_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));

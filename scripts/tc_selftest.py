@@ -6,7 +6,7 @@ g = torch.Generator().manual_seed(3)
 x = torch.randn(128, 32, generator=g); w = torch.randn(64, 32, generator=g) * 0.3; dh = torch.randn(128, 64, generator=g) * 0.01
 x[:, 24:] = 0
 zref = (x.double() @ w.double().T).numpy(); gref = (dh.double().T @ x.double()).numpy()
-for terms in (1, 3):
+for terms in (1, 3, 11, 13):
     z = torch.full((128, 64), float("nan"), device="cuda"); gg = torch.full((64, 32), float("nan"), device="cuda")
     st = torch.full((1,), -1, dtype=torch.int32, device="cuda")
     xd, wd, dd = x.cuda().contiguous(), w.cuda().contiguous(), dh.cuda().contiguous()
