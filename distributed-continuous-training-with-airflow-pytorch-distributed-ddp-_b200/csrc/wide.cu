@@ -12,7 +12,9 @@
 //                  db_l = colsum(dZ_l)                 wide_colsum_kernel + wide_reduce_kernel
 //                  dZ_{l-1} = (dZ_l W_l) * gate(H_{l-1})   GEMM, EPI_DX (W read MN-major)
 //   Adam on the fp32 master parameters, re-emitting the bf16 copies of the hidden weights in the same pass.
-#include "wide_gemm.cuh"
+#include "wide_gemm2.cuh"
+
+#include <stdlib.h>
 
 #include <math.h>
 
@@ -426,11 +428,69 @@ int launch_gemm_t(wx_ctx* ctx, const CUtensorMap& ta, const CUtensorMap& tb, con
     return WX_OK;
 }
 
+// two-SM kernel: clusters of 2 CTAs, 256 x 256 tiles (wide_gemm2.cuh)
+template <bool A_K, bool B_K, int EPI>
+int launch_gemm2_t(wx_ctx* ctx, const CUtensorMap& ta, const CUtensorMap& tb, const GemmArgs& g, cudaStream_t st) {
+    static bool attr_set[64] = {};
+    if (!attr_set[ctx->device & 63]) {
+        WX_CUDA(cudaFuncSetAttribute(wide_gemm2_kernel<A_K, B_K, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     int(GEMM2_SMEM)));
+        attr_set[ctx->device & 63] = true;
+    }
+    const int64_t tiles = (g.M / (2 * BM)) * (g.N / BN);
+    const int64_t clusters = tiles < ctx->num_sms / 2 ? tiles : ctx->num_sms / 2;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(unsigned(clusters * 2));
+    cfg.blockDim = dim3(GEMM_THREADS);
+    cfg.dynamicSmemBytes = GEMM2_SMEM;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    WX_CUDA(cudaLaunchKernelEx(&cfg, wide_gemm2_kernel<A_K, B_K, EPI>, ta, tb, g));
+    WX_LAUNCH_CHECK(ctx);
+    return WX_OK;
+}
+
+bool two_sm_enabled() {
+    static int v = -1;
+    if (v < 0) {
+        const char* e = getenv("WX_WIDE_1CTA");      // developer switch for A/B timing of the two GEMM kernels
+        v = (e != nullptr && e[0] == '1') ? 0 : 1;
+    }
+    return v == 1;
+}
+
 // D[M,N] = op(A) op(B): a_k / b_k say whether the operand is stored [M|N, K] (true) or [K, M|N] (false), row-major bf16.
 int launch_gemm(wx_ctx* ctx, bool a_k, bool b_k, int epi, const void* A, int64_t lda, const void* B, int64_t ldb,
                 GemmArgs g, cudaStream_t st) {
     CUtensorMap ta, tb;
     int rc;
+    if (g.split_k < 1) g.split_k = 1;
+    if (two_sm_enabled() && g.split_k == 1 && g.M % (2 * BM) == 0 && g.N % BN == 0 && epi != EPI_PLAIN + 100) {
+        // big aligned products: cluster pairs, each CTA stages its 128 rows of A and its 128-column half of B
+        if (a_k) rc = make_map(&ta, A, g.M, g.K, lda, BM);
+        else rc = make_map(&ta, A, g.K, g.M, lda, 64, BM / 64);
+        if (rc != WX_OK) return rc;
+        if (b_k) rc = make_map(&tb, B, g.N, g.K, ldb, BN / 2);
+        else rc = make_map(&tb, B, g.K, g.N, ldb, 64, BN / 128);
+        if (rc != WX_OK) return rc;
+        g.err = reinterpret_cast<int*>(ctx->scratch) + 8;
+        if (a_k && b_k) {
+            if (epi == EPI_FWD) return launch_gemm2_t<true, true, EPI_FWD>(ctx, ta, tb, g, st);
+            if (epi == EPI_PLAIN) return launch_gemm2_t<true, true, EPI_PLAIN>(ctx, ta, tb, g, st);
+        } else if (a_k && !b_k) {
+            if (epi == EPI_DX) return launch_gemm2_t<true, false, EPI_DX>(ctx, ta, tb, g, st);
+            if (epi == EPI_PLAIN) return launch_gemm2_t<true, false, EPI_PLAIN>(ctx, ta, tb, g, st);
+        } else if (!a_k && !b_k) {
+            if (epi == EPI_DW) return launch_gemm2_t<false, false, EPI_DW>(ctx, ta, tb, g, st);
+            if (epi == EPI_PLAIN) return launch_gemm2_t<false, false, EPI_PLAIN>(ctx, ta, tb, g, st);
+        }
+    }
     if (a_k) rc = make_map(&ta, A, g.M, g.K, lda, BM);
     else rc = make_map(&ta, A, g.K, g.M, lda, 64, BM / 64);
     if (rc != WX_OK) return rc;

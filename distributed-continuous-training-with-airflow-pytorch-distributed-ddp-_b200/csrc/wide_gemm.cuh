@@ -109,6 +109,68 @@ __device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
     return *reinterpret_cast<uint32_t*>(&v);
 }
 
+// Fused pointwise work + store of one 16-column chunk of an accumulator row (shared by the 1-CTA and 2-CTA kernels).
+template <int EPI>
+__device__ __forceinline__ void epilogue_chunk(float (&v)[16], const GemmArgs& g, int64_t row, bool row_ok, int64_t col0,
+                                               int64_t out_off) {
+    if (EPI == EPI_FWD) {
+        uint32_t keep = 0xFFFFu;
+        if (g.keep_thresh16 < 65536u) {
+            keep = 0;
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                uint32_t r[4];
+                philox4(uint32_t(row), uint32_t((col0 >> 3) + h), g.layer, g.step, g.seed_lo, g.seed_hi, r);
+#pragma unroll
+                for (int e = 0; e < 8; ++e) {
+                    const uint32_t u = (r[e >> 1] >> (16 * (e & 1))) & 0xFFFFu;
+                    keep |= uint32_t(u < g.keep_thresh16) << (h * 8 + e);
+                }
+            }
+        }
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+            float z = v[i] + (g.bias ? __ldg(g.bias + col0 + i) : 0.0f);
+            z = fmaxf(z, 0.0f);
+            v[i] = ((keep >> i) & 1u) ? z * g.inv_keep : 0.0f;
+        }
+    } else if (EPI == EPI_DX) {
+        if (row_ok) {
+            const uint4* gp = reinterpret_cast<const uint4*>(g.gate + row * g.ldg + col0);
+            const uint4 g0 = __ldg(gp), g1 = __ldg(gp + 1);
+            const uint32_t gw[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
+#pragma unroll
+            for (int i = 0; i < 16; ++i) {
+                const uint32_t bits = (gw[i >> 1] >> (16 * (i & 1))) & 0xFFFFu;
+                const bool on = (bits & 0x7FFFu) != 0 && !(bits & 0x8000u);   // gate > 0
+                v[i] = on ? v[i] * g.inv_keep : 0.0f;
+            }
+        }
+    } else if (EPI == EPI_PLAIN) {
+        if (g.bias) {
+#pragma unroll
+            for (int i = 0; i < 16; ++i) v[i] += __ldg(g.bias + col0 + i);
+        }
+    }
+    if (row_ok) {
+        if (EPI == EPI_FWD || EPI == EPI_DX) {
+            __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(g.out) + row * g.ldo + col0;
+            uint4 o0, o1;
+            o0.x = pack_bf16(v[0], v[1]);   o0.y = pack_bf16(v[2], v[3]);
+            o0.z = pack_bf16(v[4], v[5]);   o0.w = pack_bf16(v[6], v[7]);
+            o1.x = pack_bf16(v[8], v[9]);   o1.y = pack_bf16(v[10], v[11]);
+            o1.z = pack_bf16(v[12], v[13]); o1.w = pack_bf16(v[14], v[15]);
+            reinterpret_cast<uint4*>(o)[0] = o0;
+            reinterpret_cast<uint4*>(o)[1] = o1;
+        } else {
+            float* o = reinterpret_cast<float*>(g.out) + out_off + row * g.ldo + col0;
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+                reinterpret_cast<float4*>(o)[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+        }
+    }
+}
+
 // A_K: A is [M x K] row-major (contraction contiguous); else A is [K x M] row-major.  Same for B with N.
 template <bool A_K, bool B_K, int EPI>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
@@ -232,62 +294,7 @@ wide_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                 wxtc::tmem_ld_wait();
                 const int64_t col0 = n0 + c * 16;
                 if (col0 >= g.N) break;                      // warp-uniform
-                if (EPI == EPI_FWD) {
-                    uint32_t keep = 0xFFFFu;
-                    if (g.keep_thresh16 < 65536u) {
-                        keep = 0;
-#pragma unroll
-                        for (int h = 0; h < 2; ++h) {
-                            uint32_t r[4];
-                            philox4(uint32_t(row), uint32_t((col0 >> 3) + h), g.layer, g.step, g.seed_lo, g.seed_hi, r);
-#pragma unroll
-                            for (int e = 0; e < 8; ++e) {
-                                const uint32_t u = (r[e >> 1] >> (16 * (e & 1))) & 0xFFFFu;
-                                keep |= uint32_t(u < g.keep_thresh16) << (h * 8 + e);
-                            }
-                        }
-                    }
-#pragma unroll
-                    for (int i = 0; i < 16; ++i) {
-                        float z = v[i] + (g.bias ? __ldg(g.bias + col0 + i) : 0.0f);
-                        z = fmaxf(z, 0.0f);
-                        v[i] = ((keep >> i) & 1u) ? z * g.inv_keep : 0.0f;
-                    }
-                } else if (EPI == EPI_DX) {
-                    if (row_ok) {
-                        const uint4* gp = reinterpret_cast<const uint4*>(g.gate + row * g.ldg + col0);
-                        const uint4 g0 = __ldg(gp), g1 = __ldg(gp + 1);
-                        const uint32_t gw[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
-#pragma unroll
-                        for (int i = 0; i < 16; ++i) {
-                            const uint32_t bits = (gw[i >> 1] >> (16 * (i & 1))) & 0xFFFFu;
-                            const bool on = (bits & 0x7FFFu) != 0 && !(bits & 0x8000u);   // gate > 0
-                            v[i] = on ? v[i] * g.inv_keep : 0.0f;
-                        }
-                    }
-                } else if (EPI == EPI_PLAIN) {
-                    if (g.bias) {
-#pragma unroll
-                        for (int i = 0; i < 16; ++i) v[i] += __ldg(g.bias + col0 + i);
-                    }
-                }
-                if (row_ok) {
-                    if (EPI == EPI_FWD || EPI == EPI_DX) {
-                        __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(g.out) + row * g.ldo + col0;
-                        uint4 o0, o1;
-                        o0.x = pack_bf16(v[0], v[1]);   o0.y = pack_bf16(v[2], v[3]);
-                        o0.z = pack_bf16(v[4], v[5]);   o0.w = pack_bf16(v[6], v[7]);
-                        o1.x = pack_bf16(v[8], v[9]);   o1.y = pack_bf16(v[10], v[11]);
-                        o1.z = pack_bf16(v[12], v[13]); o1.w = pack_bf16(v[14], v[15]);
-                        reinterpret_cast<uint4*>(o)[0] = o0;
-                        reinterpret_cast<uint4*>(o)[1] = o1;
-                    } else {
-                        float* o = reinterpret_cast<float*>(g.out) + out_off + row * g.ldo + col0;
-#pragma unroll
-                        for (int i = 0; i < 4; ++i)
-                            reinterpret_cast<float4*>(o)[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
-                    }
-                }
+                epilogue_chunk<EPI>(v, g, row, row_ok, col0, out_off);
                 __syncwarp();
             }
             wxtc::tc_fence_before();
