@@ -26,8 +26,10 @@ def eng():
 
 
 @pytest.mark.parametrize("m,n,k", [(128, 256, 64), (256, 512, 128), (384, 256, 320), (128, 768, 512), (4096, 64, 384),
-                                   (200, 48, 64)])
+                                   (200, 48, 64), (512, 512, 256), (256, 768, 1024), (1024, 256, 64)])
 def test_gemm_three_operand_layouts(eng, m, n, k):
+    """M % 256 == 0 and N % 256 == 0 take the two-SM kernel (cta_group::2, 256 x 256 tiles per CTA pair), everything
+    else the one-CTA kernel; both must agree with a float32 matmul of the same bf16 operands."""
     torch.manual_seed(m + n + k)
     a = torch.randn(m, k, device="cuda").bfloat16()
     b = torch.randn(n, k, device="cuda").bfloat16()
