@@ -44,7 +44,7 @@ struct Layout {
     int64_t P;                    // number of fp32 parameters
     int64_t off_w[8], off_b[8];   // parameter offsets of hidden layer l = 1..L (index l), head at index L+1
     size_t wb[8];                 // workspace byte offsets: bf16 weights of hidden layer l
-    size_t x0, h[8], dz[2], dlog, part, dw1tmp, total;
+    size_t x0, h[8], dz[2], dlog, part, dw1tmp, dwtmp[8], total;
 };
 
 size_t align_up(size_t v) { return (v + 1023) & ~size_t(1023); }
@@ -86,6 +86,10 @@ int make_layout(const wx_wide_desc* d, int64_t batch, Layout* L) {
     w = align_up(w + size_t(HEAD_SLABS) * 2 * H * 4 + size_t(4096) * 4 * 4);
     L->dw1tmp = w;
     w = align_up(w + size_t(MAX_SPLIT_K) * H * KPAD * 4);
+    for (int l = 2; l <= nl; ++l) {   // second split-K slab of dW_l (wave quantisation: see wx_wide_backward_layer)
+        L->dwtmp[l] = w;
+        w = align_up(w + size_t(H) * H * 4);
+    }
     L->total = w;
     return 0;
 }
@@ -276,6 +280,16 @@ __global__ void __launch_bounds__(256) wide_colsum_kernel(const __nv_bfloat16* _
     for (int i = 0; i < 8; ++i) p[c8 * 8 + i] = a[i];
 }
 
+// dst[i] += src[i] (second split-K slab of a weight gradient)
+__global__ void __launch_bounds__(256) wide_add_kernel(float* __restrict__ dst, const float* __restrict__ src, int64_t n4) {
+    for (int64_t i = int64_t(blockIdx.x) * blockDim.x + threadIdx.x; i < n4; i += int64_t(gridDim.x) * blockDim.x) {
+        float4 a = reinterpret_cast<float4*>(dst)[i];
+        const float4 b = __ldg(reinterpret_cast<const float4*>(src) + i);
+        a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w;
+        reinterpret_cast<float4*>(dst)[i] = a;
+    }
+}
+
 // out[i] = sum over parts (in order) of part[p * stride + i]
 __global__ void __launch_bounds__(256) wide_reduce_kernel(const float* __restrict__ part, int n_parts, int64_t stride,
                                                          int64_t n, float* __restrict__ out) {
@@ -437,7 +451,7 @@ int launch_gemm2_t(wx_ctx* ctx, const CUtensorMap& ta, const CUtensorMap& tb, co
                                      int(GEMM2_SMEM)));
         attr_set[ctx->device & 63] = true;
     }
-    const int64_t tiles = (g.M / (2 * BM)) * (g.N / BN);
+    const int64_t tiles = (g.M / (2 * BM)) * (g.N / BN) * g.split_k;
     const int64_t clusters = tiles < ctx->num_sms / 2 ? tiles : ctx->num_sms / 2;
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(unsigned(clusters * 2));
@@ -471,7 +485,7 @@ int launch_gemm(wx_ctx* ctx, bool a_k, bool b_k, int epi, const void* A, int64_t
     CUtensorMap ta, tb;
     int rc;
     if (g.split_k < 1) g.split_k = 1;
-    if (two_sm_enabled() && g.split_k == 1 && g.M % (2 * BM) == 0 && g.N % BN == 0 && epi != EPI_PLAIN + 100) {
+    if (two_sm_enabled() && g.M % (2 * BM) == 0 && g.N % BN == 0 && (g.split_k == 1 || epi == EPI_DW || epi == EPI_PLAIN)) {
         // big aligned products: cluster pairs, each CTA stages its 128 rows of A and its 128-column half of B
         if (a_k) rc = make_map(&ta, A, g.M, g.K, lda, BM);
         else rc = make_map(&ta, A, g.K, g.M, lda, 64, BM / 64);
@@ -511,6 +525,18 @@ int launch_gemm(wx_ctx* ctx, bool a_k, bool b_k, int epi, const void* A, int64_t
     }
     wx_set_error("wide gemm: unsupported layout/epilogue combination (a_k=%d b_k=%d epi=%d)", int(a_k), int(b_k), epi);
     return WX_EINVAL;
+}
+
+// Number of split-K slabs of dW_layer.  (H/256)^2 tile pairs rarely fill the SM pairs evenly (256 tiles on 74 pairs = 3.46
+// rounds at H = 4096): when the last round would be less than ~80 % full the batch is cut in two -- slab 0 is the gradient
+// itself, slab 1 a workspace buffer that WX_WIDE_DW_FOLD adds in (a separate piece so it can run off the GEMM stream).
+int dw_splits(const wx_ctx* ctx, const wx_wide_desc* d, int64_t batch, int layer) {
+    if (layer <= 1 || !two_sm_enabled()) return 1;
+    const int64_t H = d->hidden;
+    const int64_t tiles = (H / (2 * BM)) * (H / BN), pairs = ctx->num_sms / 2;
+    if (pairs < 1 || tiles < pairs || batch < 1024) return 1;
+    const double rounds = double(tiles) / double(pairs);
+    return (ceil(rounds) - rounds) > 0.2 ? 2 : 1;
 }
 
 AdamS adam_consts(const wx_wide_desc* d, int64_t step) {
@@ -686,7 +712,7 @@ int wx_wide_backward_layer(wx_ctx* ctx, const wx_wide_desc* desc, void* ws, int6
                  (long long)batch);
     const int nl = desc->n_hidden;
     WX_CHECK_ARG(layer >= 1 && layer <= nl, "wx_wide_backward_layer: layer=%d outside 1..%d", layer, nl);
-    WX_CHECK_ARG(parts >= 1 && parts <= 7, "wx_wide_backward_layer: parts=%d (bit 0 dW, bit 1 db, bit 2 dZ below)", parts);
+    WX_CHECK_ARG(parts >= 1 && parts <= 15, "wx_wide_backward_layer: parts=%d (bit 0 dW, bit 1 db, bit 2 dZ below, bit 3 fold)", parts);
     WX_CUDA(cudaSetDevice(ctx->device));
     Layout L;
     make_layout(desc, batch, &L);
@@ -713,6 +739,14 @@ int wx_wide_backward_layer(wx_ctx* ctx, const wx_wide_desc* desc, void* ws, int6
             g.out = w + L.dw1tmp; g.ldo = KPAD;
         } else {
             g.out = grads + L.off_w[layer]; g.ldo = H;
+            // (H/256)^2 tile pairs rarely fill the 74 SM pairs evenly (256 tiles = 3.46 rounds at H = 4096): when the last
+            // round would be less than ~80 % full, cut the batch in two -- slab 0 is the gradient itself, slab 1 a workspace
+            // buffer that WX_WIDE_DW_FOLD adds in (kept separate so the caller can run it off the GEMM stream)
+            splits = dw_splits(ctx, desc, batch, layer);
+            if (splits == 2) {
+                g.split_k = 2;
+                g.split_stride = (reinterpret_cast<float*>(w + L.dwtmp[layer]) - (grads + L.off_w[layer]));
+            }
         }
         rc = launch_gemm(ctx, false, false, EPI_DW, dz, H, h_below, in, g, st);
         if (rc != WX_OK) return rc;
@@ -721,6 +755,11 @@ int wx_wide_backward_layer(wx_ctx* ctx, const wx_wide_desc* desc, void* ws, int6
                 reinterpret_cast<const float*>(w + L.dw1tmp), H, desc->n_features, KPAD, splits, grads + L.off_w[1]);
             WX_LAUNCH_CHECK(ctx);
         }
+    }
+    if ((parts & WX_WIDE_DW_FOLD) && dw_splits(ctx, desc, batch, layer) == 2) {
+        wide_add_kernel<<<grid_for(ctx, H * H, 4), 256, 0, st>>>(grads + L.off_w[layer],
+                                                                reinterpret_cast<const float*>(w + L.dwtmp[layer]), H * H / 4);
+        WX_LAUNCH_CHECK(ctx);
     }
     // db = column sums of dZ
     if (parts & WX_WIDE_DB) {

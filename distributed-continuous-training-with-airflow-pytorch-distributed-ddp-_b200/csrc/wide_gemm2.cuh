@@ -86,9 +86,11 @@ wide_gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const uint32_t rank = cluster_ctarank();                 // 0 = leader
     const int64_t tiles_m = g.M / (2 * BM), tiles_n = g.N / BN;
-    const int64_t n_tiles = tiles_m * tiles_n;
+    const int64_t mn_tiles = tiles_m * tiles_n;
+    const int64_t n_tiles = mn_tiles * g.split_k;            // split-K: work unit = (split, tile), one output slab per split
     const int64_t cl = blockIdx.x >> 1, n_cl = gridDim.x >> 1;
     const int kb_total = int(g.K / BK);
+    const int kb_per = (kb_total + g.split_k - 1) / g.split_k;
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < STAGES2; ++s) {
@@ -115,9 +117,12 @@ wide_gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
             const bool is_a = warp == 0;
             uint32_t it = 0;
             for (int64_t tile = cl; tile < n_tiles && ok; tile += n_cl) {
-                const int32_t m0 = int32_t(tile / tiles_n) * 2 * BM + int32_t(rank) * BM;
-                const int32_t n0 = int32_t(tile % tiles_n) * BN + int32_t(rank) * (BN / 2);
-                for (int kb = 0; kb < kb_total; ++kb, ++it) {
+                const int64_t mn = tile % mn_tiles;
+                const int split = int(tile / mn_tiles);
+                const int32_t m0 = int32_t(mn / tiles_n) * 2 * BM + int32_t(rank) * BM;
+                const int32_t n0 = int32_t(mn % tiles_n) * BN + int32_t(rank) * (BN / 2);
+                const int kb0 = split * kb_per, kb1 = (kb0 + kb_per < kb_total) ? kb0 + kb_per : kb_total;
+                for (int kb = kb0; kb < kb1; ++kb, ++it) {
                     const int s = it % STAGES2;
                     if (it >= STAGES2 && !wxtc::mbar_wait_hot(&empty[s], ((it / STAGES2) - 1) & 1)) { ok = false; break; }
                     if (is_a) {
@@ -145,7 +150,9 @@ wide_gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
                 if (local >= 2 && !wxtc::mbar_wait_hot(&tmem_empty[acc], ((local >> 1) - 1) & 1)) { ok = false; break; }
                 wxtc::tc_fence_after();
                 const uint32_t d_tmem = tmem_base + acc * BN;
-                for (int kb = 0; kb < kb_total; ++kb, ++it) {
+                const int split = int(tile / mn_tiles);
+                const int kb0 = split * kb_per, kb1 = (kb0 + kb_per < kb_total) ? kb0 + kb_per : kb_total;
+                for (int kb = kb0; kb < kb1; ++kb, ++it) {
                     const int s = it % STAGES2;
                     if (!wxtc::mbar_wait_hot(&full[s], (it / STAGES2) & 1)) { ok = false; break; }
                     wxtc::tc_fence_after();
@@ -157,7 +164,7 @@ wide_gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
                                                 : wxtc::make_smem_desc(a_addr + k * 2048, 8192, 1024);
                         const uint64_t bd = B_K ? wxtc::make_smem_desc(b_addr + k * 32, 16, 1024)
                                                 : wxtc::make_smem_desc(b_addr + k * 2048, 8192, 1024);
-                        umma2_bf16(d_tmem, ad, bd, idesc, (kb | k) != 0);
+                        umma2_bf16(d_tmem, ad, bd, idesc, ((kb - kb0) | k) != 0);
                     }
                     umma2_commit_both(&empty[s]);
                 }
@@ -173,7 +180,9 @@ wide_gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
         uint32_t local = 0;
         for (int64_t tile = cl; tile < n_tiles; tile += n_cl, ++local) {
             const uint32_t acc = local & 1;
-            const int64_t m0 = (tile / tiles_n) * 2 * BM + int64_t(rank) * BM, n0 = (tile % tiles_n) * BN;
+            const int64_t mn = tile % mn_tiles;
+            const int64_t m0 = (mn / tiles_n) * 2 * BM + int64_t(rank) * BM, n0 = (mn % tiles_n) * BN;
+            const int64_t out_off = (tile / mn_tiles) * g.split_stride;
             if (!wxtc::mbar_wait(&tmem_full[acc], (local >> 1) & 1)) {
                 if (lane == 0) atomicExch(g.err, 213);
                 break;
@@ -186,7 +195,7 @@ wide_gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
                 float v[16];
                 wxtc::tmem_ld16(tmem_base + (uint32_t(q * 32) << 16) + acc * BN + c * 16, v);
                 wxtc::tmem_ld_wait();
-                epilogue_chunk<EPI>(v, g, row, row_ok, n0 + c * 16, 0);
+                epilogue_chunk<EPI>(v, g, row, row_ok, n0 + c * 16, out_off);
                 __syncwarp();
             }
             wxtc::tc_fence_before();

@@ -153,6 +153,7 @@ class WideEngine:
             db_done[layer].record(side)
             check(lib.wx_wide_backward_layer(h, d, ws, b, layer, dropout, 1, g, mst))          # dW
             after_main()
+            check(lib.wx_wide_backward_layer(h, d, ws, b, layer, dropout, 8, g, sst))          # fold split-K slab (side)
             reduce_slice(*self.slices[layer - 1])             # starts as soon as dW is final, under the dZ product
             if layer > 1:
                 if layer + 1 in db_done:

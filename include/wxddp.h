@@ -271,7 +271,8 @@ int wx_wide_forward(wx_ctx* ctx, const wx_wide_desc* desc, const float* params, 
 #define WX_WIDE_DW 1 /* weight gradient of the layer */
 #define WX_WIDE_DB 2 /* bias gradient (column sums of dZ) */
 #define WX_WIDE_DZ 4 /* dZ of the layer below (skipped for layer 1) */
-#define WX_WIDE_ALL 7
+#define WX_WIDE_DW_FOLD 8 /* add the second split-K slab of dW into the gradient (no-op when dW was not split); must follow DW */
+#define WX_WIDE_ALL 15
 int wx_wide_backward_layer(wx_ctx* ctx, const wx_wide_desc* desc, void* ws, int64_t batch, int layer, int dropout_mode,
                            int parts, float* grads, void* stream);
 /* Adam over all P parameters (step is 1-based), rewriting the bf16 weight copies in ws in the same pass. */

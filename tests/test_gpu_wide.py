@@ -78,6 +78,26 @@ def test_step_gradients_match_oracle(eng, dropout, batch):
     assert cos > 0.999, cos
 
 
+def test_split_k_weight_gradient_at_large_hidden():
+    """hidden 2560 -> 100 tile pairs on 74 SM pairs: the dW products are cut in two along the batch and folded on the side
+    stream; the result must still match the oracle (and be reproducible bit for bit)."""
+    from wxddp.wide import WideEngine
+
+    f, h, nl, b = 20, 2560, 2, 1024
+    torch.manual_seed(11)
+    e = WideEngine(f, h, nl, max_batch=b, device=0)
+    x = torch.randn(b, f)
+    y = (torch.rand(b) < 0.3).long()
+    got = e.loss_and_grads(x.cuda(), y.cuda(), dropout=2, step=2).clone()
+    again = e.loss_and_grads(x.cuda(), y.cuda(), dropout=2, step=2).clone()
+    assert torch.equal(got, again) and e.status() == 0
+    want = wide_ref.loss_and_grads(e.params.cpu(), x, y, f, h, nl, dropout=True, seed=e.seed, step=2)
+    got = got.cpu()
+    np.testing.assert_allclose(float(got[-1]), float(want[-1]), rtol=1e-4)
+    for lo, hi in e.slices + [(e.head_slice[0], e.P)]:
+        assert rel(got[lo:hi], want[lo:hi]) < 1e-3 + 1.5 / b, (lo, hi)
+
+
 def test_grad_scale_and_dropout_stream_depend_on_step(eng):
     x = torch.randn(256, eng.F, device="cuda")
     y = (torch.rand(256, device="cuda") < 0.5).long()
