@@ -77,6 +77,7 @@ SIGNATURES = {
     "wx_wide_backward_layer": (_int, [_vp, C.POINTER(WideDesc), _vp, _i64, _int, _int, _int, _vp, _vp]),
     "wx_wide_adam_layer": (_int, [_vp, C.POINTER(WideDesc), _vp, _vp, _vp, _vp, _i64, _vp, _int, _vp]),
     "wx_wide_adam": (_int, [_vp, C.POINTER(WideDesc), _vp, _vp, _vp, _vp, _i64, _vp, _vp]),
+    "wx_wide_reserve_sms": (_int, [_vp, _int]),
     "wx_wide_eval": (_int, [_vp, C.POINTER(WideDesc), _vp, _vp, _vp, _vp, _i64, _vp, _vp]),
     "wx_wide_gemm": (_int, [_vp, _int, _int, _vp, _i64, _vp, _i64, _i64, _i64, _i64, _vp, _vp, _vp]),
 }

@@ -31,6 +31,7 @@ struct wx_ctx {
     unsigned char* inbox;     // this rank's peer inbox (wx_peer_export), NULL until exported
     wxpeer::PeerArgs peer;    // world <= 1 until wx_peer_connect
     void* peer_mapped[wxpeer::MAXW];   // cudaIpcOpenMemHandle results to close at destroy
+    int wide_reserved_sms;    // SMs the wide GEMMs leave free for a concurrent collective (wx_wide_reserve_sms), default 0
 };
 
 void wx_set_error(const char* fmt, ...);

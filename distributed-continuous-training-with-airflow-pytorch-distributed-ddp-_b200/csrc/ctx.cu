@@ -45,6 +45,7 @@ int wx_create(int device, const wx_model_desc* desc, wx_ctx** out) {
     c->n_params = int64_t(WX_HIDDEN) * desc->n_features + WX_HIDDEN + WX_CLASSES * WX_HIDDEN + WX_CLASSES;
     c->scratch_bytes = WX_SCRATCH_BYTES;
     c->launches = 0;
+    c->wide_reserved_sms = 0;
     c->debug_times = nullptr;
     c->inbox = nullptr;
     memset(&c->peer, 0, sizeof(c->peer));

@@ -436,7 +436,8 @@ int launch_gemm_t(wx_ctx* ctx, const CUtensorMap& ta, const CUtensorMap& tb, con
         attr_set[ctx->device & 63] = true;
     }
     const int64_t tiles = ((g.M + BM - 1) / BM) * ((g.N + BN - 1) / BN) * g.split_k;
-    const int grid = int(tiles < ctx->num_sms ? tiles : ctx->num_sms);
+    const int64_t sms = ctx->num_sms - ctx->wide_reserved_sms;
+    const int grid = int(tiles < sms ? tiles : sms);
     wide_gemm_kernel<A_K, B_K, EPI><<<grid, GEMM_THREADS, GEMM_SMEM, st>>>(ta, tb, g);
     WX_LAUNCH_CHECK(ctx);
     return WX_OK;
@@ -452,7 +453,8 @@ int launch_gemm2_t(wx_ctx* ctx, const CUtensorMap& ta, const CUtensorMap& tb, co
         attr_set[ctx->device & 63] = true;
     }
     const int64_t tiles = (g.M / (2 * BM)) * (g.N / BN) * g.split_k;
-    const int64_t clusters = tiles < ctx->num_sms / 2 ? tiles : ctx->num_sms / 2;
+    const int64_t pairs = (ctx->num_sms - ctx->wide_reserved_sms) / 2;
+    const int64_t clusters = tiles < pairs ? tiles : pairs;
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(unsigned(clusters * 2));
     cfg.blockDim = dim3(GEMM_THREADS);
@@ -533,7 +535,7 @@ int launch_gemm(wx_ctx* ctx, bool a_k, bool b_k, int epi, const void* A, int64_t
 int dw_splits(const wx_ctx* ctx, const wx_wide_desc* d, int64_t batch, int layer) {
     if (layer <= 1 || !two_sm_enabled()) return 1;
     const int64_t H = d->hidden;
-    const int64_t tiles = (H / (2 * BM)) * (H / BN), pairs = ctx->num_sms / 2;
+    const int64_t tiles = (H / (2 * BM)) * (H / BN), pairs = (ctx->num_sms - ctx->wide_reserved_sms) / 2;
     if (pairs < 1 || tiles < pairs || batch < 1024) return 1;
     const double rounds = double(tiles) / double(pairs);
     return (ceil(rounds) - rounds) > 0.2 ? 2 : 1;
@@ -853,6 +855,15 @@ int wx_wide_eval(wx_ctx* ctx, const wx_wide_desc* desc, const float* params, voi
     WX_LAUNCH_CHECK(ctx);
     wide_head_finish_kernel<<<1, 256, 0, st>>>(head_part, hgrid, nullptr, out, out + 1);
     WX_LAUNCH_CHECK(ctx);
+    return WX_OK;
+}
+
+/* Leave `n` SMs (0..64, even) out of the wide GEMM grids so a collective running on another stream (the per-layer gradient
+ * all-reduce) always has somewhere to run instead of queueing behind one-CTA-per-SM persistent kernels. */
+int wx_wide_reserve_sms(wx_ctx* ctx, int n) {
+    WX_CHECK_ARG(ctx != nullptr, "wx_wide_reserve_sms: ctx is NULL");
+    WX_CHECK_ARG(n >= 0 && n <= 64 && n % 2 == 0 && n < ctx->num_sms, "wx_wide_reserve_sms: n=%d must be even, in 0..64", n);
+    ctx->wide_reserved_sms = n;
     return WX_OK;
 }
 

@@ -8,6 +8,7 @@ bucketed by layer: the all-reduce of layer l's slice runs on a side stream while
 from __future__ import annotations
 
 import ctypes as C
+import os
 
 import torch
 
@@ -64,6 +65,11 @@ class WideEngine:
             self.slices.append((off, off + n))
             off += n
         self.head_slice = (off, self.P + 1)
+        # under DDP the GEMM grids leave 16 SMs to NCCL, whose kernels otherwise queue behind the one-CTA-per-SM persistent
+        # GEMMs (8 GPUs: 3.10 -> 2.92 ms/step; profiles/r1_batch_sweep_and_wide.md)
+        reserve = int(os.environ.get("WX_WIDE_RESERVE_SMS", "16" if world > 1 else "0"))
+        if reserve:
+            check(self.lib.wx_wide_reserve_sms(self._h, reserve))
         self.cast_weights()
 
     def __del__(self):

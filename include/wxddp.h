@@ -281,6 +281,8 @@ int wx_wide_adam(wx_ctx* ctx, const wx_wide_desc* desc, float* params, const flo
 /* The same for one layer's tensors (layer 1..n_hidden, n_hidden+1 = head), e.g. on a side stream once that slice is final. */
 int wx_wide_adam_layer(wx_ctx* ctx, const wx_wide_desc* desc, float* params, const float* grads, float* m, float* v,
                        int64_t step, void* ws, int layer, void* stream);
+/* Keep `n` SMs (even, 0..64; default 0) out of the wide GEMM grids, for a collective that runs concurrently on another stream. */
+int wx_wide_reserve_sms(wx_ctx* ctx, int n);
 /* Validation pass of the wide net (the :73-85 pattern): eval-mode forward, out[0] = sum of per-row CE, out[1] = number of
  * rows whose argmax equals the label (fp32 device scalars; first index wins a tie, as torch.argmax). */
 int wx_wide_eval(wx_ctx* ctx, const wx_wide_desc* desc, const float* params, void* ws, const float* x, const int64_t* y,
