@@ -282,8 +282,9 @@ def run_wide(args, rank: int, local_rank: int, world: int) -> int:
     step_s = (ms / 1e3) / args.steps
     achieved = B * flops_per_row / step_s / 1e12
     roof = {"bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak,
-            "traffic": None, "kernel": "wide_gemm_kernel (tcgen05.mma kind::f16, 128x256x64 tiles, TMA 128B-swizzle "
-                                       "tensor maps, TMEM double buffer): 8 launches per step, ~90% of the step",
+            "traffic": None, "kernel": "wide_gemm2_kernel (tcgen05.mma.cta_group::2 kind::f16, 256x256x64 tiles per SM pair, TMA "
+                                       "128B-swizzle tensor maps, 6-stage ring, TMEM double buffer): 7 of the 8 GEMM launches "
+                                       "per step; bias gradients, all-reduce and Adam run on a side stream under them",
             "peak_source": peak_src, "algorithmic_flops_per_row": flops_per_row,
             "note": "achieved = algorithmic FLOPs of the whole step / step time, i.e. it charges the head, bias-gradient, "
                     "cast and Adam kernels and the DDP exchange to the GEMMs"}
