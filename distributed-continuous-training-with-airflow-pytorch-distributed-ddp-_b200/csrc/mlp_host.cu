@@ -25,6 +25,16 @@ small_kernel_t pick_small_kernel(int f, int* smem) {
     }
 }
 
+small_kernel_t pick_resident_kernel(int f, int* smem) {
+    switch ((f - 1) / 8) {
+        case 0: return pick_resident_kernel_g0(f, smem);
+        case 1: return pick_resident_kernel_g1(f, smem);
+        case 2: return pick_resident_kernel_g2(f, smem);
+        case 3: return pick_resident_kernel_g3(f, smem);
+        default: return nullptr;
+    }
+}
+
 int launch_grid(wx_ctx* ctx, GridArgs& a, int mode, cudaStream_t st, const char* who) {
     const int f = ctx->desc.n_features;
     int smem = 0;
@@ -204,8 +214,9 @@ int wx_train_steps_small(wx_ctx* ctx, float* params, float* m, float* v, int64_t
                          int dropout_mode, const uint64_t* keep_mask, uint64_t seed, float* loss_out, void* stream) {
     WX_CHECK_ARG(ctx != nullptr, "wx_train_steps_small: ctx is NULL");
     WX_CHECK_ARG(params && m && v && state && x && y && loss_out, "wx_train_steps_small: NULL pointer");
-    WX_CHECK_ARG(batch >= 1 && batch <= WARPS * R, "wx_train_steps_small: batch=%lld outside 1..%d (use wx_train_step)",
-                 (long long)batch, WARPS * R);
+    WX_CHECK_ARG(batch >= 1 && batch <= WX_RESIDENT_MAX_BATCH,
+                 "wx_train_steps_small: batch=%lld outside 1..%d (use wx_train_step)", (long long)batch,
+                 WX_RESIDENT_MAX_BATCH);
     WX_CHECK_ARG(n_steps >= 0, "wx_train_steps_small: n_steps < 0");
     WX_CHECK_ARG(row_idx != nullptr || row0 >= 0, "wx_train_steps_small: row0 < 0");
     int rc = check_dropout(ctx, dropout_mode, keep_mask, "wx_train_steps_small");
@@ -229,9 +240,35 @@ int wx_train_steps_small(wx_ctx* ctx, float* params, float* m, float* v, int64_t
     sa.seed = seed;
     sa.loss_out = loss_out;
     int smem = 0;
+    WX_CUDA(cudaSetDevice(ctx->device));
+    if (batch > WARPS * R) {
+        // more rows than one CTA's eight warps take in a pass: the resident multi-CTA kernel (grid barrier per step)
+        small_kernel_t kr = pick_resident_kernel(ctx->desc.n_features, &smem);
+        WX_CHECK_ARG(kr != nullptr, "wx_train_steps_small: no kernel for F=%d", ctx->desc.n_features);
+        const int64_t nchunks = (batch + R - 1) / R;
+        int64_t g = (nchunks + WARPS - 1) / WARPS;                 // one chunk per warp while the CTAs last ...
+        const int64_t gmax = ctx->num_sms < 32 ? ctx->num_sms : 32;  // ... but every CTA reads every slab: keep it to 32
+        if (g > gmax) g = gmax;
+        const int64_t cpc = (nchunks + g - 1) / g;
+        g = (nchunks + cpc - 1) / cpc;                             // no CTA without work
+        const size_t slab = (size_t(64) * ctx->desc.n_features + 194 + 1 + 3) & ~size_t(3);
+        if (WX_SCRATCH_PART_OFF + 2 * size_t(g) * slab * 4 > ctx->scratch_bytes) {
+            wx_set_error("wx_train_steps_small: scratch too small");
+            return WX_ENOMEM;
+        }
+        sa.part = reinterpret_cast<float*>(ctx->scratch + WX_SCRATCH_PART_OFF);
+        sa.bar = reinterpret_cast<unsigned long long*>(ctx->scratch + 128);     // bytes [128,136) of the ticket block
+        sa.err = reinterpret_cast<int*>(ctx->scratch) + 8;
+        cudaStream_t st = (cudaStream_t)stream;
+        WX_CUDA(cudaMemsetAsync(sa.bar, 0, sizeof(unsigned long long), st));
+        WX_CUDA(cudaFuncSetAttribute(reinterpret_cast<const void*>(kr), cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        void* rargs[] = {&sa};
+        WX_CUDA(cudaLaunchCooperativeKernel(reinterpret_cast<const void*>(kr), dim3((unsigned)g), dim3(THREADS), rargs, smem, st));
+        WX_LAUNCH_CHECK(ctx);
+        return WX_OK;
+    }
     small_kernel_t k = pick_small_kernel(ctx->desc.n_features, &smem);
     WX_CHECK_ARG(k != nullptr, "wx_train_steps_small: no kernel for F=%d", ctx->desc.n_features);
-    WX_CUDA(cudaSetDevice(ctx->device));
     WX_CUDA(cudaFuncSetAttribute(reinterpret_cast<const void*>(k), cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     void* args[] = {&sa};
     WX_CUDA(cudaLaunchKernel(reinterpret_cast<const void*>(k), dim3(1), dim3(THREADS), args, smem, (cudaStream_t)stream));

@@ -49,4 +49,16 @@ small_kernel_t WX_CAT(pick_small_kernel_g, WX_F_GROUP)(int f, int* smem) {
     }
 }
 
+small_kernel_t WX_CAT(pick_resident_kernel_g, WX_F_GROUP)(int f, int* smem) {
+    switch (f) {
+#define X(FV)                                                                       \
+    case FV:                                                                        \
+        *smem = (4 * Dim<FV>::SLAB + WARPS * 2 * R * Dim<FV>::FS) * 4;              \
+        return mlp_resident_steps_kernel<FV>;
+        WX_GROUP_F(X)
+#undef X
+        default: return nullptr;
+    }
+}
+
 }  // namespace wxk

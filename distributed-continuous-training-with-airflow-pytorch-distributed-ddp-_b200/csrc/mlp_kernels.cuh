@@ -428,6 +428,10 @@ struct SmallArgs {
     const uint64_t* keep_mask;
     uint64_t seed;
     float* loss_out;
+    // resident multi-CTA variant only:
+    float* part;                    // [2][gridDim.x][slab_stride] CTA partial sums, double-buffered by step parity
+    unsigned long long* bar;        // grid barrier counter, zero at launch
+    int* err;                       // sticky status word
 };
 
 template <int F>
@@ -520,6 +524,134 @@ __global__ void __launch_bounds__(THREADS, 1) mlp_small_steps_kernel(const Small
 }
 
 
+// The same many-steps-per-launch idea for batches that need more than one CTA (64 < batch <= 8192 or so: the
+// latency-bound end of the batch sweep, BASELINE.json configs[4]).  gridDim.x CTAs stay resident (cooperative launch) and
+// every one of them keeps params / m / v in shared memory.  Per step: each CTA processes its contiguous range of 8-row
+// chunks (warps double-buffer their chunks with cp.async), folds its warps into a CTA slab in warp order, publishes the
+// slab to global memory (two buffers, by step parity), crosses ONE grid barrier, then every CTA adds all slabs in CTA
+// order and applies Adam to its own copy -- identical arithmetic everywhere, so the copies never diverge and no second
+// barrier or broadcast is needed.  CTA 0 writes the losses and, at the end, the parameters.
+template <int F>
+__global__ void __launch_bounds__(THREADS, 1) mlp_resident_steps_kernel(const SmallArgs sa) {
+    using D = Dim<F>;
+    extern __shared__ __align__(16) unsigned char smem[];
+    float* s_p = reinterpret_cast<float*>(smem);
+    float* s_m = s_p + D::SLAB;
+    float* s_v = s_m + D::SLAB;
+    float* slab = s_v + D::SLAB;
+    float* stage_base = slab + D::SLAB;                    // [WARPS][2][R*FS]
+    __shared__ AdamScalars s_adam;
+    __shared__ int s_fail;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int G = int(gridDim.x);
+    for (int i = tid; i < D::P; i += THREADS) {
+        s_p[i] = sa.params[i];
+        s_m[i] = sa.m[i];
+        s_v[i] = sa.v[i];
+    }
+    if (tid == 0) s_fail = 0;
+    __syncthreads();
+    const int64_t step0 = sa.state[0];
+    const uint2 key = make_uint2(uint32_t(sa.seed), uint32_t(sa.seed >> 32));
+    const int64_t nchunks = (sa.batch + R - 1) / R;
+    const int64_t cpc = (nchunks + G - 1) / G;             // chunks per CTA (the host sizes G so that every CTA has work)
+    const int64_t c_lo = int64_t(blockIdx.x) * cpc;
+    const int64_t c_hi = (c_lo + cpc < nchunks) ? c_lo + cpc : nchunks;
+    const int n_active = int((c_hi - c_lo) < WARPS ? (c_hi - c_lo > 0 ? c_hi - c_lo : 0) : WARPS);
+    const float scale = 1.0f / float(sa.batch);
+    const float ds = (sa.dropout_mode == WX_DROPOUT_OFF) ? 1.0f : 1.25f;
+    float* stg0 = stage_base + warp * 2 * R * D::FS;
+    constexpr int SLAB_STRIDE = (D::P + 1 + 3) & ~3;
+
+    GridArgs ga;
+    ga.loader = LOAD_ROWMAJOR;
+    ga.x = sa.x;
+    ga.y = sa.y;
+    ga.batch = sa.batch;
+    ga.dropout_mode = sa.dropout_mode;
+
+    for (int64_t s = 0; s < sa.n_steps; ++s) {
+        ga.row_idx = sa.row_idx ? sa.row_idx + s * sa.batch : nullptr;
+        ga.row0 = sa.row0 + s * sa.batch;
+        ga.keep_mask = sa.keep_mask ? sa.keep_mask + s * sa.batch : nullptr;
+        if (warp < n_active) {
+            LaneState<F> st;
+            st.load_weights(s_p, lane);
+            st.zero_grads();
+            int64_t c = c_lo + warp;
+            ChunkMeta nxt = load_meta<F>(ga, c, lane);
+            stage_chunk<F, LOAD_ROWMAJOR>(ga, c, nxt, stg0, lane);
+            cp_async_commit();
+            int buf = 0;
+            const uint64_t step_word = uint64_t(step0 + s);
+            for (; c < c_hi; c += WARPS) {
+                const ChunkMeta cur = nxt;
+                const int64_t cn = c + WARPS;
+                if (cn < c_hi) {
+                    nxt = load_meta<F>(ga, cn, lane);
+                    stage_chunk<F, LOAD_ROWMAJOR>(ga, cn, nxt, stg0 + (buf ^ 1) * R * D::FS, lane);
+                }
+                cp_async_commit();
+                cp_async_wait<1>();
+                __syncwarp();
+                const uint32_t keepbits = chunk_keep_bits(sa.dropout_mode, cur, lane, c * R, key, uint32_t(step_word),
+                                                          uint32_t(step_word >> 32));
+                process_chunk<F, MODE_TRAIN>(st, stg0 + buf * R * D::FS, cur, keepbits, ds, scale, lane, nullptr);
+                __syncwarp();
+                buf ^= 1;
+            }
+            cp_async_wait<0>();
+            for (int w = 0; w < n_active; ++w) {                      // fold into the CTA slab in warp order
+                if (warp == w) st.flush_to_slab(slab, lane, w == 0);
+                asm volatile("bar.sync 1, %0;" ::"r"(n_active * 32) : "memory");
+            }
+        }
+        __syncthreads();
+        if (G > 1) {
+            float* mine = sa.part + (size_t(s & 1) * G + blockIdx.x) * SLAB_STRIDE;
+            for (int i = tid; i < D::P + 1; i += THREADS) mine[i] = slab[i];
+            __threadfence();
+            __syncthreads();
+            if (tid == 0) {
+                atomicAdd(sa.bar, 1ull);
+                const unsigned long long target = (unsigned long long)(s + 1) * G;
+                bool ok = false;
+                for (uint32_t spin = 0; spin < (1u << 26); ++spin) {
+                    unsigned long long seen;
+                    asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(seen) : "l"(sa.bar) : "memory");
+                    if (seen >= target) { ok = true; break; }
+                }
+                if (!ok) {
+                    s_fail = 1;
+                    atomicExch(sa.err, 30);                          // grid barrier never filled: CTAs not co-resident?
+                }
+            }
+            __syncthreads();
+            if (s_fail) return;
+            const float* all = sa.part + size_t(s & 1) * G * SLAB_STRIDE;
+            for (int i = tid; i < D::P + 1; i += THREADS) {
+                float t = 0.0f;
+                for (int g = 0; g < G; ++g) t += __ldcg(all + size_t(g) * SLAB_STRIDE + i);   // CTA order: same sum everywhere
+                slab[i] = t;
+            }
+        }
+        if (tid == 0) s_adam = adam_scalars(sa.desc, step0 + s + 1);
+        __syncthreads();
+        for (int i = tid; i < D::P; i += THREADS) adam_apply(s_p[i], slab[i], s_m[i], s_v[i], s_adam);
+        if (tid == 0 && blockIdx.x == 0) sa.loss_out[s] = slab[D::P] * scale;
+        __syncthreads();
+    }
+    if (blockIdx.x == 0) {
+        for (int i = tid; i < D::P; i += THREADS) {
+            sa.params[i] = s_p[i];
+            sa.m[i] = s_m[i];
+            sa.v[i] = s_v[i];
+        }
+        if (tid == 0) sa.state[0] = step0 + sa.n_steps;
+    }
+}
+
+
 typedef void (*grid_kernel_t)(const GridArgs);
 typedef void (*small_kernel_t)(const SmallArgs);
 
@@ -533,5 +665,9 @@ small_kernel_t pick_small_kernel_g0(int f, int* smem);
 small_kernel_t pick_small_kernel_g1(int f, int* smem);
 small_kernel_t pick_small_kernel_g2(int f, int* smem);
 small_kernel_t pick_small_kernel_g3(int f, int* smem);
+small_kernel_t pick_resident_kernel_g0(int f, int* smem);
+small_kernel_t pick_resident_kernel_g1(int f, int* smem);
+small_kernel_t pick_resident_kernel_g2(int f, int* smem);
+small_kernel_t pick_resident_kernel_g3(int f, int* smem);
 
 }  // namespace wxk

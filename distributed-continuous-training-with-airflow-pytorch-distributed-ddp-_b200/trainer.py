@@ -27,7 +27,7 @@ from .engine import StepEngine, init_params_like_reference
 from .surface import MetricLogger, TopOneCheckpoint, build_checkpoint
 
 SEED = 42                      # pl.seed_everything(42), train_lightning_ddp.py:14
-SMALL_BATCH_MAX = 64           # wx_train_steps_small limit
+SMALL_BATCH_MAX = 512          # many steps per launch pay off up to here (one CTA to 64 rows, resident multi-CTA above)
 STEPS_PER_LAUNCH = 4096
 
 

@@ -364,6 +364,43 @@ def test_small_steps_kernel_free_running_loss_curve(wx):
     np.testing.assert_allclose(out, losses.cpu().numpy(), rtol=1e-5)
 
 
+@pytest.mark.parametrize("f,batch,mode", [(5, 256, "mask"), (20, 1000, "philox"), (20, 4096, "philox"), (7, 72, "off"),
+                                          (20, 16384, "philox")])
+def test_resident_multi_cta_steps_equal_step_by_step_launches(wx, f, batch, mode):
+    """wx_train_steps_small with 64 < batch: several co-resident CTAs, one grid barrier per step.  Must reproduce the
+    same steps launched one by one through wx_train_step (same rows, same dropout bits), ragged last chunk included."""
+    torch.manual_seed(f + batch)
+    c = ctx_for(wx, f)
+    steps = 6
+    n = steps * batch + 5
+    x = torch.randn(n, f, device="cuda")
+    y = (torch.rand(n, device="cuda") < 0.3).long()
+    p0 = (torch.randn(c.P, device="cuda") * 0.2)
+    dm = {"mask": wx.DROPOUT_MASK, "philox": wx.DROPOUT_PHILOX, "off": wx.DROPOUT_OFF}[mode]
+    mk = None
+    if mode == "mask":
+        bits = (torch.rand(steps * batch, 64) < 0.8)
+        mk = mask_dev(np.packbits(bits.numpy(), axis=1, bitorder="little").view(np.uint64).reshape(-1))
+    idx = torch.randperm(n, device="cuda")[:steps * batch].contiguous() if f == 5 else None
+    p, m, v = p0.clone(), torch.zeros(c.P, device="cuda"), torch.zeros(c.P, device="cuda")
+    st = torch.zeros(2, dtype=torch.int64, device="cuda")
+    losses = torch.zeros(steps, device="cuda")
+    c.train_steps_small(p, m, v, st, x, y, losses, n_steps=steps, batch=batch, row_idx=idx, dropout=dm, keep_mask=mk, seed=9)
+    assert st[0].item() == steps and c.tc_status() == 0
+    p2, m2, v2 = p0.clone(), torch.zeros_like(m), torch.zeros_like(v)
+    st2 = torch.zeros(2, dtype=torch.int64, device="cuda"); l2 = torch.zeros(1, device="cuda")
+    want = []
+    for s in range(steps):
+        c.train_step(p2, m2, v2, st2, x, y, l2, row0=s * batch, batch=batch, dropout=dm, seed=9,
+                     row_idx=None if idx is None else idx[s * batch:(s + 1) * batch].contiguous(),
+                     keep_mask=None if mk is None else mk[s * batch:(s + 1) * batch].contiguous())
+        want.append(l2.item())
+    np.testing.assert_allclose(losses.cpu().numpy(), want, rtol=2e-5)
+    np.testing.assert_allclose(m.cpu().numpy(), m2.cpu().numpy(), rtol=2e-4, atol=1e-7)
+    # Adam moves a weight whose gradient is rounding noise by +-lr either way; compare where the two runs agree on m
+    np.testing.assert_allclose(p.cpu().numpy(), p2.cpu().numpy(), rtol=1e-3, atol=2e-4)
+
+
 @pytest.mark.parametrize("tag,f", [("F5", 5), ("F20", 20)])
 def test_eval_and_predict_match_reference_validation_step(wx, tag, f):
     g = load(f"eval_{tag}.npz")
