@@ -248,6 +248,37 @@ def test_col_stats_trend_and_outliers(wx):
         np.testing.assert_allclose(got[j, 3], s, rtol=1e-11)
 
 
+@pytest.mark.parametrize("f,n", [(20, 1000), (20, 256), (5, 777), (8, 513), (32, 300)])
+def test_k1_kernels_stay_inside_their_outputs(wx, f, n):
+    """Guard words around the outputs of wx_normalize_pack (TMA bulk store of the ragged last tile, vector stores) and
+    wx_label_encode (4 rows per thread): nothing outside [0, n) may be touched."""
+    c = ctx_for(wx, f)
+    t = synth.synth_table(5, n, f, null_rate=0.01)
+    cols = [dev(t["raw"][j].astype(np.float32)) for j in range(f)]
+    stats = c.col_stats(cols)
+    pad = 64
+    buf = torch.full((n * f + 2 * pad,), -12345.0, device="cuda")
+    nmb = torch.full((n + 2 * pad,), 0x5A5A5A5A, dtype=torch.int32, device="cuda")
+    out = buf[pad:pad + n * f].view(n, f)
+    from wxddp import _lib
+    check = _lib.check
+    check(c.lib.wx_normalize_pack(c._h, _lib.ptr_array([x.data_ptr() for x in cols]), 0, None, n, stats.data_ptr(), 1,
+                                  out.data_ptr(), nmb[pad:].data_ptr(), None))
+    torch.cuda.synchronize()
+    assert (buf[:pad] == -12345.0).all() and (buf[pad + n * f:] == -12345.0).all()
+    assert (nmb[:pad] == 0x5A5A5A5A).all() and (nmb[pad + n:] == 0x5A5A5A5A).all()
+    ref, _ = c.normalize_pack(cols, stats, impute=1)
+    assert torch.equal(out, ref)
+    off, data, valid = synth.to_arrow_strings(t["labels"])
+    offd, datad, validd = dev(off), dev(data), dev(valid)
+    lab = torch.full((n + 2 * pad,), -7, dtype=torch.int64, device="cuda")
+    check(c.lib.wx_label_encode(c._h, offd.data_ptr(), datad.data_ptr(), validd.data_ptr(), n, lab[pad:].data_ptr(), None,
+                                None))
+    torch.cuda.synchronize()
+    assert (lab[:pad] == -7).all() and (lab[pad + n:] == -7).all()
+    np.testing.assert_array_equal(lab[pad:pad + n].cpu().numpy(), preprocess_ref.label_encode(t["labels"]))
+
+
 def test_normalize_with_gpu_stats_within_one_ulp(wx):
     f, n = 20, 145_460
     t = synth.synth_table(1234, n, f, null_rate=0.0, const_col=f - 1)
