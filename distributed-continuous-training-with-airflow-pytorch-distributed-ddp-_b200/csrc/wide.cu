@@ -535,7 +535,7 @@ int launch_gemm(wx_ctx* ctx, bool a_k, bool b_k, int epi, const void* A, int64_t
 int dw_splits(const wx_ctx* ctx, const wx_wide_desc* d, int64_t batch, int layer) {
     if (layer <= 1 || !two_sm_enabled()) return 1;
     const int64_t H = d->hidden;
-    const int64_t tiles = (H / (2 * BM)) * (H / BN), pairs = (ctx->num_sms - ctx->wide_reserved_sms) / 2;
+    const int64_t tiles = (H / (2 * BM)) * (H / BN), pairs = ctx->num_sms / 2;   // NOT the reserved count: DW and FOLD calls must agree
     if (pairs < 1 || tiles < pairs || batch < 1024) return 1;
     const double rounds = double(tiles) / double(pairs);
     return (ceil(rounds) - rounds) > 0.2 ? 2 : 1;

@@ -67,9 +67,7 @@ class WideEngine:
         self.head_slice = (off, self.P + 1)
         # under DDP the GEMM grids leave 16 SMs to NCCL, whose kernels otherwise queue behind the one-CTA-per-SM persistent
         # GEMMs (8 GPUs: 3.10 -> 2.92 ms/step; profiles/r1_batch_sweep_and_wide.md)
-        reserve = int(os.environ.get("WX_WIDE_RESERVE_SMS", "16" if world > 1 else "0"))
-        if reserve:
-            check(self.lib.wx_wide_reserve_sms(self._h, reserve))
+        self._reserve = int(os.environ.get("WX_WIDE_RESERVE_SMS", "16" if world > 1 else "0"))
         self.cast_weights()
 
     def __del__(self):
@@ -146,6 +144,9 @@ class WideEngine:
                 check(lib.wx_wide_adam_layer(h, d, self.params.data_ptr(), g, self.m.data_ptr(), self.v.data_ptr(),
                                              adam_step, ws, layer, sst))
 
+        reserve = self._reserve if reduce else 0
+        if self._reserve:
+            check(lib.wx_wide_reserve_sms(h, 0))               # nothing else runs during the forward: all SMs
         check(lib.wx_wide_forward(h, d, self.params.data_ptr(), ws, x.data_ptr(), y.data_ptr(), b, dropout, self.seed, step,
                                   scale, g, mst))
         after_main()                                           # dZ_L, head gradients and the loss are enqueued
@@ -158,6 +159,8 @@ class WideEngine:
             db_done[layer] = torch.cuda.Event()
             db_done[layer].record(side)
             check(lib.wx_wide_backward_layer(h, d, ws, b, layer, dropout, 1, g, mst))          # dW
+            if reserve and layer == self.L:
+                check(lib.wx_wide_reserve_sms(h, reserve))     # from here on a big all-reduce is always in flight
             after_main()
             check(lib.wx_wide_backward_layer(h, d, ws, b, layer, dropout, 8, g, sst))          # fold split-K slab (side)
             reduce_slice(*self.slices[layer - 1])             # starts as soon as dW is final, under the dZ product
