@@ -450,7 +450,8 @@ def main() -> int:
             eng.connect_peers()
         n_host = 4
         host_cols = [torch.empty(f, B, dtype=torch.float32).pin_memory() for _ in range(n_host)]
-        host_y = [torch.empty(B, dtype=torch.int64).pin_memory() for _ in range(n_host)]
+        # labels travel as int32, the dtype Spark wrote them in (preprocess.py:24); the int64 cast of :46 happens on the device
+        host_y = [torch.empty(B, dtype=torch.int32).pin_memory() for _ in range(n_host)]
         for i in range(n_host):
             host_cols[i].copy_(raw[:, i * B:(i + 1) * B])
             host_y[i].copy_(y[i * B:(i + 1) * B])
@@ -473,9 +474,9 @@ def main() -> int:
         if world > 1:
             dist.all_reduce(tt, op=dist.ReduceOp.MAX)
         dt = float(tt.item())
-        e2e = {"value": args.steps * B * world / dt, "unit": UNIT, "h2d_bytes_per_step": B * (4 * f + 8),
+        e2e = {"value": args.steps * B * world / dt, "unit": UNIT, "h2d_bytes_per_step": B * (4 * f + 4),
                "d2h_bytes_per_step": 4, "ms_per_step": 1e3 * dt / args.steps, "last_loss": last,
-               "api": "wxddp.engine.StepEngine.submit_host(pinned raw columns, labels) -> loss of the previous step; drain() for the last (H2D of batch i overlaps the kernel of batch i-1)"}
+               "api": "wxddp.engine.StepEngine.submit_host(pinned raw fp32 columns, int32 labels) -> loss of the previous step; drain() for the last (H2D of batch i overlaps the kernel of batch i-1)"}
 
     if rank != 0:
         if world > 1:

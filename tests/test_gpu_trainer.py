@@ -200,6 +200,12 @@ def test_host_buffer_steps_sync_and_pipelined_agree():
             piped.append(r)
     piped.append(engines[2].drain())
     assert engines[2].drain() is None
+    # int32 labels (the dtype Spark wrote) through the same pipeline: widened on the device, same losses
+    e32 = StepEngine(f, device=0, params=p0)
+    e32.set_stats(stats)
+    got32 = [e32.submit_host(c, l.to(torch.int32).pin_memory()) for c, l in host]
+    got32 = [v for v in got32 if v is not None] + [e32.drain()]
+    assert got32 == piped
     assert sync == piped and len(piped) == n_steps
     assert torch.equal(engines[1].params, engines[2].params)
     # device-resident windows of one big table vs per-batch staging buffers: same rows, same kernel
