@@ -605,6 +605,7 @@ int wx_wide_cast_weights(wx_ctx* ctx, const wx_wide_desc* desc, const float* par
     WX_CHECK_ARG(ctx && params && ws, "wx_wide_cast_weights: NULL argument");
     int rc = check_desc(desc, "wx_wide_cast_weights");
     if (rc != WX_OK) return rc;
+    WX_CHECK_ARG((reinterpret_cast<uintptr_t>(ws) & 1023) == 0, "wx_wide_cast_weights: ws must be 1024-byte aligned");
     WX_CUDA(cudaSetDevice(ctx->device));
     Layout L;
     make_layout(desc, 128, &L);
@@ -666,6 +667,7 @@ int wx_wide_forward(wx_ctx* ctx, const wx_wide_desc* desc, const float* params, 
     WX_CHECK_ARG(ctx && params && ws && x && y && grads, "wx_wide_forward: NULL argument");
     int rc = check_desc(desc, "wx_wide_forward");
     if (rc != WX_OK) return rc;
+    WX_CHECK_ARG((reinterpret_cast<uintptr_t>(ws) & 1023) == 0, "wx_wide_forward: ws must be 1024-byte aligned");
     WX_CHECK_ARG(batch >= 128 && batch % 128 == 0, "wx_wide_forward: batch=%lld must be a positive multiple of 128",
                  (long long)batch);
     WX_CHECK_ARG(dropout_mode == WX_DROPOUT_OFF || dropout_mode == WX_DROPOUT_PHILOX,
@@ -710,6 +712,7 @@ int wx_wide_backward_layer(wx_ctx* ctx, const wx_wide_desc* desc, void* ws, int6
     WX_CHECK_ARG(ctx && ws && grads, "wx_wide_backward_layer: NULL argument");
     int rc = check_desc(desc, "wx_wide_backward_layer");
     if (rc != WX_OK) return rc;
+    WX_CHECK_ARG((reinterpret_cast<uintptr_t>(ws) & 1023) == 0, "wx_wide_backward_layer: ws must be 1024-byte aligned");
     WX_CHECK_ARG(batch >= 128 && batch % 128 == 0, "wx_wide_backward_layer: batch=%lld must be a positive multiple of 128",
                  (long long)batch);
     const int nl = desc->n_hidden;
@@ -794,6 +797,7 @@ int wx_wide_adam_layer(wx_ctx* ctx, const wx_wide_desc* desc, float* params, con
     WX_CHECK_ARG(ctx && params && grads && m && v && ws, "wx_wide_adam_layer: NULL argument");
     int rc = check_desc(desc, "wx_wide_adam_layer");
     if (rc != WX_OK) return rc;
+    WX_CHECK_ARG((reinterpret_cast<uintptr_t>(ws) & 1023) == 0, "wx_wide_adam_layer: ws must be 1024-byte aligned");
     WX_CHECK_ARG(step >= 1, "wx_wide_adam_layer: step=%lld must be >= 1", (long long)step);
     const int nl = desc->n_hidden;
     WX_CHECK_ARG(layer >= 1 && layer <= nl + 1, "wx_wide_adam_layer: layer=%d outside 1..%d (%d = head)", layer, nl + 1, nl + 1);
@@ -836,6 +840,7 @@ int wx_wide_eval(wx_ctx* ctx, const wx_wide_desc* desc, const float* params, voi
     WX_CHECK_ARG(ctx && params && ws && x && y && out, "wx_wide_eval: NULL argument");
     int rc = check_desc(desc, "wx_wide_eval");
     if (rc != WX_OK) return rc;
+    WX_CHECK_ARG((reinterpret_cast<uintptr_t>(ws) & 1023) == 0, "wx_wide_eval: ws must be 1024-byte aligned");
     WX_CHECK_ARG(batch >= 128 && batch % 128 == 0, "wx_wide_eval: batch=%lld must be a positive multiple of 128",
                  (long long)batch);
     WX_CUDA(cudaSetDevice(ctx->device));

@@ -37,7 +37,9 @@ class WideEngine:
         nbytes = int(self.lib.wx_wide_workspace_bytes(C.byref(self.desc), max_batch))
         if nbytes < 0:
             check(-1)
-        self.ws = torch.empty(nbytes, dtype=torch.uint8, device=self.device)
+        self._ws_raw = torch.empty(nbytes + 1024, dtype=torch.uint8, device=self.device)
+        skew = (-self._ws_raw.data_ptr()) % 1024                     # the C ABI wants the workspace 1024-byte aligned
+        self.ws = self._ws_raw[skew:skew + nbytes]
         self.world, self.rank, self.dist = world, rank, process_group
         if world > 1 and process_group is None:
             raise WxError("world > 1 needs an initialised torch.distributed (NCCL) handle")
