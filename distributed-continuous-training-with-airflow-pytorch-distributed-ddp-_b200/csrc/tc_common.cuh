@@ -33,13 +33,27 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
         : "memory");
     return ok != 0;
 }
+// try_wait with a suspend-time hint: the hardware parks the thread for up to `ns` instead of returning after its default
+// time slice, so a waiting role issues one instruction per `ns` rather than a polling loop's worth
+__device__ __forceinline__ bool mbar_try_wait_hint(uint64_t* bar, uint32_t parity, uint32_t ns) {
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"
+        "selp.b32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"(smem_u32(bar)), "r"(parity), "r"(ns)
+        : "memory");
+    return ok != 0;
+}
+
 // Bounded wait: returns false if the barrier did not flip within ~2 s (a protocol bug must not hang the GPU).
 __device__ __forceinline__ bool mbar_wait(uint64_t* bar, uint32_t parity) {
     if (mbar_try_wait(bar, parity)) return true;
 #pragma unroll 1
-    for (uint32_t spin = 0; spin < (1u << 24); ++spin) {
-        __nanosleep(40);                      // back off: idle roles must not steal issue slots from the row workers
-        if (mbar_try_wait(bar, parity)) return true;
+    for (uint32_t spin = 0; spin < (1u << 21); ++spin) {
+        // idle roles must not steal issue slots from the row workers: park in hardware, ~1 us at a time
+        if (mbar_try_wait_hint(bar, parity, 1000u)) return true;
     }
     return false;
 }

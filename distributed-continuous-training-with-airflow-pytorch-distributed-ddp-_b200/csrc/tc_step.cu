@@ -69,6 +69,9 @@ __device__ __forceinline__ void st4(void* base, uint32_t off, float a, float b, 
     *reinterpret_cast<float4*>(static_cast<unsigned char*>(base) + off) = make_float4(a, b, c, d);
 }
 
+// RAW: raw-column loader (column segments [F][128] in the landing buffer, standardised on the way) vs dense row-major rows.
+// A template parameter so that every landing-buffer access has a compile-time stride (immediate LDS offsets).
+template <bool RAW>
 __global__ void __launch_bounds__(TC_THREADS, 1) tc_step_kernel(const GridArgs a, const int F, int* __restrict__ err_out) {
     extern __shared__ __align__(1024) unsigned char raw[];     // 1024-byte alignment: the swizzle atoms need it
     TcSmem& s = *reinterpret_cast<TcSmem*>(raw);               // direct cast keeps the shared address space (LDS/STS)
@@ -78,7 +81,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_step_kernel(const GridArgs a
     const int slab_stride = (P + 1 + 3) & ~3;
     constexpr int K1 = 32;                        // GEMM1 K extent: features [0,F) | zeros | 1 at column 29 (| dl at 30,31: zero weights)
     constexpr int N2 = 32;                        // GEMM2 N extent
-    const bool raw_cols = a.loader != wxk::LOAD_ROWMAJOR;
+    constexpr bool raw_cols = RAW;
     const int64_t ntiles = (a.batch + TILE - 1) / TILE;
     const int64_t my_tiles = (ntiles - blockIdx.x + gridDim.x - 1) / gridDim.x;     // >= 1 by construction of the grid
 
@@ -307,14 +310,16 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_step_kernel(const GridArgs a
             if (!mbar_wait(&s.land_full[st], uint32_t((i / STAGES) & 1))) s.err = 5;
             const bool valid = r < tile_rows(tile);
             float* lx = s.land_x[st] + (raw_cols ? r : r * F);     // element c of this row at lx[c * cstride]
-            const int cstride = raw_cols ? TILE : 1;
+            constexpr int cstride = raw_cols ? TILE : 1;
 #pragma unroll 1
             for (int c8 = 0; c8 < 4; ++c8) {
                 float t[8];
 #pragma unroll
-                for (int e = 0; e < 8; ++e) {                       // unconditional (clamped) loads: all eight in flight
+                for (int e = 0; e < 8; ++e) {
+                    // unconditional loads at compile-time offsets, all eight in flight; columns >= F read whatever follows in
+                    // the landing ring (still inside TcSmem) and are discarded by the selects below
                     const int c = c8 * 8 + e;
-                    t[e] = lx[(c < F ? c : F - 1) * cstride];
+                    t[e] = lx[c * cstride];
                 }
                 if (raw_cols) {
 #pragma unroll
@@ -455,14 +460,14 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_step_kernel(const GridArgs a
             // Xaug row (MN-major): features, 1, dl0, dl1
             {
                 const float* lx = s.land_x[st] + (raw_cols ? r : r * F);
-                const int cstride = raw_cols ? TILE : 1;
+                constexpr int cstride = raw_cols ? TILE : 1;
 #pragma unroll 1
                 for (int g8 = 0; g8 < 4; ++g8) {
                     float t[8], hi[8], lo[8];
 #pragma unroll
                     for (int e = 0; e < 8; ++e) {
                         const int c = g8 * 8 + e;
-                        t[e] = lx[(c < F ? c : F - 1) * cstride];
+                        t[e] = lx[c * cstride];
                     }
 #pragma unroll
                     for (int e = 0; e < 8; ++e) {
@@ -664,7 +669,8 @@ int tc_launch(wx_ctx* ctx, GridArgs& a, cudaStream_t st, const char* who) {
     const int smem = int(sizeof(TcSmem));
     static bool attr_set = false;
     if (!attr_set) {
-        WX_CUDA(cudaFuncSetAttribute(tc_step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        WX_CUDA(cudaFuncSetAttribute(tc_step_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        WX_CUDA(cudaFuncSetAttribute(tc_step_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
         attr_set = true;
     }
     const int64_t ntiles = (a.batch + TILE - 1) / TILE;
@@ -683,7 +689,8 @@ int tc_launch(wx_ctx* ctx, GridArgs& a, cudaStream_t st, const char* who) {
         a.scale = a.scale / float(ctx->peer.world);          // mean over W*B rows (what DDP's averaged gradients give)
     }
     int* err = reinterpret_cast<int*>(ctx->scratch) + 8;       // word 8 of the ticket block: sticky protocol-error code
-    tc_step_kernel<<<(unsigned)grid, TC_THREADS, smem, st>>>(a, f, err);
+    if (a.loader == wxk::LOAD_ROWMAJOR) tc_step_kernel<false><<<(unsigned)grid, TC_THREADS, smem, st>>>(a, f, err);
+    else tc_step_kernel<true><<<(unsigned)grid, TC_THREADS, smem, st>>>(a, f, err);
     WX_LAUNCH_CHECK(ctx);
     return WX_OK;
 }
