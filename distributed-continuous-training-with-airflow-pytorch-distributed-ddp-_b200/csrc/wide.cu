@@ -44,7 +44,7 @@ struct Layout {
     int64_t P;                    // number of fp32 parameters
     int64_t off_w[8], off_b[8];   // parameter offsets of hidden layer l = 1..L (index l), head at index L+1
     size_t wb[8];                 // workspace byte offsets: bf16 weights of hidden layer l
-    size_t x0, h[8], dz[2], dlog, part, dw1tmp, dwtmp[8], total;
+    size_t x0, h[8], dz[2], dlog, part, part2, dw1tmp, dwtmp[8], total;
 };
 
 size_t align_up(size_t v) { return (v + 1023) & ~size_t(1023); }
@@ -84,6 +84,8 @@ int make_layout(const wx_wide_desc* d, int64_t batch, Layout* L) {
     w = align_up(w + size_t(batch) * 2 * 4);
     L->part = w;   // partial sums: max(colsum: SLABS x H, head: SLABS x (2H), head rows: grid x 4)
     w = align_up(w + size_t(HEAD_SLABS) * 2 * H * 4 + size_t(4096) * 4 * 4);
+    L->part2 = w;   // head dW_o partials (their own buffer: that piece may run beside the column sums)
+    w = align_up(w + size_t(HEAD_SLABS) * 2 * H * 4);
     L->dw1tmp = w;
     w = align_up(w + size_t(MAX_SPLIT_K) * H * KPAD * 4);
     for (int l = 2; l <= nl; ++l) {   // second split-K slab of dW_l (wave quantisation: see wx_wide_backward_layer)
@@ -144,7 +146,10 @@ __device__ __forceinline__ void unpack8(const uint4& u, float (&f)[8]) {
 __global__ void __launch_bounds__(256) wide_head_kernel(const __nv_bfloat16* __restrict__ h, int64_t batch, int H,
                                                        const float* __restrict__ w_o, const float* __restrict__ b_o,
                                                        const int64_t* __restrict__ y, float scale,
-                                                       float* __restrict__ dlog, float* __restrict__ part) {
+                                                       float* __restrict__ dlog, float* __restrict__ part,
+                                                       float inv_keep, __nv_bfloat16* __restrict__ dz) {
+    // dz != NULL: the same warp also writes dZ_L[r][c] = (dl0 W_o[0][c] + dl1 W_o[1][c]) * gate(H_L[r][c]) for its row,
+    // re-reading the row it has just pulled through L1/L2 -- H_L crosses DRAM once for logits AND dZ.
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     float acc_loss = 0.0f, acc0 = 0.0f, acc1 = 0.0f, acc_ok = 0.0f;
     for (int64_t row = int64_t(blockIdx.x) * 8 + warp; row < batch; row += int64_t(gridDim.x) * 8) {
@@ -163,14 +168,38 @@ __global__ void __launch_bounds__(256) wide_head_kernel(const __nv_bfloat16* __r
         }
         s0 = warp_sum(s0) + b_o[0];
         s1 = warp_sum(s1) + b_o[1];
+        // every lane evaluates the (identical) softmax so that all of them hold the dlogits for the dZ pass
+        const float mx = fmaxf(s0, s1);
+        const float e0 = expf(s0 - mx), e1 = expf(s1 - mx);
+        const float lse = mx + logf(e0 + e1);
+        const int64_t lab = y[row];
+        const float inv = 1.0f / (e0 + e1);
+        const float d0 = (e0 * inv - (lab == 0 ? 1.0f : 0.0f)) * scale;
+        const float d1 = (e1 * inv - (lab == 1 ? 1.0f : 0.0f)) * scale;
+        if (dz != nullptr) {
+            uint4* zp = reinterpret_cast<uint4*>(dz + row * H);
+            for (int c8 = lane; c8 < H / 8; c8 += 32) {
+                float f[8], o[8];
+                unpack8(__ldg(hp + c8), f);
+                const float4* w0 = reinterpret_cast<const float4*>(w_o + c8 * 8);
+                const float4* w1 = reinterpret_cast<const float4*>(w_o + H + c8 * 8);
+                const float4 a0 = __ldg(w0), a1 = __ldg(w0 + 1), c0 = __ldg(w1), c1 = __ldg(w1 + 1);
+                const float u0[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
+                const float u1[8] = {c0.x, c0.y, c0.z, c0.w, c1.x, c1.y, c1.z, c1.w};
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    const float dh = fmaf(d0, u0[i], d1 * u1[i]);
+                    o[i] = f[i] > 0.0f ? dh * inv_keep : 0.0f;
+                }
+                uint4 ov;
+                ov.x = pack_bf16(o[0], o[1]);
+                ov.y = pack_bf16(o[2], o[3]);
+                ov.z = pack_bf16(o[4], o[5]);
+                ov.w = pack_bf16(o[6], o[7]);
+                zp[c8] = ov;
+            }
+        }
         if (lane == 0) {
-            const float mx = fmaxf(s0, s1);
-            const float e0 = expf(s0 - mx), e1 = expf(s1 - mx);
-            const float lse = mx + logf(e0 + e1);
-            const int64_t lab = y[row];
-            const float inv = 1.0f / (e0 + e1);
-            const float d0 = (e0 * inv - (lab == 0 ? 1.0f : 0.0f)) * scale;
-            const float d1 = (e1 * inv - (lab == 1 ? 1.0f : 0.0f)) * scale;
             if (dlog != nullptr) {
                 dlog[row * 2] = d0;
                 dlog[row * 2 + 1] = d1;
@@ -209,8 +238,8 @@ __global__ void __launch_bounds__(256) wide_head_bwd_kernel(const __nv_bfloat16*
     float w0[8], w1[8], a0[8], a1[8];
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
-        w0[i] = __ldg(w_o + c8 * 8 + i);
-        w1[i] = __ldg(w_o + H + c8 * 8 + i);
+        w0[i] = dz != nullptr ? __ldg(w_o + c8 * 8 + i) : 0.0f;
+        w1[i] = dz != nullptr ? __ldg(w_o + H + c8 * 8 + i) : 0.0f;
         a0[i] = 0.0f;
         a1[i] = 0.0f;
     }
@@ -240,7 +269,7 @@ __global__ void __launch_bounds__(256) wide_head_bwd_kernel(const __nv_bfloat16*
             ov.y = pack_bf16(o[2], o[3]);
             ov.z = pack_bf16(o[4], o[5]);
             ov.w = pack_bf16(o[6], o[7]);
-            reinterpret_cast<uint4*>(dz + (rb + u) * H)[c8] = ov;
+            if (dz != nullptr) reinterpret_cast<uint4*>(dz + (rb + u) * H)[c8] = ov;
         }
     }
     float* p = part + size_t(blockIdx.y) * 2 * H;
@@ -657,7 +686,7 @@ extern "C" {
 
 /* Forward through the loss, plus the head's gradients and dZ of the last hidden layer.
  *   x      fp32 [batch, F] row-major, standardised (the output of wx_normalize_pack)
- *   grads  fp32 [P+1]: receives dW_o, db_o and, at [P], sum_rows(CE) * grad_scale
+ *   grads  fp32 [P+1]: receives db_o and, at [P], sum_rows(CE) * grad_scale
  *   grad_scale = 1 / (world * batch): gradients and loss come out pre-scaled for a SUM all-reduce (DDP, :136)
  *   dropout_mode: WX_DROPOUT_OFF or WX_DROPOUT_PHILOX (keep <=> 16 Philox bits < round((1-p) * 65536);
  *                 counter (row, col/8, layer, step), key seed -- oracle/wide_ref.py keep_mask) */
@@ -689,18 +718,13 @@ int wx_wide_forward(wx_ctx* ctx, const wx_wide_desc* desc, const float* params, 
     float* head_part = part + size_t(HEAD_SLABS) * 2 * H;       // [grid][4]
     int hgrid = int((batch + 7) / 8);
     if (hgrid > 4096) hgrid = 4096;
+    // logits, loss, dlogits AND dZ_L in one pass over H_L; dW_o (the other reader of H_L) is WX_WIDE_HEAD_DW of
+    // wx_wide_backward_layer(layer = n_hidden), so the caller can keep it off the stream the GEMMs are waiting on
     wide_head_kernel<<<hgrid, 256, 0, st>>>(hl, batch, int(H), params + L.off_w[nl + 1], params + L.off_b[nl + 1], y,
-                                           grad_scale, dlog, head_part);
+                                           grad_scale, dlog, head_part, drop ? 1.0f / keep_p : 1.0f,
+                                           reinterpret_cast<__nv_bfloat16*>(w + L.dz[0]));
     WX_LAUNCH_CHECK(ctx);
     wide_head_finish_kernel<<<1, 256, 0, st>>>(head_part, hgrid, grads + L.off_b[nl + 1], grads + L.P, nullptr);
-    WX_LAUNCH_CHECK(ctx);
-    int slabs = int(batch / 128 < HEAD_SLABS ? batch / 128 : HEAD_SLABS);
-    dim3 bg((unsigned)((H / 8 + 255) / 256), (unsigned)slabs);
-    wide_head_bwd_kernel<<<bg, 256, 0, st>>>(hl, batch, int(H), params + L.off_w[nl + 1], dlog,
-                                            drop ? 1.0f / keep_p : 1.0f,
-                                            reinterpret_cast<__nv_bfloat16*>(w + L.dz[0]), part);
-    WX_LAUNCH_CHECK(ctx);
-    wide_reduce_kernel<<<int((2 * H + 255) / 256), 256, 0, st>>>(part, slabs, 2 * H, 2 * H, grads + L.off_w[nl + 1]);
     WX_LAUNCH_CHECK(ctx);
     return WX_OK;
 }
@@ -717,7 +741,7 @@ int wx_wide_backward_layer(wx_ctx* ctx, const wx_wide_desc* desc, void* ws, int6
                  (long long)batch);
     const int nl = desc->n_hidden;
     WX_CHECK_ARG(layer >= 1 && layer <= nl, "wx_wide_backward_layer: layer=%d outside 1..%d", layer, nl);
-    WX_CHECK_ARG(parts >= 1 && parts <= 15, "wx_wide_backward_layer: parts=%d (bit 0 dW, bit 1 db, bit 2 dZ below, bit 3 fold)", parts);
+    WX_CHECK_ARG(parts >= 1 && parts <= 31, "wx_wide_backward_layer: parts=%d (bit 0 dW, bit 1 db, bit 2 dZ below, bit 3 fold, bit 4 head dW)", parts);
     WX_CUDA(cudaSetDevice(ctx->device));
     Layout L;
     make_layout(desc, batch, &L);
@@ -729,6 +753,18 @@ int wx_wide_backward_layer(wx_ctx* ctx, const wx_wide_desc* desc, void* ws, int6
     void* dz_below = w + L.dz[(nl - layer + 1) & 1];
     const void* h_below = (layer == 1) ? static_cast<const void*>(w + L.x0) : static_cast<const void*>(w + L.h[layer - 1]);
     const int64_t in = (layer == 1) ? KPAD : H;
+    // head: dW_o[k][c] = sum_r dlogits[r][k] H_L[r][c] (per-slab partial sums, then an ordered reduce)
+    if ((parts & WX_WIDE_HEAD_DW) && layer == nl) {
+        float* part = reinterpret_cast<float*>(w + L.part2);
+        int slabs = int(batch / 128 < HEAD_SLABS ? batch / 128 : HEAD_SLABS);
+        dim3 bg((unsigned)((H / 8 + 255) / 256), (unsigned)slabs);
+        wide_head_bwd_kernel<<<bg, 256, 0, st>>>(reinterpret_cast<const __nv_bfloat16*>(w + L.h[nl]), batch, int(H),
+                                                nullptr, reinterpret_cast<const float*>(w + L.dlog), 1.0f,
+                                                nullptr, part);
+        WX_LAUNCH_CHECK(ctx);
+        wide_reduce_kernel<<<int((2 * H + 255) / 256), 256, 0, st>>>(part, slabs, 2 * H, 2 * H, grads + L.off_w[nl + 1]);
+        WX_LAUNCH_CHECK(ctx);
+    }
     // dW = dZ^T H_below : A = dZ stored [batch, H] = [K, M], B = H_below stored [batch, in] = [K, N]
     if (parts & WX_WIDE_DW) {
         GemmArgs g = {};
@@ -856,7 +892,8 @@ int wx_wide_eval(wx_ctx* ctx, const wx_wide_desc* desc, const float* params, voi
     int hgrid = int((batch + 7) / 8);
     if (hgrid > 4096) hgrid = 4096;
     wide_head_kernel<<<hgrid, 256, 0, st>>>(reinterpret_cast<const __nv_bfloat16*>(w + L.h[nl]), batch, desc->hidden,
-                                           params + L.off_w[nl + 1], params + L.off_b[nl + 1], y, 1.0f, nullptr, head_part);
+                                           params + L.off_w[nl + 1], params + L.off_b[nl + 1], y, 1.0f, nullptr, head_part,
+                                           1.0f, nullptr);
     WX_LAUNCH_CHECK(ctx);
     wide_head_finish_kernel<<<1, 256, 0, st>>>(head_part, hgrid, nullptr, out, out + 1);
     WX_LAUNCH_CHECK(ctx);

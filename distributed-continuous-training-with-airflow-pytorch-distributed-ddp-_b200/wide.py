@@ -151,7 +151,8 @@ class WideEngine:
             check(lib.wx_wide_reserve_sms(h, 0))               # nothing else runs during the forward: all SMs
         check(lib.wx_wide_forward(h, d, self.params.data_ptr(), ws, x.data_ptr(), y.data_ptr(), b, dropout, self.seed, step,
                                   scale, g, mst))
-        after_main()                                           # dZ_L, head gradients and the loss are enqueued
+        after_main()                                           # dZ_L, db_o and the loss are enqueued
+        check(lib.wx_wide_backward_layer(h, d, ws, b, self.L, dropout, 16, g, sst))            # dW_o (side stream)
         reduce_slice(*self.head_slice)
         adam(self.L + 1)
         db_done = {}

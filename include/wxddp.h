@@ -264,7 +264,8 @@ int64_t wx_wide_workspace_bytes(const wx_wide_desc* desc, int64_t batch); /* byt
 /* (Re)build the bf16 copies of the hidden weights inside ws from the fp32 parameters (once after init / load). */
 int wx_wide_cast_weights(wx_ctx* ctx, const wx_wide_desc* desc, const float* params, void* ws, void* stream);
 /* Forward + loss + head gradients: x fp32 [batch,F] row-major standardised features (wx_normalize_pack output),
- * y int64 [batch].  grads fp32 [P+1] receives dW_o, db_o and, at [P], sum(CE) * grad_scale; grad_scale is normally
+ * y int64 [batch].  grads fp32 [P+1] receives db_o and, at [P], sum(CE) * grad_scale (dW_o: WX_WIDE_HEAD_DW of
+ * wx_wide_backward_layer, so that H_L is read once on the critical path -- logits and dZ_L come out of one pass); grad_scale is normally
  * 1/(world*batch).  dropout_mode: WX_DROPOUT_OFF or WX_DROPOUT_PHILOX (keep <=> 16 Philox4x32-10 bits <
  * round((1-p)*65536); counter (row, col/8, layer, step), key = seed). */
 int wx_wide_forward(wx_ctx* ctx, const wx_wide_desc* desc, const float* params, void* ws, const float* x,
@@ -278,7 +279,8 @@ int wx_wide_forward(wx_ctx* ctx, const wx_wide_desc* desc, const float* params, 
 #define WX_WIDE_DB 2 /* bias gradient (column sums of dZ) */
 #define WX_WIDE_DZ 4 /* dZ of the layer below (skipped for layer 1) */
 #define WX_WIDE_DW_FOLD 8 /* add the second split-K slab of dW into the gradient (no-op when dW was not split); must follow DW */
-#define WX_WIDE_ALL 15
+#define WX_WIDE_HEAD_DW 16 /* with layer == n_hidden only: the head's weight gradient dW_o (wx_wide_forward leaves it to this piece) */
+#define WX_WIDE_ALL 31
 int wx_wide_backward_layer(wx_ctx* ctx, const wx_wide_desc* desc, void* ws, int64_t batch, int layer, int dropout_mode,
                            int parts, float* grads, void* stream);
 /* Adam over all P parameters (step is 1-based), rewriting the bf16 weight copies in ws in the same pass. */
