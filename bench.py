@@ -88,6 +88,49 @@ class ClockSampler:
                 "samples": len(sm), "reasons": sorted(reasons)}
 
 
+def profiled_traffic(matches_profiled_workload: bool):
+    """roofline.traffic is not measurable inside an un-profiled run: it is dram__bytes_read.sum + dram__bytes_write.sum per
+    launch of the step kernel from the committed ncu --set full capture of this exact workload (profiles/traffic.json,
+    which names the capture); any other workload has no capture -> null."""
+    path = os.path.join(ROOT, "profiles", "traffic.json")
+    if not matches_profiled_workload or not os.path.exists(path):
+        return None, None
+    with open(path) as fh:
+        d = json.load(fh)
+    return float(d["dram_bytes_per_launch"]), d["source"]
+
+
+def median(xs):
+    xs = sorted(xs)
+    n = len(xs)
+    return xs[n // 2] if n % 2 else 0.5 * (xs[n // 2 - 1] + xs[n // 2])
+
+
+def timed_repeats(torch, dist, world, device, one_step, steps: int, repeats: int, barrier, fill_ms: float = 1000.0):
+    """Time `steps` steps `repeats` times (CUDA events on the launch stream, barrier + synchronize on both sides of
+    every repeat, max over ranks per repeat).  repeats == 0: as many as fill ~`fill_ms` of device time, at least 5, so
+    that the clock sampler sees the region.  Returns the per-repeat milliseconds."""
+    def once():
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        barrier()
+        ev0.record()
+        for _ in range(steps):
+            one_step()
+        ev1.record()
+        barrier()
+        t = torch.tensor([ev0.elapsed_time(ev1)], dtype=torch.float64, device=device)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    times = [once()]
+    if repeats <= 0:
+        repeats = max(5, min(400, int(fill_ms / max(times[0], 1e-3)) + 1))
+    while len(times) < repeats:
+        times.append(once())
+    return times
+
+
 def synth_raw_on_device(torch, n_rows: int, f: int, seed: int, device):
     """Raw (un-standardised) fp32 columns + int64 labels, generated on the GPU (same family of distributions
     as oracle/synth.py; generation is outside every timed region)."""
@@ -316,9 +359,11 @@ def main() -> int:
     ap.add_argument("--features", type=int, default=20)
     ap.add_argument("--rows-per-step", type=int, default=1 << 20)
     ap.add_argument("--table-rows", type=int, default=1 << 24)
-    ap.add_argument("--cpu-rows-per-step", type=int, default=65536,
-                    help="CPU arms: rows per step of the bounded sample (0 = --rows-per-step)")
-    ap.add_argument("--cpu-steps", type=int, default=300)
+    ap.add_argument("--cpu-rows-per-step", type=int, default=0,
+                    help="CPU arms: rows per step (0 = --rows-per-step, i.e. the GPU arm's configuration)")
+    ap.add_argument("--cpu-steps", type=int, default=20, help="steps of the cpu_baseline leg inside the default run")
+    ap.add_argument("--repeats", type=int, default=0,
+                    help="timed repeats of --steps steps each (0 = as many as fill ~1 s, at least 5); the median is reported")
     ap.add_argument("--kernel", default="auto", choices=["auto", "tc", "ffma"], help="step kernel at N=1")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
@@ -424,20 +469,10 @@ def main() -> int:
     if rank == 0:
         sampler.start()
     launches0 = ctx.launch_count
-    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    barrier()
-    ev0.record()
-    for _ in range(args.steps):
-        one_step()
-    ev1.record()
-    barrier()
-    ms = ev0.elapsed_time(ev1)
-    launches = ctx.launch_count - launches0
+    times = timed_repeats(torch, dist, world, device, one_step, args.steps, args.repeats, barrier)
+    ms = median(times)
+    launches = (ctx.launch_count - launches0) // len(times)
     clocks = sampler.stop() if rank == 0 else None
-    t = torch.tensor([ms], dtype=torch.float64, device=device)
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms = float(t.item())
     final_loss = float(loss.item()) if (world == 1 or fused_ddp) else float(grads[P].item())
 
     # ---- e2e: public API with HOST buffers; H2D of the step's raw rows + labels and D2H of the loss inside ----
@@ -491,11 +526,12 @@ def main() -> int:
     flops_per_row = 2 * (2 * f * 64 + 3 * 64 * 2)
     # dram__bytes_read.sum + dram__bytes_write.sum per launch from the ncu --set full capture of this exact workload
     # (profiles/README.md: 92.46 MB + 2.5 MB); any other workload has no capture -> null
-    traffic = 94.96e6 if (world == 1 and use_tc and f == 20 and B == (1 << 20)) else None
+    traffic, traffic_src = profiled_traffic(use_tc and f == 20 and B == (1 << 20))
     roof = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
             "traffic": traffic, "kernel": kernel_name if (world == 1 or fused_ddp)
             else ("tc_step_kernel (wx_tc_mlp_grad)" if grad_fn == ctx.tc_mlp_grad else "mlp_grid_kernel<F,TRAIN,ROWMAJOR> (wx_mlp_grad)")
             + " + NCCL all-reduce + adam_kernel",
+            "traffic_source": traffic_src,
             "peak_source": peak_src, "algorithmic_bytes_per_row": bytes_per_row,
             "fp32_pipe": {"achieved_tflops": B * flops_per_row / kernel_s / 1e12, "peak_tflops": 74.4,
                           "frac": B * flops_per_row / kernel_s / 1e12 / 74.4,
@@ -503,7 +539,10 @@ def main() -> int:
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": workload_config(args, B),
-            "roofline": roof, "clocks": clocks, "gpu_launches": int(launches), "final_loss": final_loss}
+            "roofline": roof, "clocks": clocks, "gpu_launches": int(launches), "final_loss": final_loss,
+            "repeats": len(times), "ms_per_step_min": min(times) / args.steps, "ms_per_step_max": max(times) / args.steps,
+            "timing": f"median of {len(times)} repeats of {args.steps} steps each (CUDA events, barrier + synchronize around "
+                      f"every repeat, max over ranks); gpu_launches counts one repeat"}
     if e2e is not None:
         line["e2e"] = e2e
     if not args.no_cpu_baseline and world == 1:

@@ -286,10 +286,16 @@ def _ddp_bench_worker(rank: int, world: int, port: int, n_rows: int, f: int, bat
     import torch.distributed as dist
 
     torch.set_num_threads(threads)
-    os.environ["MASTER_ADDR"] = "127.0.0.1"
-    os.environ["MASTER_PORT"] = str(port)
+    # The workers may be spawned from a rank that torchrun started: drop every rendezvous variable that was
+    # inherited (TORCHELASTIC_USE_AGENT_STORE makes env:// wait for the agent's store instead of hosting one)
+    # and rendezvous over an explicit tcp:// address on a port the parent found free.
+    for k in list(os.environ):
+        if k.startswith("TORCHELASTIC_") or k in ("RANK", "LOCAL_RANK", "WORLD_SIZE", "LOCAL_WORLD_SIZE", "GROUP_RANK",
+                                                   "ROLE_RANK", "ROLE_WORLD_SIZE", "GROUP_WORLD_SIZE", "MASTER_ADDR",
+                                                   "MASTER_PORT"):
+            os.environ.pop(k, None)
     if world > 1:
-        dist.init_process_group("gloo", rank=rank, world_size=world)
+        dist.init_process_group("gloo", init_method=f"tcp://127.0.0.1:{port}", rank=rank, world_size=world)
     torch.manual_seed(SEED)
     g = torch.Generator().manual_seed(1234)
     feats = torch.randn(n_rows, f, generator=g)
@@ -332,8 +338,16 @@ def _ddp_bench_worker(rank: int, world: int, port: int, n_rows: int, f: int, bat
         dist.destroy_process_group()
 
 
+def _free_port() -> int:
+    import socket
+
+    with socket.socket(socket.AF_INET, socket.SOCK_STREAM) as s:
+        s.bind(("127.0.0.1", 0))
+        return int(s.getsockname()[1])
+
+
 def time_cpu_ddp(f: int, batch: int, steps: int, warmup: int = 20, world: int = 2, threads: int = 1,
-                 n_rows: int = 145_460, per_sample: bool = True, port: int = 29731) -> dict:
+                 n_rows: int = 145_460, per_sample: bool = True, port: int | None = None) -> dict:
     """Time `steps` optimizer steps of the restated reference step on CPU with gloo DDP.
 
     `per_sample=True` keeps the reference's per-row `__getitem__` + collate (:49,:122).
@@ -341,6 +355,8 @@ def time_cpu_ddp(f: int, batch: int, steps: int, warmup: int = 20, world: int = 
     """
     import torch.multiprocessing as mp
 
+    if port is None:
+        port = _free_port()
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
     procs = [ctx.Process(target=_ddp_bench_worker,
@@ -348,7 +364,20 @@ def time_cpu_ddp(f: int, batch: int, steps: int, warmup: int = 20, world: int = 
              for r in range(world)]
     for p in procs:
         p.start()
-    dt = q.get(timeout=1800)
+    import queue as _queue
+    import time as _time
+
+    dt, deadline = None, _time.time() + 1800
+    while dt is None:
+        try:
+            dt = q.get(timeout=1.0)
+        except _queue.Empty:
+            dead = [p.exitcode for p in procs if p.exitcode not in (None, 0)]
+            if dead or _time.time() > deadline:
+                for p in procs:
+                    if p.is_alive():
+                        p.terminate()
+                raise RuntimeError(f"time_cpu_ddp: worker exit codes {dead or 'timeout'}")
     for p in procs:
         p.join(timeout=60)
     return {"seconds": dt, "samples_per_sec": steps * batch * world / dt, "cores": world * threads}
