@@ -69,6 +69,7 @@ SIGNATURES = {
                                     _vp, _vp]),
     "wx_mlp_eval": (_int, [_vp, _vp, _vp, _vp, _vp, _i64, _i64, _vp, _vp]),
     "wx_mlp_predict": (_int, [_vp, _vp, _vp, _i64, _vp, _vp]),
+    "wx_mlp_logits": (_int, [_vp, _vp, _vp, _i64, _vp, _vp]),
     "wx_wide_n_params": (_i64, [C.POINTER(WideDesc)]),
     "wx_wide_workspace_bytes": (_i64, [C.POINTER(WideDesc), _i64]),
     "wx_wide_cast_weights": (_int, [_vp, C.POINTER(WideDesc), _vp, _vp, _vp]),

@@ -52,6 +52,13 @@ int launch_grid(wx_ctx* ctx, GridArgs& a, int mode, cudaStream_t st, const char*
     if (grid > WX_MAX_GRID_PARTS) grid = WX_MAX_GRID_PARTS;
     if (grid < 1) grid = 1;
     const size_t slab = (size_t(64) * f + 64 + 128 + 2 + 1 + 3) & ~size_t(3);
+    // one partial slab per CTA: never launch more CTAs than the scratch area holds slabs for (the kernels walk their
+    // chunks grid-stride, so a smaller grid computes the same sums) -- this is what bounds the grid of the fixed
+    // 1.5 MiB array behind wx_mlp_grad_static
+    if (ctx->scratch_bytes > WX_SCRATCH_PART_OFF) {
+        const int64_t fit = int64_t((ctx->scratch_bytes - WX_SCRATCH_PART_OFF) / (mode == MODE_TRAIN ? slab * 4 : 16));
+        if (fit >= 1 && grid > fit) grid = fit;
+    }
     const size_t need = mode == MODE_TRAIN ? size_t(grid) * slab * 4 : size_t(grid) * 16;
     if (WX_SCRATCH_PART_OFF + need > ctx->scratch_bytes) {
         wx_set_error("%s: scratch too small (%zu needed)", who, need);
@@ -302,11 +309,12 @@ int wx_mlp_eval(wx_ctx* ctx, const float* params, const float* x, const int64_t*
     return launch_grid(ctx, a, MODE_EVAL, (cudaStream_t)stream, "wx_mlp_eval");
 }
 
-int wx_mlp_predict(wx_ctx* ctx, const float* params, const float* x, int64_t n, float* probs_out, void* stream) {
-    WX_CHECK_ARG(ctx != nullptr, "wx_mlp_predict: ctx is NULL");
-    WX_CHECK_ARG(n >= 0, "wx_mlp_predict: n < 0");
+static int predict_common(wx_ctx* ctx, const float* params, const float* x, int64_t n, float* probs_out, void* stream,
+                          bool logits, const char* who) {
+    WX_CHECK_ARG(ctx != nullptr, "%s: ctx is NULL", who);
+    WX_CHECK_ARG(n >= 0, "%s: n < 0", who);
     if (n == 0) return WX_OK;
-    WX_CHECK_ARG(params && x && probs_out, "wx_mlp_predict: NULL pointer");
+    WX_CHECK_ARG(params && x && probs_out, "%s: NULL pointer", who);
     GridArgs a;
     zero_args(a);
     a.params = params;
@@ -316,9 +324,17 @@ int wx_mlp_predict(wx_ctx* ctx, const float* params, const float* x, int64_t n, 
     a.row0 = 0;
     a.batch = n;
     a.dropout_mode = WX_DROPOUT_OFF;
-    a.scale = 1.0f;
+    a.scale = logits ? 0.0f : 1.0f;     // MODE_PREDICT reads `scale` as the output selector (process_chunk)
     a.probs_out = probs_out;
-    return launch_grid(ctx, a, MODE_PREDICT, (cudaStream_t)stream, "wx_mlp_predict");
+    return launch_grid(ctx, a, MODE_PREDICT, (cudaStream_t)stream, who);
+}
+
+int wx_mlp_predict(wx_ctx* ctx, const float* params, const float* x, int64_t n, float* probs_out, void* stream) {
+    return predict_common(ctx, params, x, n, probs_out, stream, false, "wx_mlp_predict");
+}
+
+int wx_mlp_logits(wx_ctx* ctx, const float* params, const float* x, int64_t n, float* logits_out, void* stream) {
+    return predict_common(ctx, params, x, n, logits_out, stream, true, "wx_mlp_logits");
 }
 
 }  // extern "C"
@@ -405,7 +421,7 @@ extern "C" int wx_mlp_grad_static(int n_features, const float* params, const flo
     // zero, so it is cleared here (a fill, not an allocation) in case an earlier launch was aborted.
     WX_CUDA(cudaMemsetAsync(slot->ptr, 0, WX_SCRATCH_PART_OFF, st));
     // A context-shaped view of the static array on the stack, so the same launch path as wx_mlp_grad is used.
-    wx_ctx view;
+    wx_ctx view{};
     view.device = dev;
     view.num_sms = slot->num_sms;
     view.desc.n_features = n_features;

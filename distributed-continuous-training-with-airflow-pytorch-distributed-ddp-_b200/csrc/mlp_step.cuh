@@ -273,7 +273,8 @@ __device__ __forceinline__ uint32_t chunk_keep_bits(int mode, const ChunkMeta& c
 
 // One chunk: forward for R rows, softmax/loss, and (TRAIN) backward accumulation.
 //   xs: smem [R][FS] fp32 standardised features of the chunk (rows past the end hold zeros)
-//   MODE: 0 = train (grads), 1 = eval (loss sum + correct), 2 = predict (probs written to probs_out)
+//   MODE: 0 = train (grads), 1 = eval (loss sum + correct), 2 = predict (written to probs_out: softmax probabilities,
+//         or the raw logits of forward() when `scale` == 0)
 template <int F, int MODE>
 __device__ __forceinline__ void process_chunk(LaneState<F>& st, const float* __restrict__ xs, const ChunkMeta& cm,
                                               uint32_t keepbits, float drop_scale, float scale, int lane,
@@ -332,7 +333,8 @@ __device__ __forceinline__ void process_chunk(LaneState<F>& st, const float* __r
     const float lp0 = s0 - lsum, lp1 = s1 - lsum;
     float dl0 = 0.0f, dl1 = 0.0f;
     if (MODE == 2) {
-        if (valid && (lane & 1) == 0) probs_out[rid * 2 + (c1 ? 1 : 0)] = expf(c1 ? lp1 : lp0);
+        if (valid && (lane & 1) == 0)
+            probs_out[rid * 2 + (c1 ? 1 : 0)] = (scale == 0.0f) ? (c1 ? lg1 : lg0) : expf(c1 ? lp1 : lp0);
         return;
     }
     const float lrow = -(yv ? lp1 : lp0);

@@ -667,11 +667,12 @@ int tc_launch(wx_ctx* ctx, GridArgs& a, cudaStream_t st, const char* who) {
                  "%s: keep_mask must be 16-byte aligned", who);
     WX_CUDA(cudaSetDevice(ctx->device));
     const int smem = int(sizeof(TcSmem));
-    static bool attr_set = false;
-    if (!attr_set) {
+    // the opt-in to > 48 KB of dynamic shared memory is a per-device function attribute
+    static bool attr_set[64] = {};
+    if (ctx->device < 0 || ctx->device >= 64 || !attr_set[ctx->device]) {
         WX_CUDA(cudaFuncSetAttribute(tc_step_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
         WX_CUDA(cudaFuncSetAttribute(tc_step_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-        attr_set = true;
+        if (ctx->device >= 0 && ctx->device < 64) attr_set[ctx->device] = true;
     }
     const int64_t ntiles = (a.batch + TILE - 1) / TILE;
     int64_t grid = ntiles < ctx->num_sms ? ntiles : ctx->num_sms;

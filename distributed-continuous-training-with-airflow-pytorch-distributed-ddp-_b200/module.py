@@ -121,9 +121,12 @@ class WeatherClassifier(_Base):
     def forward(self, x):                                                                   # :64
         if x.is_cuda and not torch.is_grad_enabled():
             lead = x.shape[:-1]
-            probs = self._ctx(x.device).mlp_predict(self.flat_parameters().detach().contiguous(),
+            if self.training:
+                # train-mode forward outside training_step draws torch's own dropout stream: leave it to torch
+                return self.net(x)
+            logits = self._ctx(x.device).mlp_logits(self.flat_parameters().detach().contiguous(),
                                                     x.reshape(-1, self.input_dim).contiguous())
-            return torch.log(probs).reshape(*lead, 2)      # logits up to a per-row constant (softmax-equivalent)
+            return logits.reshape(*lead, 2)                # the raw logits, as the reference's forward returns them
         return self.net(x)
 
     def training_step(self, batch, batch_idx):                                              # :66-71

@@ -364,3 +364,12 @@ class Context:
         out = torch.empty(n, 2, dtype=torch.float32, device=self.device)
         check(self.lib.wx_mlp_predict(self._h, _p(params), _p(x), n, _p(out), self._stream()))
         return out
+
+    def mlp_logits(self, params, x) -> torch.Tensor:
+        """forward() in eval mode (train_lightning_ddp.py:64): the two raw logits per row, [N,2]."""
+        self._chk(params, torch.float32, "params", self.P)
+        self._chk(x, torch.float32, "x")
+        n = x.numel() // self.n_features
+        out = torch.empty(n, 2, dtype=torch.float32, device=self.device)
+        check(self.lib.wx_mlp_logits(self._h, _p(params), _p(x), n, _p(out), self._stream()))
+        return out

@@ -122,7 +122,9 @@ def fit(features: torch.Tensor, labels: torch.Tensor, *, device, rank: int = 0, 
             if global_step % log_every == 0:
                 hist["logged"].append((global_step, l))
                 if logger is not None and rank == 0:
-                    logger.log_metrics({"train_loss": l, "epoch": epoch}, step=global_step)
+                    # Lightning 2.1 logs against `_batches_that_stepped`, which is bumped only after the batch's metrics
+                    # were written: the 5th batch lands at step 4, the 10th at 9, ...
+                    logger.log_metrics({"train_loss": l, "epoch": epoch}, step=global_step - 1)
         if max_steps is not None and global_step >= max_steps:
             done = True
         # validation epoch (:73-85): eval mode, rank-weighted means (C4)
@@ -135,7 +137,7 @@ def fit(features: torch.Tensor, labels: torch.Tensor, *, device, rank: int = 0, 
             print(f"Epoch {epoch}: train_loss={hist['train_loss'][-1]:.4f} val_loss={val_loss:.4f} val_acc={val_acc:.4f}",
                   flush=True)
         if logger is not None and rank == 0:
-            logger.log_metrics({"val_loss": val_loss, "val_acc": val_acc, "epoch": epoch}, step=global_step)
+            logger.log_metrics({"val_loss": val_loss, "val_acc": val_acc, "epoch": epoch}, step=global_step - 1)
         if checkpoint is not None and rank == 0:
             p, m, v = eng.params.cpu(), eng.m.cpu(), eng.v.cpu()
             checkpoint.on_validation_end(lambda cb: build_checkpoint(p, m, v, f, epoch, global_step, callbacks=cb),

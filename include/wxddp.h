@@ -240,6 +240,11 @@ int wx_mlp_eval(wx_ctx* ctx, const float* params, const float* x, const int64_t*
 int wx_mlp_predict(wx_ctx* ctx, const float* params, const float* x, int64_t n, float* probs_out,
                    void* stream);
 
+/* Eval-mode forward() itself (train_lightning_ddp.py:64 with dropout off): logits_out[i][c] = the two raw logits,
+ * what WeatherClassifier.forward returns to callers that read logits rather than probabilities. */
+int wx_mlp_logits(wx_ctx* ctx, const float* params, const float* x, int64_t n, float* logits_out,
+                  void* stream);
+
 /* ---- wide tabular MLP on bf16 tcgen05 GEMMs (BASELINE.json configs[3]; SURVEY 8(b) "wx_wide_mlp_fwd/bwd") ----------
  * No counterpart in the reference, whose only model is Linear(F,64)-ReLU-Dropout-Linear(64,2)
  * (jobs/train_lightning_ddp.py:57-62).  Same layer pattern widened: n_hidden x [Linear, ReLU, Dropout(p)] then

@@ -447,6 +447,18 @@ def test_eval_and_predict_match_reference_validation_step(wx, tag, f):
     probs = c.mlp_predict(p, x).cpu().numpy()
     want = torch.softmax(train_ref.forward_with_mask(torch.from_numpy(g["params"]), f, torch.from_numpy(g["x"]), None), 1)
     np.testing.assert_allclose(probs, want.numpy(), rtol=RTOL, atol=1e-7)
+    # forward() itself: raw logits (train_lightning_ddp.py:64), also where a probability would underflow
+    lg_ref = train_ref.forward_with_mask(torch.from_numpy(g["params"]), f, torch.from_numpy(g["x"]), None).numpy()
+    np.testing.assert_allclose(c.mlp_logits(p, x).cpu().numpy(), lg_ref, rtol=RTOL, atol=1e-6)
+    from wxddp.module import WeatherClassifier
+    model = WeatherClassifier(f)
+    model.load_flat(torch.from_numpy(g["params"]))
+    model = model.cuda().eval()
+    with torch.no_grad():
+        out = model(x)
+        big = model(x * 1e4)                      # logit gaps far beyond 103: log(softmax) would give -inf here
+    np.testing.assert_allclose(out.cpu().numpy(), lg_ref, rtol=RTOL, atol=1e-6)
+    assert torch.isfinite(big).all()
 
 
 # ---------------------------------------------------------------------------------------------

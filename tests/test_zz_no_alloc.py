@@ -71,6 +71,28 @@ def test_static_scratch_entry_matches_context_entry_twice_in_a_row():
     ctx.close()
 
 
+@pytest.mark.parametrize("f", [1, 8, 16, 17, 32])
+def test_static_scratch_entry_large_batch_every_width(f):
+    """1 Mi rows at narrow and wide models: the launch must size its grid to the slabs the fixed array holds (a narrow
+    model reaches several CTAs per SM, a wide one has large slabs) and still return wx_mlp_grad's sums."""
+    import wxddp
+
+    lib = wxddp.load()
+    n = 1 << 20
+    g = torch.Generator(device="cuda").manual_seed(5 + f)
+    x = torch.randn(n, f, device="cuda", generator=g)
+    y = (torch.rand(n, device="cuda", generator=g) < 0.3).long()
+    p = torch.randn(64 * f + 194, device="cuda", generator=g) * 0.2
+    got = _call_static(lib, f, p, x, y, n, mode=wxddp.DROPOUT_PHILOX, seed=9, step=2).cpu().numpy()
+    ctx = wxddp.Context(f, device=0)
+    want = ctx.mlp_grad(p, x, y, dropout=wxddp.DROPOUT_PHILOX, seed=9, step=2).cpu().numpy()
+    ctx.close()
+    assert np.isfinite(got).all()
+    np.testing.assert_allclose(got[-1], want[-1], rtol=RTOL)
+    # the two launches may use different grids (different partial-sum grouping): one part in 1e5 of the largest entry
+    np.testing.assert_allclose(got[:-1], want[:-1], rtol=RTOL, atol=1e-5 * np.abs(want[:-1]).max())
+
+
 def test_static_scratch_entry_rejects_requests_beyond_its_limits():
     import wxddp
 
