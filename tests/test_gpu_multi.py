@@ -58,24 +58,34 @@ def _run(worker, world, port, feats, labels):
     return res
 
 
-@pytest.mark.parametrize("world", [2])
+@pytest.mark.parametrize("world", [2, 4])
 def test_ddp_on_gpus_matches_gloo_ddp_oracle(world):
     _need(world)
     t = synth.synth_table(31, 203, 5)
     pp = preprocess_ref.preprocess_table(t["raw"], t["labels"])
     feats, labels = torch.from_numpy(pp["features"]), torch.from_numpy(pp["labels"])
-    got = _run(_nccl_worker, world, 29671, feats, labels)
-    ref = _run(_gloo_worker, world, 29673, feats, labels)
+    got = _run(_nccl_worker, world, _free_port(), feats, labels)
+    ref = _run(_gloo_worker, world, _free_port(), feats, labels)
     for g, r in zip(got, ref):
         np.testing.assert_allclose(g[1], r[1], rtol=2e-4, atol=1e-6)      # per-step rank-mean train_loss
         np.testing.assert_allclose(g[2], r[2], rtol=2e-4)
         np.testing.assert_allclose(g[3], r[3], rtol=1e-6)
         np.testing.assert_allclose(g[4], r[4], rtol=2e-3, atol=2e-5)
-    np.testing.assert_array_equal(got[0][4], got[1][4])                   # replicas stay bit-identical
+    for r in range(1, world):
+        np.testing.assert_array_equal(got[0][4], got[r][4])               # replicas stay bit-identical
+
+
+def _free_port() -> int:
+    import socket
+
+    with socket.socket(socket.AF_INET, socket.SOCK_STREAM) as sk:
+        sk.bind(("127.0.0.1", 0))
+        return int(sk.getsockname()[1])
 
 
 def _peer_worker(rank, world, port, q):
-    """Fused in-kernel exchange (NVLink peer memory) vs the NCCL bucket path, same data, same dropout bits."""
+    """Fused in-kernel exchange (NVLink peer memory) vs the NCCL bucket path (same data, same dropout bits), and vs a
+    one-GPU run on the concatenated batch (dropout off: SURVEY 8(e) "equal up to summation order")."""
     import torch.distributed as dist
 
     os.environ["MASTER_ADDR"] = "127.0.0.1"
@@ -86,48 +96,79 @@ def _peer_worker(rank, world, port, q):
     import wxddp
     from wxddp.engine import StepEngine
 
-    f, b, steps = 20, 4096 + 128 * rank, 6        # per-rank batches of different size are fine for the exchange itself
-    b = 4096
-    g = torch.Generator().manual_seed(100 + rank)
-    x = torch.randn(steps * b, f, generator=g).to(dev); y = (torch.rand(steps * b, generator=g) < 0.3).long().to(dev)
-    torch.manual_seed(5)
+    f, b, steps = 20, 8192, 6
+    g = torch.Generator().manual_seed(100)
+    x_all = torch.randn(steps, world, b, f, generator=g)                    # [step][rank][row][feature]
+    y_all = (torch.rand(steps, world, b, generator=g) < 0.3).long()
+    x = x_all[:, rank].reshape(steps * b, f).contiguous().to(dev)
+    y = y_all[:, rank].reshape(steps * b).contiguous().to(dev)
     res = {}
-    for name, use_peers in (("nccl", False), ("peer", True)):
+    for name, use_peers, mode in (("nccl", False, wxddp.DROPOUT_PHILOX), ("peer", True, wxddp.DROPOUT_PHILOX),
+                                  ("peer_nodrop", True, wxddp.DROPOUT_OFF)):
         torch.manual_seed(5)
         eng = StepEngine(f, device=dev, world=world, rank=rank, process_group=dist)
         if use_peers:
             eng.connect_peers()
         losses = []
         for s in range(steps):
-            l = eng.step(x, y, row0=s * b, batch=b, dropout=wxddp.DROPOUT_PHILOX)
+            l = eng.step(x, y, row0=s * b, batch=b, dropout=mode)
             losses.append(float(l.item()))
         torch.cuda.synchronize()
         res[name] = (losses, eng.params.cpu().numpy(), eng.ctx.tc_status(), int(eng.state[0].item()) if use_peers else steps)
         dist.barrier()
+    # raw-column form (what bench.py launches): standardisation fused, statistics merged across ranks
+    raw = (x.t().contiguous() * 7.0 + 50.0)
+    cols = [raw[j] for j in range(f)]
+    torch.manual_seed(5)
+    eng = StepEngine(f, device=dev, world=world, rank=rank, process_group=dist)
+    eng.fit_stats(cols)
+    eng.connect_peers()
+    raw_losses = [float(eng.step_raw(cols, y, row0=s * b, batch=b, dropout=wxddp.DROPOUT_OFF).item()) for s in range(steps)]
+    res["peer_raw"] = (raw_losses, eng.params.cpu().numpy(), eng.ctx.tc_status(), int(eng.state[0].item()))
+    dist.barrier()
+    if rank == 0:
+        # the same optimisation on ONE GPU over the concatenated batches
+        torch.manual_seed(5)
+        one = StepEngine(f, device=dev, world=1, rank=0)
+        xc = x_all.reshape(steps * world * b, f).contiguous().to(dev)
+        yc = y_all.reshape(steps * world * b).contiguous().to(dev)
+        l1 = [float(one.step(xc, yc, row0=s * world * b, batch=world * b, dropout=wxddp.DROPOUT_OFF).item())
+              for s in range(steps)]
+        res["single"] = (l1, one.params.cpu().numpy(), one.ctx.tc_status(), steps)
     q.put((rank, res))
+    dist.barrier()
     dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("world", [2])
+@pytest.mark.parametrize("world", [2, 4, 8])
 def test_in_kernel_peer_allreduce_matches_nccl_bucket_path(world):
     _need(world)
     import torch.multiprocessing as mp
 
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
-    procs = [ctx.Process(target=_peer_worker, args=(r, world, 29691, q)) for r in range(world)]
+    port = _free_port()
+    procs = [ctx.Process(target=_peer_worker, args=(r, world, port, q)) for r in range(world)]
     for p in procs:
         p.start()
-    out = sorted([q.get(timeout=600) for _ in range(world)], key=lambda t: t[0])
+    out = sorted([q.get(timeout=900) for _ in range(world)], key=lambda t: t[0])
     for p in procs:
         p.join(timeout=120)
         assert p.exitcode == 0
     for rank, res in out:
-        assert res["peer"][2] == 0 and res["peer"][3] == 6
+        for name in ("peer", "peer_nodrop", "peer_raw"):
+            assert res[name][2] == 0 and res[name][3] == 6, (rank, name, res[name][2:])
         np.testing.assert_allclose(res["peer"][0], res["nccl"][0], rtol=1e-5)              # rank-mean train_loss per step
         np.testing.assert_allclose(res["peer"][1], res["nccl"][1], rtol=1e-4, atol=1e-6)   # parameters after 6 Adam steps
-    np.testing.assert_array_equal(out[0][1]["peer"][1], out[1][1]["peer"][1])              # replicas bit-identical
-    np.testing.assert_allclose(out[0][1]["peer"][0], out[1][1]["peer"][0], rtol=0, atol=0)
+    for name in ("peer", "peer_nodrop", "peer_raw"):                                       # replicas stay bit-identical
+        for rank in range(1, world):
+            np.testing.assert_array_equal(out[0][1][name][1], out[rank][1][name][1])
+            assert out[0][1][name][0] == out[rank][1][name][0]
+    single = out[0][1]["single"]
+    np.testing.assert_allclose(out[0][1]["peer_nodrop"][0], single[0], rtol=2e-5)          # W ranks == one GPU, all rows
+    np.testing.assert_allclose(out[0][1]["peer_nodrop"][1], single[1], rtol=2e-4, atol=2e-6)
+    # raw columns standardised inside the step == the standardised rows (x*7+50 is undone by the statistics up to scale)
+    assert abs(out[0][1]["peer_raw"][0][0] - out[0][1]["peer_nodrop"][0][0]) < 0.2
 
 
 def _wide_worker(rank, world, port, q):
@@ -158,6 +199,15 @@ def _wide_worker(rank, world, port, q):
     dist.destroy_process_group()
 
 
+_PORT = {}
+
+
+def _free_port_once() -> int:
+    if "wide" not in _PORT:
+        _PORT["wide"] = _free_port()
+    return _PORT["wide"]
+
+
 def test_wide_ddp_overlapped_reduce():
     _need(2)
     import torch.multiprocessing as mp
@@ -165,7 +215,7 @@ def test_wide_ddp_overlapped_reduce():
 
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
-    procs = [ctx.Process(target=_wide_worker, args=(r, 2, 29681, q)) for r in range(2)]
+    procs = [ctx.Process(target=_wide_worker, args=(r, 2, _free_port_once(), q)) for r in range(2)]
     for p in procs:
         p.start()
     res = sorted([q.get(timeout=600) for _ in range(2)], key=lambda r: r[0])

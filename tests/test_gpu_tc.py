@@ -150,3 +150,120 @@ def test_tc_selftest_gemms(wx):
         assert st.item() == 0
         assert np.abs(z.cpu().numpy() - zref).max() <= tol * np.abs(zref).max()
         assert np.abs(gg.cpu().numpy() - gref).max() <= tol * np.abs(gref).max()
+
+
+# ---------------------------------------------------------------------------------------------
+# The configuration bench.py times (BASELINE.json configs[1]): F=20, 1 Mi rows per step, raw fp32 columns with nulls
+# and a constant column, Philox dropout, mean imputation -- ~55 tile-slots per CTA, so the landing ring, every mbarrier
+# phase bit and the TMEM-resident accumulators wrap many times.
+# ---------------------------------------------------------------------------------------------
+_BENCH = {}
+
+
+def bench_table(n_total=(1 << 20) + 4096, f=20):
+    """Raw table + oracle standardisation (oracle statistics), shared by the tests below."""
+    if "t" not in _BENCH:
+        rng = np.random.default_rng(77)
+        raw = np.empty((f, n_total), dtype=np.float32)
+        for j in range(f):
+            raw[j] = np.round(rng.normal(synth._MU[j % 5] + 3.0 * (j // 5), synth._SIGMA[j % 5] * (1 + 0.25 * (j // 5)),
+                                         size=n_total), 2).astype(np.float32)
+        raw[f - 1] = 42.5                                              # constant column: std guard (preprocess.py:36)
+        nulls = rng.random((f, n_total)) < 0.01
+        nulls[f - 1] = False
+        raw[nulls] = np.nan
+        z0 = (np.nan_to_num(raw[0], nan=20.0) - 20.0) / 8.0
+        z1 = (np.nan_to_num(raw[1], nan=65.0) - 65.0) / 20.0
+        y = ((-1.6 + 0.9 * z1 - 0.7 * z0 + rng.normal(0, 0.6, size=n_total)) > 0).astype(np.int64)
+        raw64 = raw.astype(np.float64)
+        st = [preprocess_ref.column_stats(raw64[j]) for j in range(f)]
+        stats = np.array([[c, m, (s or 0.0) ** 2 * (c - 1), preprocess_ref.std_guard(s)] for c, m, s in st])
+        feats = np.empty((n_total, f), dtype=np.float32)
+        for j in range(f):
+            feats[:, j] = preprocess_ref.zscore(raw64[j], stats[j, 1], stats[j, 3]).astype(np.float32)
+        feats[np.isnan(feats)] = 0.0                                   # WX_IMPUTE_MEAN
+        _BENCH["t"] = dict(raw=raw, y=y, stats=stats, feats=feats)
+    return _BENCH["t"]
+
+
+def _oracle_grads(p, feats, y, n, seed, step):
+    mask = torch.from_numpy(philox_ref.dropout_keep_mask(n, seed, step).astype(np.float32))
+    loss, grad = train_ref.loss_and_grads(p, feats.shape[1], torch.from_numpy(feats), torch.from_numpy(y), mask)
+    return float(loss), grad.numpy()
+
+
+@pytest.mark.parametrize("n,row0", [(1 << 20, 0), ((1 << 20) - 77, 2052)])
+def test_tc_grad_at_bench_configuration_matches_oracle(wx, n, row0):
+    """wx_tc_mlp_grad on 1 Mi rows (8192 tiles over 148 CTAs), full and with a ragged last tile at row0 != 0."""
+    t = bench_table()
+    f = 20
+    c = ctx_for(wx, f)
+    p = torch.randn(c.P, generator=torch.Generator().manual_seed(4)) * 0.2
+    seed, step = 42, 3
+    loss_ref, g_ref = _oracle_grads(p, t["feats"][row0:row0 + n], t["y"][row0:row0 + n], n, seed, step)
+    x = dev(t["feats"]); y = dev(t["y"])
+    out = c.tc_mlp_grad(p.cuda(), x, y, row0=row0, batch=n, dropout=wx.DROPOUT_PHILOX, seed=seed, step=step).cpu().numpy()
+    assert c.tc_status() == 0
+    np.testing.assert_allclose(out[-1], loss_ref, rtol=RTOL)
+    assert np.linalg.norm(out[:-1] - g_ref) <= 1e-5 * np.linalg.norm(g_ref)
+    np.testing.assert_allclose(out[:-1], g_ref, rtol=RTOL, atol=ATOL_G + 3.0 / n)      # + one row's contribution
+
+
+@pytest.mark.parametrize("n,row0", [(1 << 20, 0), ((1 << 20) - 77, 2052)])
+def test_tc_raw_step_at_bench_configuration_matches_oracle_and_ffma(wx, n, row0):
+    """wx_tc_train_step_raw exactly as bench.py launches it, against (i) the oracle: Adam's first step from zero state
+    gives m = 0.1 * grad, v = 0.001 * grad^2 and the parameter update, and (ii) wx_train_step_raw (FFMA kernel)."""
+    t = bench_table()
+    f = 20
+    c = ctx_for(wx, f)
+    p0 = torch.randn(c.P, generator=torch.Generator().manual_seed(4)) * 0.2
+    seed = 42
+    loss_ref, g_ref = _oracle_grads(p0, t["feats"][row0:row0 + n], t["y"][row0:row0 + n], n, seed, 0)
+    p_ref, m_ref, v_ref = p0.clone(), torch.zeros(c.P), torch.zeros(c.P)
+    train_ref.adam_update(p_ref, torch.from_numpy(g_ref), m_ref, v_ref, 1)
+    cols = [dev(t["raw"][j]) for j in range(f)]
+    y = dev(t["y"]); stats = dev(t["stats"])
+    res = {}
+    for name, fn in (("tc", c.tc_train_step_raw), ("ffma", c.train_step_raw)):
+        p = p0.cuda(); m = torch.zeros_like(p); v = torch.zeros_like(p)
+        st = torch.zeros(2, dtype=torch.int64, device="cuda"); loss = torch.zeros(1, device="cuda")
+        fn(p, m, v, st, cols, stats, y, loss, row0=row0, batch=n, impute=wx.IMPUTE_MEAN, dropout=wx.DROPOUT_PHILOX,
+           seed=seed)
+        torch.cuda.synchronize()
+        assert st.cpu().tolist() == [1, 0]
+        res[name] = (loss.item(), m.cpu().numpy(), p.cpu().numpy())
+    assert c.tc_status() == 0
+    for name in ("tc", "ffma"):
+        loss, m, p = res[name]
+        np.testing.assert_allclose(loss, loss_ref, rtol=RTOL, err_msg=name)
+        assert np.linalg.norm(m - m_ref.numpy()) <= 1e-5 * np.linalg.norm(m_ref.numpy()), name
+        np.testing.assert_allclose(m, m_ref.numpy(), rtol=RTOL, atol=0.1 * (ATOL_G + 3.0 / n), err_msg=name)
+        big = np.abs(g_ref) > 1e-4 * np.abs(g_ref).max()              # Adam's first step is lr*sign(g): skip g ~ 0
+        np.testing.assert_allclose(p[big], p_ref.numpy()[big], rtol=RTOL, atol=2e-7, err_msg=name)
+    np.testing.assert_allclose(res["tc"][1], res["ffma"][1], rtol=2 * RTOL, atol=0.1 * (2 * ATOL_G + 3.0 / n))
+
+
+def test_tc_raw_steps_track_the_oracle_over_several_steps(wx):
+    """Five consecutive fused steps over different 256 Ki-row windows (device step counter drives Philox and Adam's
+    bias correction): loss of every step and the final parameters against the oracle run on the same windows."""
+    t = bench_table()
+    f, n = 20, 1 << 18
+    c = ctx_for(wx, f)
+    p0 = torch.randn(c.P, generator=torch.Generator().manual_seed(6)) * 0.2
+    cols = [dev(t["raw"][j]) for j in range(f)]
+    y = dev(t["y"]); stats = dev(t["stats"])
+    p = p0.cuda(); m = torch.zeros_like(p); v = torch.zeros_like(p)
+    st = torch.zeros(2, dtype=torch.int64, device="cuda"); loss = torch.zeros(1, device="cuda")
+    p_ref, m_ref, v_ref = p0.clone(), torch.zeros(c.P), torch.zeros(c.P)
+    for s in range(5):
+        row0 = (s % 4) * n
+        c.tc_train_step_raw(p, m, v, st, cols, stats, y, loss, row0=row0, batch=n, impute=wx.IMPUTE_MEAN,
+                            dropout=wx.DROPOUT_PHILOX, seed=42)
+        loss_ref, g_ref = _oracle_grads(p_ref, t["feats"][row0:row0 + n], t["y"][row0:row0 + n], n, 42, s)
+        train_ref.adam_update(p_ref, torch.from_numpy(g_ref), m_ref, v_ref, s + 1)
+        np.testing.assert_allclose(loss.item(), loss_ref, rtol=1e-4)          # free-running: tolerance of the loss curve
+    assert c.tc_status() == 0 and st.cpu().tolist() == [5, 0]
+    # Adam's early steps are ~lr*sign(g): an entry whose gradient is within rounding of zero may move by a different
+    # +-0.01 (SURVEY 7, hard part 4), so the parameters are compared as a distribution, not entry by entry
+    d = np.abs(p.cpu().numpy() - p_ref.numpy())
+    assert np.quantile(d, 0.99) <= 1e-3 and d.max() <= 0.11
