@@ -32,13 +32,13 @@ struct Dim {
 };
 
 // ---------------------------------------------------------------------------------------------
-// Philox4x32-10 (Salmon et al., SC'11).  Dropout stream contract (WX_DROPOUT_PHILOX), one 64-bit keep mask per
-// batch position b (bit j = keep hidden unit j):
-//   key = (seed_lo, seed_hi); for q = 0..7: counter = (b_lo, b_hi, step_lo, (step_hi << 3) | q) -> words W[4q..4q+3];
-//   calls 0..3 serve hidden units 0..31, calls 4..7 units 32..63 (a thread that owns half a row needs only its four):
-//   the 32 words form 16 digit planes U_d = W[d] | W[16 + d] << 32 (d = 0 most significant): bit j of U_d is binary
-//   digit d of a 16-bit uniform u_j;  keep_j <=> u_j < 0xCCCD (= 52429, 52429/65536 = 0.80000305), evaluated for all
-//   64 units at once: lt = 0; for d = 15..0: lt = T_d ? (~U_d | lt) : (~U_d & lt), T = 0xCCCD MSB first.
+// Philox4x32-10 (Salmon et al., SC'11).  Dropout stream contract (WX_DROPOUT_PHILOX; specified in oracle/philox_ref.py):
+// one 64-bit keep mask per batch position b (bit j = keep hidden unit j) from TWO Philox calls q = 0, 1,
+//   key = (seed_lo, seed_hi), counter = (b_lo, b_hi, step_lo, (step_hi << 3) | q) -> words W[4q .. 4q+3];
+// word W[k] serves units 8k .. 8k+7 through its first eight base-5 digits:
+//   s_0 = W[k]; digit_t = hi32(5 * s_t); s_{t+1} = lo32(5 * s_t);   keep_{8k+t} <=> digit_t != 0
+// so P(keep) = 1 - ceil(2^32 / 5) / 2^32 = 0.8 (nn.Dropout(0.2), train_lightning_ddp.py:60) at one 32x32->64 multiply
+// per unit.
 // ---------------------------------------------------------------------------------------------
 __device__ __forceinline__ uint4 philox4x32_10(uint4 c, uint2 k) {
     constexpr uint32_t M0 = 0xD2511F53u, M1 = 0xCD9E8D57u, W0 = 0x9E3779B9u, W1 = 0xBB67AE85u;
@@ -52,51 +52,42 @@ __device__ __forceinline__ uint4 philox4x32_10(uint4 c, uint2 k) {
     }
     return c;
 }
-constexpr uint32_t PHILOX_KEEP_THRESH = 52429u;   // 0xCCCD
 
-// digits d0 .. d0+3 of the comparison, most significant of the four last (call order: d = d0+3, .., d0)
-__device__ __forceinline__ uint64_t keep_digits4(uint64_t lt, const uint32_t (&w)[8], int d0) {
-#pragma unroll
-    for (int k = 3; k >= 0; --k) {
-        const uint64_t u = uint64_t(w[2 * k]) | (uint64_t(w[2 * k + 1]) << 32);
-        const bool t = (PHILOX_KEEP_THRESH >> (15 - (d0 + k))) & 1u;
-        lt = t ? (~u | lt) : (~u & lt);
-    }
-    return lt;
+// one base-5 digit: returns digit != 0 (keep) and advances the state
+__device__ __forceinline__ bool keep_digit(uint32_t& s) {
+    const uint64_t prod = uint64_t(s) * 5ull;
+    s = uint32_t(prod);
+    return uint32_t(prod >> 32) != 0u;
 }
 
-// the whole 64-bit keep mask of batch position b (8 Philox calls); used where one thread owns a row
-__device__ __forceinline__ uint64_t philox_keep_mask(uint64_t b, uint2 key, uint64_t step) {
-    uint64_t lt = 0;
-#pragma unroll 1
-    for (int sub = 3; sub >= 0; --sub) {
-        uint32_t w[8];
+// keep bits of units 8k .. 8k+7 (bit t = unit 8k+t) from word W[k]
+__device__ __forceinline__ uint32_t keep8_from_word(uint32_t s) {
+    uint32_t bits = 0;
 #pragma unroll
-        for (int h = 0; h < 2; ++h) {          // call sub: low halves of planes 4sub..4sub+3; call 4+sub: high halves
-            const uint4 o = philox4x32_10(make_uint4(uint32_t(b), uint32_t(b >> 32), uint32_t(step),
-                                                     (uint32_t(step >> 32) << 3) | uint32_t(4 * h + sub)), key);
-            w[h] = o.x; w[2 + h] = o.y; w[4 + h] = o.z; w[6 + h] = o.w;
-        }
-        lt = keep_digits4(lt, w, 4 * sub);
-    }
-    return lt;
+    for (int t = 0; t < 8; ++t) bits |= uint32_t(keep_digit(s)) << t;
+    return bits;
 }
 
-// keep bits of units 32*half .. 32*half+31 of batch position b: the four Philox calls of that half
-__device__ __forceinline__ uint32_t philox_keep_half(uint64_t b, int half, uint2 key, uint64_t step) {
-    uint32_t lt = 0;
-#pragma unroll 1
-    for (int sub = 3; sub >= 0; --sub) {
+// the eight words of batch position b (two Philox calls)
+__device__ __forceinline__ void philox_keep_words(uint64_t b, uint2 key, uint64_t step, uint32_t (&w)[8]) {
+#pragma unroll
+    for (int q = 0; q < 2; ++q) {
         const uint4 o = philox4x32_10(make_uint4(uint32_t(b), uint32_t(b >> 32), uint32_t(step),
-                                                 (uint32_t(step >> 32) << 3) | uint32_t(4 * half + sub)), key);
-        const uint32_t w[4] = {o.x, o.y, o.z, o.w};
-#pragma unroll
-        for (int k = 3; k >= 0; --k) {
-            const bool t = (PHILOX_KEEP_THRESH >> (15 - (4 * sub + k))) & 1u;
-            lt = t ? (~w[k] | lt) : (~w[k] & lt);
-        }
+                                                 (uint32_t(step >> 32) << 3) | uint32_t(q)), key);
+        w[4 * q] = o.x; w[4 * q + 1] = o.y; w[4 * q + 2] = o.z; w[4 * q + 3] = o.w;
     }
-    return lt;
+}
+
+// keep bits of units 32q .. 32q+31 of batch position b: Philox call q
+__device__ __forceinline__ uint32_t philox_keep_half(uint64_t b, int q, uint2 key, uint64_t step) {
+    const uint4 o = philox4x32_10(make_uint4(uint32_t(b), uint32_t(b >> 32), uint32_t(step),
+                                             (uint32_t(step >> 32) << 3) | uint32_t(q)), key);
+    return keep8_from_word(o.x) | (keep8_from_word(o.y) << 8) | (keep8_from_word(o.z) << 16) | (keep8_from_word(o.w) << 24);
+}
+
+// the whole 64-bit keep mask of batch position b; used where one thread owns a row
+__device__ __forceinline__ uint64_t philox_keep_mask(uint64_t b, uint2 key, uint64_t step) {
+    return uint64_t(philox_keep_half(b, 0, key, step)) | (uint64_t(philox_keep_half(b, 1, key, step)) << 32);
 }
 
 __device__ __forceinline__ void cp_async4(void* smem_dst, const void* gsrc) {
@@ -243,28 +234,14 @@ __device__ __forceinline__ uint32_t chunk_keep_bits(int mode, const ChunkMeta& c
         }
         return kb;
     }
-    // WX_DROPOUT_PHILOX: lane -> (row r = lane >> 2 of the chunk, quarter sub = lane & 3 of that row's 8 Philox calls).
-    // The four lanes of a row chain their digit planes (sub 3 -> 0) with shuffles, then every lane picks its two
-    // units' bits out of each row's mask.
-    const int sub = lane & 3;
+    // WX_DROPOUT_PHILOX: lane -> (row r = lane >> 2 of the chunk, Philox call q = lane & 1 of that row): lane 4r holds the
+    // keep bits of units 0..31 of row r, lane 4r+1 those of units 32..63; every lane then picks its two units' bits.
     const uint64_t b = uint64_t(chunk_pos0) + uint64_t(lane >> 2);
-    uint32_t w[8];
-#pragma unroll
-    for (int h = 0; h < 2; ++h) {
-        const uint4 o = philox4x32_10(make_uint4(uint32_t(b), uint32_t(b >> 32), step_lo, (step_hi << 3) | uint32_t(4 * h + sub)), key);
-        w[h] = o.x; w[2 + h] = o.y; w[4 + h] = o.z; w[6 + h] = o.w;
-    }
-    uint64_t cur = 0;
-#pragma unroll
-    for (int st = 3; st >= 0; --st) {
-        const uint64_t mine = keep_digits4(cur, w, 4 * sub);                 // meaningful on the lane with sub == st
-        cur = __shfl_sync(0xffffffffu, mine, (lane & ~3) | st);
-    }
-    const uint32_t mlo = uint32_t(cur), mhi = uint32_t(cur >> 32);
+    const uint32_t half = philox_keep_half(b, lane & 1, key, (uint64_t(step_hi) << 32) | step_lo);
 #pragma unroll
     for (int r = 0; r < R; ++r) {
-        const uint32_t lo = __shfl_sync(0xffffffffu, mlo, 4 * r);
-        const uint32_t hi = __shfl_sync(0xffffffffu, mhi, 4 * r);
+        const uint32_t lo = __shfl_sync(0xffffffffu, half, 4 * r);
+        const uint32_t hi = __shfl_sync(0xffffffffu, half, 4 * r + 1);
         kb |= ((lo >> lane) & 1u) << (2 * r);
         kb |= ((hi >> lane) & 1u) << (2 * r + 1);
     }

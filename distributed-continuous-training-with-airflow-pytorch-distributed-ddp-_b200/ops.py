@@ -268,10 +268,10 @@ class Context:
         self.peer_world = world
 
     # -- kernel choice --------------------------------------------------------------------------------
-    TC_MAX_FEATURES = 29
+    TC_MAX_FEATURES = 31
 
     def tc_ok_rowmajor(self, x, y, row0: int, row_idx=None) -> bool:
-        """True when the tensor-core step kernel can take this batch (contiguous rows, F <= 29, TMA alignment)."""
+        """True when the tensor-core step kernel can take this batch (contiguous rows, F <= 31, TMA alignment)."""
         return (row_idx is None and self.n_features <= self.TC_MAX_FEATURES
                 and (x.data_ptr() + row0 * self.n_features * 4) % 16 == 0 and (y.data_ptr() + row0 * 8) % 16 == 0)
 

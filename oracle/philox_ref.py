@@ -10,7 +10,6 @@ import numpy as np
 
 M0, M1 = np.uint64(0xD2511F53), np.uint64(0xCD9E8D57)
 W0, W1 = 0x9E3779B9, 0xBB67AE85
-KEEP_THRESH = 52429        # 0xCCCD; P(keep) = 52429/65536
 
 
 def philox4x32_10(c0, c1, c2, c3, k0, k1):
@@ -33,22 +32,23 @@ def philox4x32_10(c0, c1, c2, c3, k0, k1):
 def dropout_keep_mask(batch: int, seed: int, step: int) -> np.ndarray:
     """[batch, 64] bool keep mask the kernels use for (seed, step): batch position b, hidden unit j.
 
-    For q = 0..7: counter (b_lo, b_hi, step_lo, (step_hi << 3) | q) -> words W[4q..4q+3] (calls 0..3 serve units
-    0..31, calls 4..7 units 32..63); digit plane U_d = W[d] | W[16 + d] << 32 (d = 0 most significant); bit j of U_d
-    is binary digit d of a 16-bit uniform u_j; keep_j <=> u_j < 0xCCCD.
+    Two Philox calls per batch position, q = 0, 1: counter (b_lo, b_hi, step_lo, (step_hi << 3) | q), key = seed
+    -> words W[4q .. 4q+3].  Word W[k] serves hidden units 8k .. 8k+7 through its first eight base-5 digits:
+        s_0 = W[k];   s_{t+1} = (5 * s_t) mod 2^32;   digit_t = floor(5 * s_t / 2^32)  in {0..4}
+    and keep_{8k+t} <=> digit_t != 0, i.e. P(keep) = 1 - ceil(2^32 / 5) / 2^32 = 0.8 to within 1e-10 (the reference's
+    nn.Dropout(0.2), train_lightning_ddp.py:60).  One 32x32->64 multiply per unit in the kernels.
     """
     b = np.arange(batch, dtype=np.uint64)
     b_lo = (b & np.uint64(0xFFFFFFFF)).astype(np.uint32)
     b_hi = (b >> np.uint64(32)).astype(np.uint32)
-    words = np.empty((32, batch), dtype=np.uint32)
-    for q in range(8):
+    keep = np.empty((batch, 64), dtype=bool)
+    for q in range(2):
         c3 = np.uint32((((step >> 32) << 3) | q) & 0xFFFFFFFF)
         out = philox4x32_10(b_lo, b_hi, np.uint32(step & 0xFFFFFFFF), c3, seed & 0xFFFFFFFF, (seed >> 32) & 0xFFFFFFFF)
         for i in range(4):
-            words[4 * q + i] = out[i]
-    u = np.zeros((batch, 64), dtype=np.uint32)                      # the 16-bit uniform of every (row, unit)
-    for d in range(16):
-        plane = words[d].astype(np.uint64) | (words[16 + d].astype(np.uint64) << np.uint64(32))
-        bits = ((plane[:, None] >> np.arange(64, dtype=np.uint64)) & np.uint64(1)).astype(np.uint32)
-        u |= bits << np.uint32(15 - d)
-    return u < KEEP_THRESH
+            s = out[i].astype(np.uint64)
+            for t in range(8):
+                prod = s * np.uint64(5)
+                keep[:, 8 * (4 * q + i) + t] = (prod >> np.uint64(32)) != 0
+                s = prod & np.uint64(0xFFFFFFFF)
+    return keep

@@ -71,7 +71,7 @@ def test_tc_fused_step_matches_reference_module(wx, tag):
 
 
 @pytest.mark.parametrize("f,n,row0,mode", [(20, 128, 0, 0), (20, 100, 0, 1), (5, 257, 0, 2), (20, 1000, 128, 1),
-                                           (29, 3000, 0, 1), (1, 500, 0, 0), (13, 999, 12, 2), (7, 1, 0, 0),
+                                           (29, 3000, 0, 1), (31, 2000, 0, 2), (8, 1500, 0, 2), (16, 700, 0, 1), (24, 300, 0, 0), (1, 500, 0, 0), (13, 999, 12, 2), (7, 1, 0, 0),
                                            (20, 56909, 0, 0), (5, 70001, 4, 2)])
 def test_tc_grad_against_oracle_and_ffma_kernel(wx, f, n, row0, mode):
     c = ctx_for(wx, f)
