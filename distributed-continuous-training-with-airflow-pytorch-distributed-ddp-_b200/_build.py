@@ -22,6 +22,7 @@ NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", 
 UNITS = [("ctx.cu", "ctx.o", []), ("preprocess.cu", "preprocess.o", []), ("mlp_host.cu", "mlp_host.o", []),
          ("tc_selftest.cu", "tc_selftest.o", []), ("tc_step.cu", "tc_step.o", []), ("wide.cu", "wide.o", [])]
 UNITS += [("mlp_inst.cu", f"mlp_inst_g{g}.o", [f"-DWX_F_GROUP={g}"]) for g in range(4)]
+UNITS += [("tc_step_inst.cu", f"tc_step_ft{ft}.o", [f"-DWX_TC_FT={ft}"]) for ft in (0, 5, 20)]
 EXTRA_UNITS: list[tuple[str, str, list[str]]] = []
 
 

@@ -1,759 +1,23 @@
-// Tensor-core (tcgen05) version of the fused weather-MLP step: [standardise +] forward + cross-entropy + backward
-// (+ DDP exchange + Adam).  Replaces /root/reference/jobs/train_lightning_ddp.py:57-71,:88,:136 (and, with the
-// raw-column loader, /root/reference/jobs/preprocess.py:38-41) like mlp_grid_kernel, with the two F x 64 contractions
-// on the 5th-generation tensor cores and as little per-row CUDA-core work as the arithmetic allows:
-//
-//   GEMM1   z[128 x 64]    = D[128 x K1] . W1s[64 x K1]^T           M=128 N=64  K1 = ceil((F+1)/8)*8   K-major, SW128
-//   GEMM2   T[64 x 2 K1]  += Gate[128 x 64]^T . [U_hi | U_lo]       M=64  N=2K1 K = 128 rows           MN-major, SW128_B32
-//
-//   D     = [d_0 .. d_{F-1}, 1, 0..]      d_c = x_c - float(mean_c): the raw column, centred only.  The scale 1/std and
-//           the fp32 remainder of the mean are folded into the weights once per launch:
-//           W1s[n] = [W1[n][c] / std_c .., b1[n] - sum_c W1[n][c] (mean_c - float(mean_c)) / std_c]   (computed in fp64)
-//           so standardisation ((x - mean) / std, preprocess.py:38-41) costs ONE subtraction per cell on the CUDA cores.
-//   Gate  = 1.0 where the unit is active (z > 0 and kept by dropout), else 0.0 -- exact in tf32, so GEMM2 needs no
-//           hi/lo split of its A operand and the same Gate tile serves the hi and the lo half of U in ONE pass.
-//   U     = delta * D with delta = (dl0 - dl1) / 2: for two classes the logit gradients are dl1 = -dl0 (softmax - onehot
-//           sums to zero; their fp32 values differ by a rounding of 1/batch at most), hence with ds = 1/(1-p)
-//               dh[r][j]  = gate[r][j] * delta[r] * ds (W2[0][j] - W2[1][j])
-//               dW1[j][c] = ds (W2[0][j] - W2[1][j]) / std_c * (T[j][c] - (mean_c - float(mean_c)) T[j][F]),   db1[j] = (..) T[j][F]
-//           applied once per CTA when T leaves tensor memory.  T accumulates in TMEM over ALL tiles of the CTA.
-//
-// fp32 accuracy on tf32 tensor cores: x = hi + lo (hi = x rounded to 11 significant bits, lo exact); GEMM1 sums
-// hi*lo + lo*hi + hi*hi (~2^-21 relative); GEMM2's A operand is exact, so hi + lo of U alone gives the same accuracy.
-// dW2 / db2 / loss are row-local sums: dW2 lives in per-thread TMEM columns (packed fp32x2 FMAs), db2 / loss in registers.
-//
-// Roles (320 threads, one CTA per SM, persistent over 128-row tiles; tile i belongs to worker group i & 1):
-//   warps 0-3 / 4-7  two row-worker groups: thread r <-> tile row r <-> TMEM lane r (row-local work, no shuffles)
-//   warp 8           TMA producer (cp.async.bulk of rows or F column segments + labels [+ keep bits], 2-3 stage ring)
-//   warp 9           MMA issuer (whole warp runs the loop, elect.sync picks the issuing lane)
-// Tail: CTA slabs are summed by a two-level ticket tree (12 CTAs per group, then the groups) in fixed order -- the
-// result is bit-reproducible -- then the cross-rank exchange (csrc/peer.cuh) and Adam run in the last CTA.
-#include <math.h>
-#include <stddef.h>
+// Host API of the tensor-core step kernel (csrc/tc_step_kernel.cuh): argument checks behind the C ABI.  The kernel is
+// compiled three times (csrc/tc_step_inst.cu): for F = 20 and F = 5 with the feature count as a compile-time constant
+// (BASELINE.json configs[1] and the reference's own table, preprocess.py:29), and once for any other F <= 31.
 #include <string.h>
 
 #include "mlp_kernels.cuh"
-#include "tc_common.cuh"
+
+int wx_tc_launch_ft0(wx_ctx* ctx, wxk::GridArgs& a, cudaStream_t st, const char* who);
+int wx_tc_launch_ft5(wx_ctx* ctx, wxk::GridArgs& a, cudaStream_t st, const char* who);
+int wx_tc_launch_ft20(wx_ctx* ctx, wxk::GridArgs& a, cudaStream_t st, const char* who);
 
 namespace {
-using namespace wxtc;
-using wxk::AdamScalars;
 using wxk::GridArgs;
 
-constexpr int TILE = 128;
-constexpr int NGROUPS = 2;
-constexpr int WORKERS = NGROUPS * TILE;          // 256 row-worker threads
-constexpr int TC_THREADS = WORKERS + 64;         // + producer warp + MMA warp
-constexpr int PRODUCER_WARP = WORKERS / 32, MMA_WARP = WORKERS / 32 + 1;
-constexpr int MAX_STAGES = 3;
-constexpr int MAXF_TC = 31;                      // F feature columns + the ones column fit the 32-column operand tile
-constexpr int TMEM_COLS = 512;                   // D1 x2 [0,128) | T [128,192) | dW2 sums of group g [256+128g, 384+128g)
-constexpr int TM_T = 128, TM_ACC = 256;
-constexpr int GROUP_CTAS = 12;                   // fan-in of the slab reduction tree
-constexpr int TICKET_GROUP0 = 16, TICKET_TOP = 40;   // words of the ticket block (common.cuh: 64 words, 1/2/8 in use)
-constexpr int SMEM_LIMIT = 232448 - 1024;        // 227 KB per CTA on sm_100, minus the static block (a flag, padded to the 1024-byte alignment of the dynamic part)
-
-enum { DROP_OFF = WX_DROPOUT_OFF, DROP_MASK = WX_DROPOUT_MASK, DROP_PHILOX = WX_DROPOUT_PHILOX };
-
-struct TcSmem {
-    // operand tiles (all 1024-byte aligned)
-    float w_hi[64 * 32], w_lo[64 * 32];          // W1s  [n][32]     K-major SW128         (GEMM1 B)
-    float xk_hi[TILE * 32], xk_lo[TILE * 32];    // D    [row][32]   K-major SW128         (GEMM1 A)
-    float gate[NGROUPS][TILE * 64];              // Gate [k=row][m=64]  MN-major SW128_B32 (GEMM2 A); reused by the final reductions
-    float u[NGROUPS][TILE * 64];                 // U    [k=row][n: hi | lo] MN-major SW128_B32 (GEMM2 B); u[0]/u[1] hold the slab / bucket at the end
-    float2 w2p[64];                              // ds * (W2[0][j], W2[1][j])
-    float b2[2];
-    __align__(16) float mean_hi[32];             // raw loader: float(mean_c)
-    float col_scale[32], col_shift[32];          // epilogue: 1/std_c and (mean_c - float(mean_c)) as floats
-    float red_small[WORKERS / 32][4];            // db2_0, db2_1, loss per worker warp
-    uint64_t land_full[MAX_STAGES], land_empty[MAX_STAGES];
-    uint64_t xk_ready, a2_ready[NGROUPS], a2_free[NGROUPS], d1_full[NGROUPS];
-    uint32_t tmem_base;
-    int err;
-    int role;                                    // 0 = not last, 1 = last of its group, 2 = last of the grid
-    AdamScalars adam;
-    __align__(128) unsigned char landing[128];   // ring: stages x { x[TILE*F] fp32 | y[TILE] i64 | keep[TILE] u64 } (dynamic size)
-};
-
-__device__ __forceinline__ void st4(void* base, uint32_t off, float a, float b, float c, float d) {
-    *reinterpret_cast<float4*>(static_cast<unsigned char*>(base) + off) = make_float4(a, b, c, d);
-}
-__device__ __forceinline__ void tmem_ld32(uint32_t taddr, float (&v)[32]) {
-    float a[16], b[16];
-    tmem_ld16(taddr, a);
-    tmem_ld16(taddr + 16, b);
-#pragma unroll
-    for (int i = 0; i < 16; ++i) {
-        v[i] = a[i];
-        v[16 + i] = b[i];
-    }
-}
-
-struct TcGeom {
-    int stages;          // landing ring depth (2 or 3)
-    int x_bytes;         // TILE * F * 4 rounded up to 128
-    int stage_bytes;     // x_bytes + 2 * TILE * 8
-};
-
-// RAW : raw-column loader (column segments [F][128] in the landing buffer, centred on the way) vs dense row-major rows.
-// DROP: dropout mode -- compile-time so the per-unit keep test is one multiply (Philox digits) or one bit test (mask).
-template <bool RAW, int DROP>
-__global__ void __launch_bounds__(TC_THREADS, 1) tc_step_kernel(const GridArgs a, const int F, const TcGeom geo,
-                                                                int* __restrict__ err_out) {
-    extern __shared__ __align__(1024) unsigned char raw[];     // 1024-byte alignment: the swizzle atoms need it
-    TcSmem& s = *reinterpret_cast<TcSmem*>(raw);               // direct cast keeps the shared address space (LDS/STS)
-    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const int P = 64 * F + 194;
-    const int OFF_B1 = 64 * F, OFF_W2 = 64 * F + 64, OFF_B2 = 64 * F + 192;
-    const int slab_stride = (P + 1 + 3) & ~3;
-    const int K1 = (F + 1 + 7) & ~7;              // GEMM1 K extent: features | 1 at column F | zeros
-    const int N2 = 2 * K1;                        // GEMM2 N extent: [U_hi | U_lo]
-    const int nfull = F >> 3;                     // column groups of 8 that hold features only
-    const int64_t ntiles = (a.batch + TILE - 1) / TILE;
-    const int64_t my_tiles = (ntiles - blockIdx.x + gridDim.x - 1) / gridDim.x;     // >= 1 by construction of the grid
-    const float ds = DROP != DROP_OFF ? 1.25f : 1.0f;           // 1/(1-0.2), train_lightning_ddp.py:60
-
-    if (tid == 0 && (smem_u32(raw) & 1023u) != 0) atomicExch(err_out, 99);   // dynamic smem base not 1024-aligned
-    if (tid == 0) {
-        for (int i = 0; i < MAX_STAGES; ++i) {
-            mbar_init(&s.land_full[i], 1);
-            mbar_init(&s.land_empty[i], TILE);
-        }
-        mbar_init(&s.xk_ready, TILE);
-        for (int g = 0; g < NGROUPS; ++g) {
-            mbar_init(&s.a2_ready[g], TILE);
-            mbar_init(&s.a2_free[g], 1);
-            mbar_init(&s.d1_full[g], 1);
-        }
-        fence_mbar_init();
-        s.err = 0;
-    }
-    if (warp == 0) tmem_alloc(&s.tmem_base, TMEM_COLS);
-    // W1s operand (hi/lo, K-major SW128), one thread per hidden unit; fp64 so that folding 1/std and the mean remainder
-    // into the weights costs no accuracy (the products are rounded to fp32 once, like W1 itself)
-    if (tid < 64) {
-        const int n = tid;
-        double shift = 0.0;
-#pragma unroll 1
-        for (int c4 = 0; c4 < 8; ++c4) {
-            float hi[4], lo[4];
-#pragma unroll
-            for (int e = 0; e < 4; ++e) {
-                const int c = c4 * 4 + e;
-                float v = 0.0f;
-                if (c < F) {
-                    double w = double(a.params[n * F + c]);
-                    if (RAW) {
-                        const double mean = a.stats[c * 4 + 1], rs = 1.0 / a.stats[c * 4 + 3];
-                        w *= rs;
-                        shift += w * (mean - double(float(mean)));
-                    }
-                    v = float(w);
-                }
-                split_tf32(v, hi[e], lo[e]);
-            }
-            const uint32_t off = sw128_offset(n, c4 * 4);
-            st4(s.w_hi, off, hi[0], hi[1], hi[2], hi[3]);
-            st4(s.w_lo, off, lo[0], lo[1], lo[2], lo[3]);
-        }
-        float bh, bl;
-        split_tf32(float(double(a.params[OFF_B1 + n]) - shift), bh, bl);
-        const uint32_t off = sw128_offset(n, F);
-        *reinterpret_cast<float*>(reinterpret_cast<unsigned char*>(s.w_hi) + off) = bh;
-        *reinterpret_cast<float*>(reinterpret_cast<unsigned char*>(s.w_lo) + off) = bl;
-        s.w2p[n] = make_float2(ds * a.params[OFF_W2 + n], ds * a.params[OFF_W2 + 64 + n]);
-    } else if (tid < 96) {
-        const int c = tid - 64;
-        float mh = 0.0f, sc = 1.0f, sh = 0.0f;
-        if (RAW && c < F) {
-            const double mean = a.stats[c * 4 + 1];
-            mh = float(mean);
-            sc = float(1.0 / a.stats[c * 4 + 3]);
-            sh = float(mean - double(mh));
-        }
-        s.mean_hi[c] = mh;
-        s.col_scale[c] = sc;
-        s.col_shift[c] = sh;
-        if (c < 2) s.b2[c] = a.params[OFF_B2 + c];
-    }
-    fence_proxy_async();
-    tc_fence_before();
-    __syncthreads();
-    tc_fence_after();
-    const uint32_t tm = s.tmem_base;
-    const uint64_t step_word = (a.state != nullptr) ? uint64_t(a.state[0]) : a.step;
-
-    auto tile_rows = [&](int64_t t) -> int {
-        const int64_t left = a.batch - t * TILE;
-        return left < TILE ? int(left) : TILE;
-    };
-    auto land_x = [&](int st) -> float* { return reinterpret_cast<float*>(s.landing + size_t(st) * geo.stage_bytes); };
-    auto land_y = [&](int st) -> long long* {
-        return reinterpret_cast<long long*>(s.landing + size_t(st) * geo.stage_bytes + geo.x_bytes);
-    };
-    auto land_m = [&](int st) -> unsigned long long* {
-        return reinterpret_cast<unsigned long long*>(s.landing + size_t(st) * geo.stage_bytes + geo.x_bytes + TILE * 8);
-    };
-
-    if (warp == PRODUCER_WARP) {
-        // ================= TMA producer =================
-        const int S = geo.stages;
-        int st = 0;
-        uint32_t round = 0;                      // how many times the ring has wrapped
-        for (int64_t i = 0; i < my_tiles; ++i) {
-            const int64_t tile = blockIdx.x + i * gridDim.x;
-            if (round > 0 && !mbar_wait(&s.land_empty[st], (round - 1) & 1u)) s.err = 2;
-            const int nr = tile_rows(tile);
-            const int64_t row = a.row0 + tile * TILE;
-            float* lx = land_x(st);
-            if (nr == TILE) {           // full tile: every size is a multiple of 16 B; start alignment is checked on the host
-                const uint32_t by = TILE * 8;
-                if (lane == 0)
-                    mbar_arrive_expect_tx(&s.land_full[st], uint32_t(TILE) * F * 4 + by + (DROP == DROP_MASK ? by : 0u));
-                __syncwarp();
-                if (!RAW) {
-                    if (lane == 0) bulk_g2s(lx, a.x + row * F, uint32_t(TILE) * F * 4, &s.land_full[st]);
-                } else if (lane < F) {  // one 512-byte column segment per lane
-                    bulk_g2s(lx + lane * TILE, static_cast<const float*>(a.cols.col[lane]) + row, TILE * 4, &s.land_full[st]);
-                }
-                if (lane == 0) {
-                    bulk_g2s(land_y(st), a.y + row, by, &s.land_full[st]);
-                    if (DROP == DROP_MASK) bulk_g2s(land_m(st), a.keep_mask + tile * TILE, by, &s.land_full[st]);
-                }
-            } else {
-                // ragged last tile: plain loads by the whole warp; rows past the end are filled with values that centre
-                // to exactly zero (they must not put NaN into the operand tiles), then a normal arrive
-                if (!RAW) {
-                    const float* gx = a.x + row * F;
-                    for (int e = lane; e < TILE * F; e += 32) lx[e] = e < nr * F ? gx[e] : 0.0f;
-                } else {
-                    for (int c = 0; c < F; ++c)
-                        for (int e = lane; e < TILE; e += 32)
-                            lx[c * TILE + e] = e < nr ? static_cast<const float*>(a.cols.col[c])[row + e] : s.mean_hi[c];
-                }
-                for (int e = lane; e < TILE; e += 32) {
-                    land_y(st)[e] = e < nr ? a.y[row + e] : 0;
-                    if (DROP == DROP_MASK) land_m(st)[e] = e < nr ? a.keep_mask[tile * TILE + e] : 0ull;
-                }
-                __threadfence_block();
-                __syncwarp();
-                if (lane == 0) mbar_arrive(&s.land_full[st]);
-            }
-            if (++st == S) {
-                st = 0;
-                ++round;
-            }
-        }
-    } else if (warp == MMA_WARP) {
-        // ================= MMA issuer =================
-        // The WHOLE warp runs this code and one elected lane issues each MMA: operands stay warp-uniform (uniform
-        // registers) -- 3x faster issue than a lone thread.  One base descriptor per operand; a k-step only adds a
-        // constant to the start-address field.
-        const uint32_t id1 = make_idesc_tf32(128, 64, false, false);
-        const uint32_t id2 = make_idesc_tf32(64, N2, true, true);
-        const uint64_t xk_d[2] = {make_smem_desc(smem_u32(s.xk_hi), 16, 1024), make_smem_desc(smem_u32(s.xk_lo), 16, 1024)};
-        const uint64_t wk_d[2] = {make_smem_desc(smem_u32(s.w_hi), 16, 1024), make_smem_desc(smem_u32(s.w_lo), 16, 1024)};
-        // group 1's tiles sit 32 KB after group 0's: + 2048 in the start-address field (16-byte units)
-        const uint64_t gate_d0 = make_smem_desc(smem_u32(s.gate[0]), 512, 1024, LAYOUT_SW128_B32);
-        const uint64_t u_d0 = make_smem_desc(smem_u32(s.u[0]), 512, 1024, LAYOUT_SW128_B32);
-        constexpr uint64_t GROUP_STEP = sizeof(float) * TILE * 64 / 16;
-        const int k1steps = K1 / 8;
-        auto gemm1 = [&](uint32_t dst) {
-            bool acc = false;                    // small terms first: hi*lo, lo*hi, then hi*hi
-#pragma unroll
-            for (int term = 0; term < 3; ++term) {
-                const uint64_t ad = xk_d[term == 1 ? 1 : 0], bd = wk_d[term == 0 ? 1 : 0];
-#pragma unroll 1
-                for (int k = 0; k < k1steps; ++k) {
-                    umma_tf32_warp(dst, ad + uint64_t(k * 2), bd + uint64_t(k * 2), id1, acc);       // +32 B per k-step
-                    acc = true;
-                }
-            }
-        };
-        auto gemm2 = [&](int g, bool first) {
-            bool acc = !first;
-            const uint64_t gd = gate_d0 + uint64_t(g) * GROUP_STEP, ud = u_d0 + uint64_t(g) * GROUP_STEP;
-#pragma unroll
-            for (int k = 0; k < TILE / 8; ++k) {
-                umma_tf32_warp(tm + TM_T, gd + uint64_t(k * 128), ud + uint64_t(k * 128), id2, acc);   // +2048 B
-                acc = true;
-            }
-        };
-        for (int64_t i = 0; i < my_tiles; ++i) {
-            if (!mbar_wait_hot(&s.xk_ready, uint32_t(i & 1))) s.err = 3;
-            tc_fence_after();
-            gemm1(tm + uint32_t(i & 1) * 64);
-            umma_commit_warp(&s.d1_full[i & 1]);
-            if (i > 0) {
-                const int g = int((i - 1) & 1);
-                if (!mbar_wait_hot(&s.a2_ready[g], uint32_t(((i - 1) >> 1) & 1))) s.err = 4;
-                tc_fence_after();
-                gemm2(g, i - 1 == 0);
-                umma_commit_warp(&s.a2_free[g]);
-            }
-        }
-        const int g = int((my_tiles - 1) & 1);
-        if (!mbar_wait_hot(&s.a2_ready[g], uint32_t(((my_tiles - 1) >> 1) & 1))) s.err = 4;
-        tc_fence_after();
-        gemm2(g, my_tiles - 1 == 0);
-        umma_commit_warp(&s.a2_free[g]);
-    } else {
-        // ================= row workers: group 0 = warps 0-3, group 1 = warps 4-7 =================
-        const int grp = warp >> 2;
-        const int r = tid & (TILE - 1);                           // tile row == TMEM lane
-        const uint32_t lane_addr = uint32_t((warp & 3) * 32) << 16;
-        const uint32_t acc_base = tm + TM_ACC + uint32_t(grp) * 128 + lane_addr;
-        const uint32_t d1 = tm + uint32_t(grp) * 64 + lane_addr;
-        const uint2 key = make_uint2(uint32_t(a.seed), uint32_t(a.seed >> 32));
-        float gb2_0 = 0.0f, gb2_1 = 0.0f, loss_acc = 0.0f;
-        const float b2_0 = s.b2[0], b2_1 = s.b2[1];
-        const bool impute = a.impute == WX_IMPUTE_MEAN;
-        constexpr int cstride = RAW ? TILE : 1;
-        {   // zero this thread's dW2 sums in TMEM
-            float zero[16];
-#pragma unroll
-            for (int q = 0; q < 16; ++q) zero[q] = 0.0f;
-#pragma unroll
-            for (int c = 0; c < 8; ++c) tmem_st16(acc_base + c * 16, zero);
-            tmem_st_wait();
-        }
-
-        int64_t it = 0;                                           // tiles this group has processed
-        for (int64_t i = grp; i < my_tiles; i += NGROUPS, ++it) {
-            const int st = int(i % geo.stages);
-            const int64_t tile = blockIdx.x + i * gridDim.x;
-            const uint32_t par = uint32_t(it & 1);                // parity of this group's per-tile barriers
-            // XK is shared by both groups: GEMM1 of the tile before this one must have read it
-            if (i > 0 && !mbar_wait(&s.d1_full[grp ^ 1], uint32_t(((i - 1) >> 1) & 1))) s.err = 10;
-            if (!mbar_wait(&s.land_full[st], uint32_t((i / geo.stages) & 1))) s.err = 5;
-            float* lx = land_x(st) + (RAW ? r : r * F);           // element c of this row at lx[c * cstride]
-
-            // ---- D row -> K-major hi/lo operand tile (GEMM1 A).  Raw columns are centred here (one subtraction per cell;
-            //      nulls become 0 = the column mean under WX_IMPUTE_MEAN) and written back for their second use in U ----
-#pragma unroll 1
-            for (int c8 = 0; c8 < nfull; ++c8) {
-                float t[8], hi[8], lo[8];
-#pragma unroll
-                for (int e = 0; e < 8; ++e) t[e] = lx[(c8 * 8 + e) * cstride];
-                if (RAW) {
-                    const float4 m0 = *reinterpret_cast<const float4*>(&s.mean_hi[c8 * 8]);
-                    const float4 m1 = *reinterpret_cast<const float4*>(&s.mean_hi[c8 * 8 + 4]);
-                    const float mh[8] = {m0.x, m0.y, m0.z, m0.w, m1.x, m1.y, m1.z, m1.w};
-#pragma unroll
-                    for (int e = 0; e < 8; ++e) {
-                        float d = t[e] - mh[e];
-                        if (impute) d = (t[e] != t[e]) ? 0.0f : d;
-                        t[e] = d;
-                        lx[(c8 * 8 + e) * cstride] = d;
-                    }
-                }
-#pragma unroll
-                for (int e = 0; e < 8; ++e) split_tf32(t[e], hi[e], lo[e]);
-                const uint32_t off0 = sw128_offset(r, c8 * 8), off1 = sw128_offset(r, c8 * 8 + 4);
-                st4(s.xk_hi, off0, hi[0], hi[1], hi[2], hi[3]);
-                st4(s.xk_hi, off1, hi[4], hi[5], hi[6], hi[7]);
-                st4(s.xk_lo, off0, lo[0], lo[1], lo[2], lo[3]);
-                st4(s.xk_lo, off1, lo[4], lo[5], lo[6], lo[7]);
-            }
-            {   // last group: the remaining features, the ones column at F, zeros
-                const int c0 = nfull * 8;
-                float hi[8], lo[8];
-#pragma unroll
-                for (int e = 0; e < 8; ++e) {
-                    const int c = c0 + e;
-                    float d = 0.0f;
-                    if (c < F) {
-                        const float x = lx[c * cstride];
-                        d = x;
-                        if (RAW) {
-                            d = x - s.mean_hi[c];
-                            if (impute) d = (x != x) ? 0.0f : d;
-                            lx[c * cstride] = d;
-                        }
-                    } else if (c == F) {
-                        d = 1.0f;
-                    }
-                    split_tf32(d, hi[e], lo[e]);
-                }
-                const uint32_t off0 = sw128_offset(r, c0), off1 = sw128_offset(r, c0 + 4);
-                st4(s.xk_hi, off0, hi[0], hi[1], hi[2], hi[3]);
-                st4(s.xk_hi, off1, hi[4], hi[5], hi[6], hi[7]);
-                st4(s.xk_lo, off0, lo[0], lo[1], lo[2], lo[3]);
-                st4(s.xk_lo, off1, lo[4], lo[5], lo[6], lo[7]);
-            }
-            fence_proxy_async();
-            tc_fence_before();                   // this thread's TMEM reads of D1[grp] (two tiles ago) precede GEMM1's write
-            mbar_arrive(&s.xk_ready);
-
-            // ---- dropout words / bits and the label: independent of GEMM1, fetched while it runs ----
-            uint32_t pw[8];
-            uint64_t keep = ~0ull;
-            if (DROP == DROP_PHILOX) wxk::philox_keep_words(uint64_t(tile * TILE + r), key, step_word, pw);
-            if (DROP == DROP_MASK) keep = land_m(st)[r];
-            const int yv = int(land_y(st)[r]);
-            const bool valid = r < tile_rows(tile);
-            // Gate / U of this group are free once GEMM2 of its previous tile has drained (issued a whole tile ago)
-            if (it > 0 && !mbar_wait(&s.a2_free[grp], par ^ 1u)) s.err = 7;
-            if (!mbar_wait(&s.d1_full[grp], par)) s.err = 6;
-            tc_fence_after();
-
-            // ---- phase A: a = relu(z) where kept (dropout scale folded into W2 and the dlogits), logits, Gate tile ----
-            float2 lg = make_float2(0.0f, 0.0f), lgb = make_float2(0.0f, 0.0f);
-#pragma unroll
-            for (int cc = 0; cc < 4; ++cc) {
-                float z[16], gt[16];
-                tmem_ld16(d1 + cc * 16, z);
-                uint32_t s0 = 0, s1 = 0;
-                if (DROP == DROP_PHILOX) {
-                    s0 = pw[2 * cc];
-                    s1 = pw[2 * cc + 1];
-                }
-                const uint32_t kb = uint32_t(keep >> (cc * 16)) & 0xffffu;
-                tmem_ld_wait();
-#pragma unroll
-                for (int q = 0; q < 16; ++q) {
-                    bool kp = true;
-                    if (DROP == DROP_PHILOX) kp = wxk::keep_digit(q < 8 ? s0 : s1);
-                    if (DROP == DROP_MASK) kp = (kb >> q) & 1u;
-                    const bool on = kp && !(z[q] <= 0.0f);                 // relu as torch's threshold: NaN passes
-                    const float av = on ? z[q] : 0.0f;
-                    gt[q] = on ? 1.0f : 0.0f;
-                    const float2 w = s.w2p[cc * 16 + q];
-                    if (q & 1) lgb = __ffma2_rn(make_float2(av, av), w, lgb);
-                    else lg = __ffma2_rn(make_float2(av, av), w, lg);
-                    z[q] = av;
-                }
-                tmem_st16(d1 + cc * 16, z);                                  // a replaces z in place: phase B reads it back
-#pragma unroll
-                for (int g8 = 0; g8 < 2; ++g8) {
-                    const uint32_t off = mn32_offset(cc * 16 + g8 * 8, r, 512, 1024);
-                    st4(s.gate[grp], off, gt[g8 * 8], gt[g8 * 8 + 1], gt[g8 * 8 + 2], gt[g8 * 8 + 3]);
-                    st4(s.gate[grp], off + 16, gt[g8 * 8 + 4], gt[g8 * 8 + 5], gt[g8 * 8 + 6], gt[g8 * 8 + 7]);
-                }
-            }
-            const float lg0 = (lg.x + lgb.x) + b2_0;
-            const float lg1 = (lg.y + lgb.y) + b2_1;
-            // ---- softmax / loss / dlogits, ATen's operation order ----
-            const float mx = fmaxf(lg0, lg1);
-            const float e0 = lg0 - mx, e1 = lg1 - mx;
-            const float lsum = logf(expf(e0) + expf(e1));
-            const float lp0 = e0 - lsum, lp1 = e1 - lsum;
-            float dl0 = 0.0f, dl1 = 0.0f;
-            if (valid) {
-                loss_acc += -(yv ? lp1 : lp0);
-                dl0 = (expf(lp0) - (yv == 0 ? 1.0f : 0.0f)) * a.scale;
-                dl1 = (expf(lp1) - (yv == 1 ? 1.0f : 0.0f)) * a.scale;
-                gb2_0 += dl0;
-                gb2_1 += dl1;
-            }
-            // ---- phase B: dW2 sums, (g0, g1)[j] += a_j * ds * (dl0, dl1), in this thread's TMEM columns ----
-            tmem_st_wait();
-            {
-                const float2 dl2 = make_float2(dl0 * ds, dl1 * ds);
-#pragma unroll 1
-                for (int cc = 0; cc < 4; ++cc) {
-                    float av[16], g[32];
-                    tmem_ld16(d1 + cc * 16, av);
-                    tmem_ld32(acc_base + cc * 32, g);
-                    tmem_ld_wait();
-#pragma unroll
-                    for (int q = 0; q < 16; ++q) {
-                        const float2 n = __ffma2_rn(make_float2(av[q], av[q]), dl2, make_float2(g[2 * q], g[2 * q + 1]));
-                        g[2 * q] = n.x;
-                        g[2 * q + 1] = n.y;
-                    }
-                    float g0[16], g1[16];
-#pragma unroll
-                    for (int q = 0; q < 16; ++q) {
-                        g0[q] = g[q];
-                        g1[q] = g[16 + q];
-                    }
-                    tmem_st16(acc_base + cc * 32, g0);
-                    tmem_st16(acc_base + cc * 32 + 16, g1);
-                }
-            }
-            // ---- U row = delta * D (MN-major, hi at columns [0,K1), lo at [K1, 2 K1)) ----
-            {
-                const float delta = 0.5f * (dl0 - dl1);              // the dropout scale rides in w2p (epilogue)
-                unsigned char* ub = reinterpret_cast<unsigned char*>(s.u[grp]);
-#pragma unroll 1
-                for (int c8 = 0; c8 < nfull; ++c8) {
-                    float hi[8], lo[8];
-#pragma unroll
-                    for (int e = 0; e < 8; ++e) split_tf32(delta * lx[(c8 * 8 + e) * cstride], hi[e], lo[e]);
-                    const uint32_t oh = mn32_offset(c8 * 8, r, 512, 1024), ol = mn32_offset(K1 + c8 * 8, r, 512, 1024);
-                    st4(ub, oh, hi[0], hi[1], hi[2], hi[3]);
-                    st4(ub, oh + 16, hi[4], hi[5], hi[6], hi[7]);
-                    st4(ub, ol, lo[0], lo[1], lo[2], lo[3]);
-                    st4(ub, ol + 16, lo[4], lo[5], lo[6], lo[7]);
-                }
-                const int c0 = nfull * 8;
-                float hi[8], lo[8];
-#pragma unroll
-                for (int e = 0; e < 8; ++e) {
-                    const int c = c0 + e;
-                    const float v = c < F ? delta * lx[c * cstride] : (c == F ? delta : 0.0f);
-                    split_tf32(v, hi[e], lo[e]);
-                }
-                const uint32_t oh = mn32_offset(c0, r, 512, 1024), ol = mn32_offset(K1 + c0, r, 512, 1024);
-                st4(ub, oh, hi[0], hi[1], hi[2], hi[3]);
-                st4(ub, oh + 16, hi[4], hi[5], hi[6], hi[7]);
-                st4(ub, ol, lo[0], lo[1], lo[2], lo[3]);
-                st4(ub, ol + 16, lo[4], lo[5], lo[6], lo[7]);
-            }
-            tmem_st_wait();
-            fence_proxy_async();
-            tc_fence_before();
-            mbar_arrive(&s.a2_ready[grp]);
-            mbar_arrive(&s.land_empty[st]);
-        }
-        // ---- all tiles done: wait for this group's last GEMM2, then (after both groups) read T and assemble the slab ----
-        if (it > 0 && !mbar_wait(&s.a2_free[grp], uint32_t((it - 1) & 1))) s.err = 8;
-        tc_fence_after();
-        asm volatile("bar.sync 1, 256;" ::: "memory");
-        float* slab = s.u[0];                                       // GEMM2 is done with both U buffers
-        if (grp == 0) {
-            // T[m][n] (M=64 accumulator: row m = 16*warp + lane, lanes 0-15 of each sub-partition), hi half + lo half
-            float v0[32], v1[32];
-            tmem_ld32(tm + TM_T + lane_addr, v0);
-            tmem_ld32(tm + TM_T + lane_addr + 32, v1);
-            tmem_ld_wait();
-            if (lane < 16) {
-                // through shared memory (U[1] is free): the column arithmetic below depends on the runtime K1 and F
-                const int m = (warp & 3) * 16 + lane;
-                float* trow = s.u[1] + m * 65;
-#pragma unroll
-                for (int q = 0; q < 32; ++q) {
-                    trow[q] = v0[q];
-                    trow[32 + q] = v1[q];
-                }
-                const float2 w = s.w2p[m];
-                const float wd = w.x - w.y;                         // ds * (W2[0][m] - W2[1][m])
-                const float tone = trow[F] + trow[K1 + F];          // T[m][F]: sum over rows of gate * delta
-                slab[OFF_B1 + m] = wd * tone;
-                for (int c = 0; c < F; ++c)
-                    slab[m * F + c] = wd * s.col_scale[c] * ((trow[c] + trow[K1 + c]) - s.col_shift[c] * tone);
-            }
-        }
-        // dW2: per-thread sums -> ordered column sums through smem (the Gate tiles are free now), one group at a time.
-        // Row r keeps its 128 values at column (c + 4 r) & 127, so both the row-wise stores and the column-wise reads
-        // are free of bank conflicts.
-        float* red = s.gate[0];                                       // [128 rows][128] floats = 64 KB = both Gate tiles
-        float colsum = 0.0f;
-#pragma unroll 1
-        for (int g = 0; g < NGROUPS; ++g) {
-            if (grp == g) {
-#pragma unroll 1
-                for (int c = 0; c < 8; ++c) {
-                    float v[16];
-                    tmem_ld16(acc_base + c * 16, v);
-                    tmem_ld_wait();
-#pragma unroll
-                    for (int q4 = 0; q4 < 4; ++q4)
-                        *reinterpret_cast<float4*>(&red[r * 128 + ((c * 16 + q4 * 4 + 4 * r) & 127)]) =
-                            make_float4(v[q4 * 4], v[q4 * 4 + 1], v[q4 * 4 + 2], v[q4 * 4 + 3]);
-                }
-            }
-            asm volatile("bar.sync 1, 256;" ::: "memory");
-            if (grp == 0)
-                for (int k = 0; k < TILE; ++k) colsum += red[k * 128 + ((r + 4 * k) & 127)];
-            asm volatile("bar.sync 1, 256;" ::: "memory");
-        }
-        if (grp == 0) slab[OFF_W2 + (r & 1) * 64 + (r >> 1)] = colsum;        // TMEM column 2j+c holds dW2[c][j]
-        // db2 / loss: warp sums in a fixed order
-        const float w0 = warp_sum(gb2_0), w1 = warp_sum(gb2_1), w2 = warp_sum(loss_acc);
-        if (lane == 0) {
-            s.red_small[warp][0] = w0;
-            s.red_small[warp][1] = w1;
-            s.red_small[warp][2] = w2;
-        }
-        asm volatile("bar.sync 1, 256;" ::: "memory");
-        if (tid < 3) {
-            float t = 0.0f;
-            for (int k = 0; k < WORKERS / 32; ++k) t += s.red_small[k][tid];
-            slab[tid < 2 ? OFF_B2 + tid : P] = t;
-        }
-    }
-    // ================= CTA slab -> global; two-level ticket tree sums the slabs in a fixed order =================
-    tc_fence_before();
-    __syncthreads();
-    if (warp == 0) tmem_dealloc(tm, TMEM_COLS);
-    const float* slab = s.u[0];
-    const unsigned nparts = gridDim.x;
-    const unsigned ngroups = (nparts + GROUP_CTAS - 1) / GROUP_CTAS;
-    const unsigned mygroup = blockIdx.x / GROUP_CTAS;
-    float* mypart = a.part + size_t(blockIdx.x) * slab_stride;
-    float* gpart = a.part + size_t(nparts) * slab_stride;             // [ngroups][slab_stride] group sums
-    unsigned int* tick = a.ticket - 1;                                // word 0 of the ticket block
-    for (int i = tid; i < slab_stride; i += TC_THREADS) mypart[i] = i < P + 1 ? slab[i] : 0.0f;
-    if (tid == 0 && s.err != 0) atomicExch(err_out, s.err);
-    __threadfence();
-    __syncthreads();
-    if (tid == 0) {
-        const unsigned gsize = min(unsigned(GROUP_CTAS), nparts - mygroup * GROUP_CTAS);
-        s.role = atomicAdd(&tick[TICKET_GROUP0 + mygroup], 1u) == gsize - 1 ? 1 : 0;
-    }
-    __syncthreads();
-    if (s.role == 0) return;
-    __threadfence();
-    const int ng4 = slab_stride / 4;
-    {   // level 1: this CTA arrived last in its group -> sum the group's slabs in CTA order
-        const unsigned b0 = mygroup * GROUP_CTAS, b1 = min(b0 + GROUP_CTAS, nparts);
-        for (int g = tid; g < ng4; g += TC_THREADS) {
-            const float4* src = reinterpret_cast<const float4*>(a.part) + g;
-            float4 t[GROUP_CTAS];
-#pragma unroll
-            for (int u = 0; u < GROUP_CTAS; ++u)
-                t[u] = b0 + u < b1 ? __ldcg(src + size_t(b0 + u) * ng4) : make_float4(0.0f, 0.0f, 0.0f, 0.0f);
-            float4 acc = t[0];
-#pragma unroll
-            for (int u = 1; u < GROUP_CTAS; ++u) {
-                acc.x += t[u].x; acc.y += t[u].y; acc.z += t[u].z; acc.w += t[u].w;
-            }
-            reinterpret_cast<float4*>(gpart)[size_t(mygroup) * ng4 + g] = acc;
-        }
-    }
-    __threadfence();
-    __syncthreads();
-    if (tid == 0) s.role = atomicAdd(&tick[TICKET_TOP], 1u) == ngroups - 1 ? 2 : 1;
-    __syncthreads();
-    if (s.role != 2) return;
-    __threadfence();
-    if (a.tail == wxk::TAIL_ADAM && tid == 0) s.adam = wxk::adam_scalars(a.desc, a.state[0] + 1);
-    // level 2: the group sums in group order -> this rank's [P+1] bucket in shared memory
-    float* bucket = s.u[1];
-    for (int g = tid; g < ng4; g += TC_THREADS) {
-        const float4* src = reinterpret_cast<const float4*>(gpart) + g;
-        float4 acc = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
-#pragma unroll 1
-        for (unsigned b = 0; b < ngroups; b += 4) {
-            float4 t[4];
-#pragma unroll
-            for (int u = 0; u < 4; ++u)
-                t[u] = b + u < ngroups ? __ldcg(src + size_t(b + u) * ng4) : make_float4(0.0f, 0.0f, 0.0f, 0.0f);
-#pragma unroll
-            for (int u = 0; u < 4; ++u) {
-                acc.x += t[u].x; acc.y += t[u].y; acc.z += t[u].z; acc.w += t[u].w;
-            }
-        }
-        reinterpret_cast<float4*>(bucket)[g] = acc;
-    }
-    __syncthreads();
-    if (tid == 0) bucket[P] *= a.scale;                               // mean loss
-    __syncthreads();
-    bool apply = true;
-    if (a.peer.world > 1 && a.tail == wxk::TAIL_ADAM) {
-        // DDP exchange inside the kernel: one-shot all-reduce over NVLink peer memory (csrc/peer.cuh).  If a peer does
-        // not show up in time the step is NOT applied on this rank (parameters, moments and step counter stay as they
-        // were) and the sticky error code says so -- a visible stall instead of silently diverging replicas.
-        apply = wxpeer::allreduce_cta(bucket, P + 1, a.peer, uint64_t(a.state[0]) + 1, tid, TC_THREADS);
-        if (!apply && tid == 0) atomicExch(err_out, 20);
-    }
-    for (int i = tid; i < P + 1; i += TC_THREADS) {
-        const float sum = bucket[i];
-        if (a.tail == wxk::TAIL_GRADS) {
-            a.out[i] = sum;
-        } else if (!apply) {
-            continue;
-        } else if (i < P) {
-            float p = a.p_rw[i], m = a.m[i], v = a.v[i];
-            wxk::adam_apply(p, sum, m, v, s.adam);
-            a.p_rw[i] = p;
-            a.m[i] = m;
-            a.v[i] = v;
-        } else {
-            *a.loss_out = sum;
-        }
-    }
-    if (tid < 32) {
-        for (unsigned g = tid; g < ngroups; g += 32) tick[TICKET_GROUP0 + g] = 0u;
-        if (tid == 0) {
-            tick[TICKET_TOP] = 0u;
-            if (a.tail == wxk::TAIL_ADAM && apply) a.state[0] += 1;
-        }
-    }
-}
-
-template <bool RAW, int DROP>
-int tc_launch_inst(wx_ctx* ctx, const GridArgs& a, unsigned grid, int smem, const TcGeom& geo, int* err, cudaStream_t st) {
-    // the opt-in to > 48 KB of dynamic shared memory is a per-device function attribute
-    static bool attr_set[64] = {};
-    const int dev = ctx->device;
-    if (dev < 0 || dev >= 64 || !attr_set[dev]) {
-        WX_CUDA(cudaFuncSetAttribute(tc_step_kernel<RAW, DROP>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
-        if (dev >= 0 && dev < 64) attr_set[dev] = true;
-    }
-    tc_step_kernel<RAW, DROP><<<grid, TC_THREADS, smem, st>>>(a, ctx->desc.n_features, geo, err);
-    return WX_OK;
-}
-
 int tc_launch(wx_ctx* ctx, GridArgs& a, cudaStream_t st, const char* who) {
-    const int f = ctx->desc.n_features;
-    WX_CHECK_ARG(f <= MAXF_TC, "%s: the tensor-core path is built for n_features <= %d (got %d)", who, MAXF_TC, f);
-    WX_CHECK_ARG(a.row_idx == nullptr, "%s: the tensor-core path takes contiguous rows only (row_idx must be NULL)", who);
-    if (a.loader == wxk::LOAD_ROWMAJOR) {
-        WX_CHECK_ARG(((reinterpret_cast<uintptr_t>(a.x) + size_t(a.row0) * f * 4) & 15) == 0,
-                     "%s: first row of the batch must start on a 16-byte boundary for the TMA loads", who);
-    } else {
-        for (int j = 0; j < f; ++j)
-            WX_CHECK_ARG(((reinterpret_cast<uintptr_t>(a.cols.col[j]) + size_t(a.row0) * 4) & 15) == 0,
-                         "%s: column %d must be 16-byte aligned at row0 for the TMA loads (row0 %% 4 == 0)", who, j);
+    switch (ctx->desc.n_features) {
+        case 5: return wx_tc_launch_ft5(ctx, a, st, who);
+        case 20: return wx_tc_launch_ft20(ctx, a, st, who);
+        default: return wx_tc_launch_ft0(ctx, a, st, who);
     }
-    WX_CHECK_ARG(((reinterpret_cast<uintptr_t>(a.y) + size_t(a.row0) * 8) & 15) == 0,
-                 "%s: labels of the batch must start on a 16-byte boundary for the TMA loads", who);
-    WX_CHECK_ARG(a.dropout_mode != WX_DROPOUT_MASK || (reinterpret_cast<uintptr_t>(a.keep_mask) & 15) == 0,
-                 "%s: keep_mask must be 16-byte aligned", who);
-    WX_CUDA(cudaSetDevice(ctx->device));
-    // landing ring: as many stages (at most 3) as fit beside the fixed operand tiles
-    TcGeom geo;
-    geo.x_bytes = (TILE * f * 4 + 127) & ~127;
-    geo.stage_bytes = geo.x_bytes + 2 * TILE * 8;
-    const int fixed = int(offsetof(TcSmem, landing));
-    geo.stages = (SMEM_LIMIT - fixed) / geo.stage_bytes;
-    if (geo.stages > MAX_STAGES) geo.stages = MAX_STAGES;
-    if (geo.stages < 2) {
-        wx_set_error("%s: shared memory does not hold two landing stages for n_features=%d", who, f);
-        return WX_ENOMEM;
-    }
-    const int smem = fixed + geo.stages * geo.stage_bytes;
-    const int64_t ntiles = (a.batch + TILE - 1) / TILE;
-    int64_t grid = ntiles < ctx->num_sms ? ntiles : ctx->num_sms;
-    const size_t slab = (size_t(64) * f + 194 + 1 + 3) & ~size_t(3);
-    const size_t ngroups = (size_t(grid) + GROUP_CTAS - 1) / GROUP_CTAS;
-    if (WX_SCRATCH_PART_OFF + (size_t(grid) + ngroups) * slab * 4 > ctx->scratch_bytes ||
-        ngroups > size_t(TICKET_TOP - TICKET_GROUP0)) {
-        wx_set_error("%s: scratch too small", who);
-        return WX_ENOMEM;
-    }
-    a.part = reinterpret_cast<float*>(ctx->scratch + WX_SCRATCH_PART_OFF);
-    a.ticket = reinterpret_cast<unsigned int*>(ctx->scratch) + 1;
-    a.desc = ctx->desc;
-    a.dbg = nullptr;
-    if (a.tail == wxk::TAIL_ADAM && ctx->peer.world > 1) {
-        a.peer = ctx->peer;
-        a.scale = a.scale / float(ctx->peer.world);          // mean over W*B rows (what DDP's averaged gradients give)
-    }
-    int* err = reinterpret_cast<int*>(ctx->scratch) + 8;       // word 8 of the ticket block: sticky protocol-error code
-    const bool rawl = a.loader != wxk::LOAD_ROWMAJOR;
-    int rc;
-    const unsigned g = unsigned(grid);
-    switch (a.dropout_mode) {
-        case WX_DROPOUT_OFF:
-            rc = rawl ? tc_launch_inst<true, DROP_OFF>(ctx, a, g, smem, geo, err, st)
-                      : tc_launch_inst<false, DROP_OFF>(ctx, a, g, smem, geo, err, st);
-            break;
-        case WX_DROPOUT_MASK:
-            rc = rawl ? tc_launch_inst<true, DROP_MASK>(ctx, a, g, smem, geo, err, st)
-                      : tc_launch_inst<false, DROP_MASK>(ctx, a, g, smem, geo, err, st);
-            break;
-        default:
-            rc = rawl ? tc_launch_inst<true, DROP_PHILOX>(ctx, a, g, smem, geo, err, st)
-                      : tc_launch_inst<false, DROP_PHILOX>(ctx, a, g, smem, geo, err, st);
-            break;
-    }
-    if (rc != WX_OK) return rc;
-    WX_LAUNCH_CHECK(ctx);
-    return WX_OK;
 }
 
 int tc_check_common(wx_ctx* ctx, int& dropout_mode, const uint64_t* keep_mask, int64_t row0, int64_t batch, const char* who) {
