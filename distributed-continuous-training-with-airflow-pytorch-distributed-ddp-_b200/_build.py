@@ -17,6 +17,8 @@ LIB_PATH = os.path.join(PKG_DIR, "libwxddp.so")
 
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC", f"-I{INCLUDE}", f"-I{CSRC}"]
+# developer builds only (e.g. WX_NVCC_EXTRA=-DWX_TC_TIMERS=1 for the phase timers of the tensor-core step kernel)
+NVCC_FLAGS += [fl for fl in os.environ.get("WX_NVCC_EXTRA", "").split() if fl]
 
 # (source, object name, extra flags)
 UNITS = [("ctx.cu", "ctx.o", []), ("preprocess.cu", "preprocess.o", []), ("mlp_host.cu", "mlp_host.o", []),

@@ -3,7 +3,7 @@
 // raw-column loader, /root/reference/jobs/preprocess.py:38-41) like mlp_grid_kernel, with the two F x 64 contractions
 // on the 5th-generation tensor cores and as little per-row CUDA-core work as the arithmetic allows:
 //
-//   GEMM1   z[128 x 64]    = D[128 x K1] . W1s[64 x K1]^T           M=128 N=64  K1 = ceil((F+1)/8)*8   K-major, SW128
+//   GEMM1   z[128 x 64]    = D[128 x K1] . W1s[64 x K1]^T           M=128 N=64  K1 = ceil((F+1)/8)*8   A from TMEM, B K-major SW128
 //   GEMM2   T[64 x 2 K1]  += Gate[128 x 64]^T . [U_hi | U_lo]       M=64  N=2K1 K = 128 rows           MN-major, SW128_B32
 //
 //   D     = [d_0 .. d_{F-1}, 1, 0..]      d_c = x_c - float(mean_c): the raw column, centred only.  The scale 1/std and
@@ -22,10 +22,12 @@
 // hi*lo + lo*hi + hi*hi (~2^-21 relative); GEMM2's A operand is exact, so hi + lo of U alone gives the same accuracy.
 // dW2 / db2 / loss are row-local sums: dW2 lives in per-thread TMEM columns (packed fp32x2 FMAs), db2 / loss in registers.
 //
-// Roles (320 threads, one CTA per SM, persistent over 128-row tiles; tile i belongs to worker group i & 1):
-//   warps 0-3 / 4-7  two row-worker groups: thread r <-> tile row r <-> TMEM lane r (row-local work, no shuffles)
-//   warp 8           TMA producer (cp.async.bulk of rows or F column segments + labels [+ keep bits], 2-3 stage ring)
-//   warp 9           MMA issuer (whole warp runs the loop, elect.sync picks the issuing lane)
+// Roles (448 threads, one CTA per SM, persistent over 128-row tiles; tile i belongs to worker group i & 1):
+//   warps 0-3 / 4-7  two row-worker groups: thread r <-> tile row r <-> TMEM lane r (row-local work, no shuffles):
+//                    everything from the GEMM1 accumulator on (ReLU/dropout/logits/softmax/dW2/Gate/U)
+//   warps 8-11       operand builders, every tile: centre + hi/lo split of the landed row (GEMM1 A), Philox words
+//   warp 12          TMA producer (cp.async.bulk of rows or F column segments + labels [+ keep bits], 2-3 stage ring)
+//   warp 13          MMA issuer (whole warp runs the loop, elect.sync picks the issuing lane)
 // Tail: CTA slabs are summed by a two-level ticket tree (12 CTAs per group, then the groups) in fixed order -- the
 // result is bit-reproducible -- then the cross-rank exchange (csrc/peer.cuh) and Adam run in the last CTA.
 #pragma once
@@ -44,12 +46,17 @@ using wxk::GridArgs;
 constexpr int TILE = 128;
 constexpr int NGROUPS = 2;
 constexpr int WORKERS = NGROUPS * TILE;          // 256 row-worker threads
-constexpr int TC_THREADS = WORKERS + 64;         // + producer warp + MMA warp
-constexpr int PRODUCER_WARP = WORKERS / 32, MMA_WARP = WORKERS / 32 + 1;
-constexpr int MAX_STAGES = 3;
+constexpr int HELPERS = TILE;                    // 128 operand-builder threads (one per tile row)
+constexpr int TC_THREADS = WORKERS + HELPERS + 64;   // + producer warp + MMA warp
+constexpr int HELPER_WARP0 = WORKERS / 32;
+constexpr int PRODUCER_WARP = (WORKERS + HELPERS) / 32, MMA_WARP = PRODUCER_WARP + 1;
+constexpr int MAX_STAGES = 6;
 constexpr int MAXF_TC = 31;                      // F feature columns + the ones column fit the 32-column operand tile
-constexpr int TMEM_COLS = 512;                   // D1 x2 [0,128) | T [128,192) | dW2 sums of group g [256+128g, 384+128g)
-constexpr int TM_T = 128, TM_ACC = 256;
+constexpr int TMEM_COLS = 512;                   // D1 x3 [0,192) | T [192,256) | dW2 sums of group g [256+64g, 320+64g) |
+                                                 // GEMM1 A operand (D hi | lo) of tile parity b [384+64b, 448+64b)
+constexpr int ND1 = 3;                           // GEMM1 accumulators in flight (tile i uses D1[i % 3])
+constexpr int NPW = 3;                           // Philox word buffers in flight (tile i uses pw[i % 3])
+constexpr int TM_T = 192, TM_ACC = 256, TM_XA = 384;
 constexpr int GROUP_CTAS = 12;                   // fan-in of the slab reduction tree
 constexpr int TICKET_GROUP0 = 16, TICKET_TOP = 40;   // words of the ticket block (common.cuh: 64 words, 1/2/8 in use)
 constexpr int SMEM_LIMIT = 232448 - 1024;        // 227 KB per CTA on sm_100, minus the static block (a flag, padded to the 1024-byte alignment of the dynamic part)
@@ -59,7 +66,7 @@ enum { DROP_OFF = WX_DROPOUT_OFF, DROP_MASK = WX_DROPOUT_MASK, DROP_PHILOX = WX_
 struct TcSmem {
     // operand tiles (all 1024-byte aligned)
     float w_hi[64 * 32], w_lo[64 * 32];          // W1s  [n][32]     K-major SW128         (GEMM1 B)
-    float xk_hi[TILE * 32], xk_lo[TILE * 32];    // D    [row][32]   K-major SW128         (GEMM1 A)
+                                                 // (GEMM1's A operand, D hi/lo, lives in TMEM: thread r writes lane r)
     float gate[NGROUPS][TILE * 64];              // Gate [k=row][m=64]  MN-major SW128_B32 (GEMM2 A); reused by the final reductions
     float u[NGROUPS][TILE * 64];                 // U    [k=row][n: hi | lo] MN-major SW128_B32 (GEMM2 B); u[0]/u[1] hold the slab / bucket at the end
     float2 w2p[64];                              // ds * (W2[0][j], W2[1][j])
@@ -67,8 +74,9 @@ struct TcSmem {
     __align__(16) float mean_hi[32];             // raw loader: float(mean_c)
     float col_scale[32], col_shift[32];          // epilogue: 1/std_c and (mean_c - float(mean_c)) as floats
     float red_small[WORKERS / 32][4];            // db2_0, db2_1, loss per worker warp
+    __align__(16) uint32_t pw[NPW][TILE][8];     // Philox words of the tiles in flight (helper -> workers), ring by tile
     uint64_t land_full[MAX_STAGES], land_empty[MAX_STAGES];
-    uint64_t xk_ready, a2_ready[NGROUPS], a2_free[NGROUPS], d1_full[NGROUPS];
+    uint64_t xa_ready[2], a2_ready[NGROUPS], a2_free[NGROUPS], d1_full[ND1], pw_ready[NPW], pw_free[NPW];
     uint32_t tmem_base;
     int err;
     int role;                                    // 0 = not last, 1 = last of its group, 2 = last of the grid
@@ -114,21 +122,59 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_step_kernel(const GridArgs a
     const int N2 = 2 * K1;                        // GEMM2 N extent: [U_hi | U_lo]
     const int nfull = F >> 3;                     // column groups of 8 that hold features only
     const int64_t ntiles = (a.batch + TILE - 1) / TILE;
-    const int64_t my_tiles = (ntiles - blockIdx.x + gridDim.x - 1) / gridDim.x;     // >= 1 by construction of the grid
+    // tiles of this CTA: >= 1 by construction of the grid, far below 2^31 -- 32-bit loop counters keep the ring
+    // arithmetic (i % 3, ...) off the 64-bit division path
+    const int my_tiles = int((ntiles - blockIdx.x + gridDim.x - 1) / gridDim.x);
     const float ds = DROP != DROP_OFF ? 1.25f : 1.0f;           // 1/(1-0.2), train_lightning_ddp.py:60
 
+#ifdef WX_TC_TIMERS
+#define WX_TC_STAMP(k)                                                   \
+    do {                                                                 \
+        if (a.dbg != nullptr && tid == 0) {                              \
+            long long t__;                                               \
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t__));      \
+            a.dbg[blockIdx.x * 8 + (k)] = t__;                           \
+        }                                                                \
+    } while (0)
+#else
+#define WX_TC_STAMP(k) do { } while (0)
+#endif
+#ifdef WX_TC_TIMERS
+    // per-role phase timers: cycles accumulated by one thread of each role, written to dbg[148*8 + (cta*4 + role)*8 + k]
+    long long ph__[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    long long mark__ = clock64();
+#define WX_TC_PH(k)                          \
+    do {                                     \
+        const long long now__ = clock64();   \
+        ph__[k] += now__ - mark__;           \
+        mark__ = now__;                      \
+    } while (0)
+#define WX_TC_PH_FLUSH(role)                                                                        \
+    do {                                                                                            \
+        if (a.dbg != nullptr)                                                                       \
+            for (int k__ = 0; k__ < 8; ++k__) a.dbg[148 * 8 + (blockIdx.x * 5 + (role)) * 8 + k__] = ph__[k__]; \
+    } while (0)
+#else
+#define WX_TC_PH(k) do { } while (0)
+#define WX_TC_PH_FLUSH(role) do { } while (0)
+#endif
+    WX_TC_STAMP(0);
     if (tid == 0 && (smem_u32(raw) & 1023u) != 0) atomicExch(err_out, 99);   // dynamic smem base not 1024-aligned
     if (tid == 0) {
         for (int i = 0; i < MAX_STAGES; ++i) {
-            mbar_init(&s.land_full[i], 1);
+            mbar_init(&s.land_full[i], 32);
             mbar_init(&s.land_empty[i], TILE);
         }
-        mbar_init(&s.xk_ready, TILE);
         for (int g = 0; g < NGROUPS; ++g) {
+            mbar_init(&s.xa_ready[g], TILE);
             mbar_init(&s.a2_ready[g], TILE);
             mbar_init(&s.a2_free[g], 1);
-            mbar_init(&s.d1_full[g], 1);
         }
+        for (int g = 0; g < NPW; ++g) {
+            mbar_init(&s.pw_ready[g], TILE);
+            mbar_init(&s.pw_free[g], TILE);
+        }
+        for (int g = 0; g < ND1; ++g) mbar_init(&s.d1_full[g], 1);
         fence_mbar_init();
         s.err = 0;
     }
@@ -184,6 +230,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_step_kernel(const GridArgs a
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
+    WX_TC_STAMP(1);
     const uint32_t tm = s.tmem_base;
     const uint64_t step_word = (a.state != nullptr) ? uint64_t(a.state[0]) : a.step;
 
@@ -204,26 +251,39 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_step_kernel(const GridArgs a
         const int S = geo.stages;
         int st = 0;
         uint32_t round = 0;                      // how many times the ring has wrapped
-        for (int64_t i = 0; i < my_tiles; ++i) {
-            const int64_t tile = blockIdx.x + i * gridDim.x;
+        for (int i = 0; i < my_tiles; ++i) {
+            const int64_t tile = int64_t(blockIdx.x) + int64_t(i) * gridDim.x;
+            WX_TC_PH(7);
             if (round > 0 && !mbar_wait(&s.land_empty[st], (round - 1) & 1u)) s.err = 2;
+            WX_TC_PH(0);
             const int nr = tile_rows(tile);
             const int64_t row = a.row0 + tile * TILE;
             float* lx = land_x(st);
-            if (nr == TILE) {           // full tile: every size is a multiple of 16 B; start alignment is checked on the host
-                const uint32_t by = TILE * 8;
-                if (lane == 0)
-                    mbar_arrive_expect_tx(&s.land_full[st], uint32_t(TILE) * F * 4 + by + (DROP == DROP_MASK ? by : 0u));
-                __syncwarp();
-                if (!RAW) {
-                    if (lane == 0) bulk_g2s(lx, a.x + row * F, uint32_t(TILE) * F * 4, &s.land_full[st]);
-                } else if (lane < F) {  // one 512-byte column segment per lane
-                    bulk_g2s(lx + lane * TILE, static_cast<const float*>(a.cols.col[lane]) + row, TILE * 4, &s.land_full[st]);
+            if (nr == TILE && RAW) {
+                // full tile of raw columns: F column segments of 512 B + labels [+ keep bits].  As bulk-TMA copies these
+                // cost ~115 cycles EACH to issue (22 per tile: the producer became the pipeline's bottleneck); as 16-byte
+                // cp.async they are one instruction per 512 B for the whole warp: lane l moves rows 4l .. 4l+3 of every
+                // column, and its completion arrive on the stage barrier follows its own copies.
+#pragma unroll UNR
+                for (int c = 0; c < F; ++c)
+                    cp_async16(lx + c * TILE + 4 * lane, static_cast<const float*>(a.cols.col[c]) + row + 4 * lane);
+                cp_async16(land_y(st) + 2 * lane, a.y + row + 2 * lane);
+                cp_async16(land_y(st) + 64 + 2 * lane, a.y + row + 64 + 2 * lane);
+                if (DROP == DROP_MASK) {
+                    cp_async16(land_m(st) + 2 * lane, a.keep_mask + tile * TILE + 2 * lane);
+                    cp_async16(land_m(st) + 64 + 2 * lane, a.keep_mask + tile * TILE + 64 + 2 * lane);
                 }
+                cp_async_mbar_arrive(&s.land_full[st]);
+            } else if (nr == TILE) {    // full tile of row-major rows: one contiguous bulk copy (+ labels [+ keep bits])
+                const uint32_t by = TILE * 8;
                 if (lane == 0) {
+                    mbar_arrive_expect_tx(&s.land_full[st], uint32_t(TILE) * F * 4 + by + (DROP == DROP_MASK ? by : 0u));
+                    bulk_g2s(lx, a.x + row * F, uint32_t(TILE) * F * 4, &s.land_full[st]);
                     bulk_g2s(land_y(st), a.y + row, by, &s.land_full[st]);
                     if (DROP == DROP_MASK) bulk_g2s(land_m(st), a.keep_mask + tile * TILE, by, &s.land_full[st]);
                 }
+                __syncwarp();
+                if (lane != 0) mbar_arrive(&s.land_full[st]);     // the barrier counts the whole warp (see the cp.async path)
             } else {
                 // ragged last tile: plain loads by the whole warp; rows past the end are filled with values that centre
                 // to exactly zero (they must not put NaN into the operand tiles), then a normal arrive
@@ -240,14 +300,15 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_step_kernel(const GridArgs a
                     if (DROP == DROP_MASK) land_m(st)[e] = e < nr ? a.keep_mask[tile * TILE + e] : 0ull;
                 }
                 __threadfence_block();
-                __syncwarp();
-                if (lane == 0) mbar_arrive(&s.land_full[st]);
+                mbar_arrive(&s.land_full[st]);
             }
+            WX_TC_PH(1);
             if (++st == S) {
                 st = 0;
                 ++round;
             }
         }
+        if (lane == 0) WX_TC_PH_FLUSH(4);
     } else if (warp == MMA_WARP) {
         // ================= MMA issuer =================
         // The WHOLE warp runs this code and one elected lane issues each MMA: operands stay warp-uniform (uniform
@@ -255,21 +316,21 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_step_kernel(const GridArgs a
         // constant to the start-address field.
         const uint32_t id1 = make_idesc_tf32(128, 64, false, false);
         const uint32_t id2 = make_idesc_tf32(64, N2, true, true);
-        const uint64_t xk_d[2] = {make_smem_desc(smem_u32(s.xk_hi), 16, 1024), make_smem_desc(smem_u32(s.xk_lo), 16, 1024)};
         const uint64_t wk_d[2] = {make_smem_desc(smem_u32(s.w_hi), 16, 1024), make_smem_desc(smem_u32(s.w_lo), 16, 1024)};
         // group 1's tiles sit 32 KB after group 0's: + 2048 in the start-address field (16-byte units)
         const uint64_t gate_d0 = make_smem_desc(smem_u32(s.gate[0]), 512, 1024, LAYOUT_SW128_B32);
         const uint64_t u_d0 = make_smem_desc(smem_u32(s.u[0]), 512, 1024, LAYOUT_SW128_B32);
         constexpr uint64_t GROUP_STEP = sizeof(float) * TILE * 64 / 16;
         const int k1steps = K1 / 8;
-        auto gemm1 = [&](uint32_t dst) {
+        auto gemm1 = [&](uint32_t dst, uint32_t xa) {
             bool acc = false;                    // small terms first: hi*lo, lo*hi, then hi*hi
 #pragma unroll
             for (int term = 0; term < 3; ++term) {
-                const uint64_t ad = xk_d[term == 1 ? 1 : 0], bd = wk_d[term == 0 ? 1 : 0];
+                const uint32_t at = xa + (term == 1 ? 32u : 0u);     // A from TMEM: hi at columns [0,32), lo at [32,64)
+                const uint64_t bd = wk_d[term == 0 ? 1 : 0];
 #pragma unroll UNR
                 for (int k = 0; k < k1steps; ++k) {
-                    umma_tf32_warp(dst, ad + uint64_t(k * 2), bd + uint64_t(k * 2), id1, acc);       // +32 B per k-step
+                    umma_tf32_ts_warp(dst, at + uint32_t(k * 8), bd + uint64_t(k * 2), id1, acc);  // 8 columns / 32 B per k-step
                     acc = true;
                 }
             }
@@ -283,137 +344,206 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_step_kernel(const GridArgs a
                 acc = true;
             }
         };
-        for (int64_t i = 0; i < my_tiles; ++i) {
-            if (!mbar_wait_hot(&s.xk_ready, uint32_t(i & 1))) s.err = 3;
-            tc_fence_after();
-            gemm1(tm + uint32_t(i & 1) * 64);
-            umma_commit_warp(&s.d1_full[i & 1]);
-            if (i > 0) {
-                const int g = int((i - 1) & 1);
-                if (!mbar_wait_hot(&s.a2_ready[g], uint32_t(((i - 1) >> 1) & 1))) s.err = 4;
+        // Two in-order queues, served as they become ready with GEMM1 first: the GEMM1 of the next tile (its operand is
+        // built ahead by the helper warps; its accumulator D1[i % 3] is free once the GEMM2 of tile i - 3 has been issued,
+        // because that waited for the rows workers' last reads) and the GEMM2 of the oldest finished tile.  A group that
+        // finishes a tile therefore finds the accumulator of its next tile already computed.
+        WX_TC_PH(7);
+        int i1 = 0, i2 = 0;                      // next GEMM1 tile, next GEMM2 tile
+        uint32_t idle = 0;
+        while (i2 < my_tiles) {
+            bool go1 = false, go2 = false;
+            if (lane == 0) {
+                go1 = i1 < my_tiles && i1 - i2 < ND1 && mbar_test_wait(&s.xa_ready[i1 & 1], uint32_t((i1 >> 1) & 1));
+                go2 = !go1 && i2 < i1 && mbar_test_wait(&s.a2_ready[i2 & 1], uint32_t((i2 >> 1) & 1));
+            }
+            go1 = __shfl_sync(0xffffffffu, go1, 0);
+            go2 = __shfl_sync(0xffffffffu, go2, 0);
+            if (go1) {
                 tc_fence_after();
-                gemm2(g, i - 1 == 0);
-                umma_commit_warp(&s.a2_free[g]);
+                WX_TC_PH(0);
+                gemm1(tm + uint32_t(i1 % ND1) * 64, tm + TM_XA + uint32_t(i1 & 1) * 64);
+                umma_commit_warp(&s.d1_full[i1 % ND1]);
+                WX_TC_PH(1);
+                ++i1;
+                idle = 0;
+            } else if (go2) {
+                tc_fence_after();
+                WX_TC_PH(2);
+                gemm2(i2 & 1, i2 == 0);
+                umma_commit_warp(&s.a2_free[i2 & 1]);
+                WX_TC_PH(3);
+                ++i2;
+                idle = 0;
+            } else if (++idle > (1u << 26)) {
+                s.err = 3;                       // neither queue moved for seconds: protocol bug, do not hang the GPU
+                break;
             }
         }
-        const int g = int((my_tiles - 1) & 1);
-        if (!mbar_wait_hot(&s.a2_ready[g], uint32_t(((my_tiles - 1) >> 1) & 1))) s.err = 4;
-        tc_fence_after();
-        gemm2(g, my_tiles - 1 == 0);
-        umma_commit_warp(&s.a2_free[g]);
+        if (lane == 0) WX_TC_PH_FLUSH(3);
+    } else if (warp >= HELPER_WARP0) {
+        // ================= operand builders (4 warps, thread r <-> tile row r, EVERY tile) =================
+        // Centre the landed row, split it into the K-major hi/lo operand of GEMM1, and draw the row's dropout words --
+        // everything a tile needs before its GEMM1, so the row workers start at the accumulator.
+        const int r = tid - HELPER_WARP0 * 32;
+        const uint2 key = make_uint2(uint32_t(a.seed), uint32_t(a.seed >> 32));
+        const bool impute = a.impute == WX_IMPUTE_MEAN;
+        constexpr int cstride = RAW ? TILE : 1;
+        const uint32_t lane_addr = uint32_t(((warp & 3) * 32)) << 16;   // helper thread r owns TMEM lane r
+        int st = 0;
+        uint32_t land_par = 0;                                    // landing ring position / phase of tile i
+        for (int i = 0; i < my_tiles; ++i) {
+            const int64_t tile = int64_t(blockIdx.x) + int64_t(i) * gridDim.x;
+            WX_TC_PH(7);
+            // ---- dropout words of this row (independent of everything else: drawn first, handed over when the ring
+            //      slot has been read by the workers of tile i - 3) ----
+            if (DROP == DROP_PHILOX) {
+                uint32_t pw[8];
+                wxk::philox_keep_words(uint64_t(tile * TILE + r), key, step_word, pw);
+                const int q = i % NPW;
+                if (i >= NPW && !mbar_wait(&s.pw_free[q], uint32_t((i / NPW - 1) & 1))) s.err = 12;
+                *reinterpret_cast<uint4*>(&s.pw[q][r][0]) = make_uint4(pw[0], pw[1], pw[2], pw[3]);
+                *reinterpret_cast<uint4*>(&s.pw[q][r][4]) = make_uint4(pw[4], pw[5], pw[6], pw[7]);
+                mbar_arrive(&s.pw_ready[q]);
+            }
+            WX_TC_PH(0);
+            if (!mbar_wait(&s.land_full[st], land_par)) s.err = 5;
+            WX_TC_PH(1);
+            // the A operand buffer of this tile parity is free once GEMM1 of tile i - 2 has completed
+            if (i >= 2 && !mbar_wait(&s.d1_full[(i - 2) % ND1], uint32_t(((i - 2) / ND1) & 1))) s.err = 10;
+            tc_fence_after();
+            WX_TC_PH(2);
+            float* lx = land_x(st) + (RAW ? r : r * F);           // element c of this row at lx[c * cstride]
+            const uint32_t xa = tm + TM_XA + uint32_t(i & 1) * 64 + lane_addr;
+
+            // ---- D row -> hi/lo A operand of GEMM1 in TMEM (lane = row, column = feature).  Raw columns are centred here
+            //      (one subtraction per cell; nulls become 0 = the column mean under WX_IMPUTE_MEAN) and written back to
+            //      the landing buffer for their second use in U ----
+            // all loads first, all stores last: the landing ring and the constants live in the same shared array, so a
+            // store between two loads would serialise them
+            float dh[32], dlo[32], xv[32], mh[32];
+#pragma unroll
+            for (int c = 0; c < 32; ++c) xv[c] = (c < K1 && c < F) ? lx[c * cstride] : 0.0f;
+            if (RAW) {
+#pragma unroll
+                for (int c4 = 0; c4 < 8; ++c4) {
+                    if (c4 * 4 < F) {
+                        const float4 m = *reinterpret_cast<const float4*>(&s.mean_hi[c4 * 4]);
+                        mh[c4 * 4] = m.x; mh[c4 * 4 + 1] = m.y; mh[c4 * 4 + 2] = m.z; mh[c4 * 4 + 3] = m.w;
+                    } else {
+                        mh[c4 * 4] = mh[c4 * 4 + 1] = mh[c4 * 4 + 2] = mh[c4 * 4 + 3] = 0.0f;
+                    }
+                }
+            }
+#pragma unroll
+            for (int c = 0; c < 32; ++c) {
+                float d = 0.0f;
+                if (c < K1) {                                     // (compile-time for the specialised builds)
+                    if (c < F) {
+                        d = xv[c];
+                        if (RAW) {
+                            d = xv[c] - mh[c];
+                            if (impute) d = (xv[c] != xv[c]) ? 0.0f : d;
+                            xv[c] = d;
+                        }
+                    } else if (c == F) {
+                        d = 1.0f;
+                    }
+                }
+                split_tf32(d, dh[c], dlo[c]);
+            }
+            if (RAW) {
+#pragma unroll
+                for (int c = 0; c < 32; ++c)
+                    if (c < K1 && c < F) lx[c * cstride] = xv[c];
+            }
+#pragma unroll
+            for (int c16 = 0; c16 < 2; ++c16) {
+                if (c16 * 16 < K1) {
+                    float h16[16], l16[16];
+#pragma unroll
+                    for (int e = 0; e < 16; ++e) {
+                        h16[e] = dh[c16 * 16 + e];
+                        l16[e] = dlo[c16 * 16 + e];
+                    }
+                    tmem_st16_nc(xa + c16 * 16, h16);
+                    tmem_st16_nc(xa + 32 + c16 * 16, l16);
+                }
+            }
+            tmem_st_wait();
+            tc_fence_before();
+            mbar_arrive(&s.xa_ready[i & 1]);
+            WX_TC_PH(3);
+            if (++st == geo.stages) {
+                st = 0;
+                land_par ^= 1u;
+            }
+        }
+        if (r == 0) WX_TC_PH_FLUSH(2);
     } else {
         // ================= row workers: group 0 = warps 0-3, group 1 = warps 4-7 =================
         const int grp = warp >> 2;
         const int r = tid & (TILE - 1);                           // tile row == TMEM lane
         const uint32_t lane_addr = uint32_t((warp & 3) * 32) << 16;
-        const uint32_t acc_base = tm + TM_ACC + uint32_t(grp) * 128 + lane_addr;
-        const uint32_t d1 = tm + uint32_t(grp) * 64 + lane_addr;
-        const uint2 key = make_uint2(uint32_t(a.seed), uint32_t(a.seed >> 32));
+        const uint32_t acc_base = tm + TM_ACC + uint32_t(grp) * 64 + lane_addr;
         float gb2_0 = 0.0f, gb2_1 = 0.0f, loss_acc = 0.0f;
         const float b2_0 = s.b2[0], b2_1 = s.b2[1];
-        const bool impute = a.impute == WX_IMPUTE_MEAN;
         constexpr int cstride = RAW ? TILE : 1;
         {   // zero this thread's dW2 sums in TMEM
             float zero[16];
 #pragma unroll
             for (int q = 0; q < 16; ++q) zero[q] = 0.0f;
 #pragma unroll
-            for (int c = 0; c < 8; ++c) tmem_st16(acc_base + c * 16, zero);
+            for (int c = 0; c < 4; ++c) tmem_st16(acc_base + c * 16, zero);
             tmem_st_wait();
         }
 
-        int64_t it = 0;                                           // tiles this group has processed
-        for (int64_t i = grp; i < my_tiles; i += NGROUPS, ++it) {
-            const int st = int(i % geo.stages);
-            const int64_t tile = blockIdx.x + i * gridDim.x;
+        int it = 0;                                               // tiles this group has processed
+        int st = grp % geo.stages;                                // landing ring position of tile i (advances by 2)
+        for (int i = grp; i < my_tiles; i += NGROUPS, ++it) {
+            const int64_t tile = int64_t(blockIdx.x) + int64_t(i) * gridDim.x;
             const uint32_t par = uint32_t(it & 1);                // parity of this group's per-tile barriers
-            // XK is shared by both groups: GEMM1 of the tile before this one must have read it
-            if (i > 0 && !mbar_wait(&s.d1_full[grp ^ 1], uint32_t(((i - 1) >> 1) & 1))) s.err = 10;
-            if (!mbar_wait(&s.land_full[st], uint32_t((i / geo.stages) & 1))) s.err = 5;
-            float* lx = land_x(st) + (RAW ? r : r * F);           // element c of this row at lx[c * cstride]
-
-            // ---- D row -> K-major hi/lo operand tile (GEMM1 A).  Raw columns are centred here (one subtraction per cell;
-            //      nulls become 0 = the column mean under WX_IMPUTE_MEAN) and written back for their second use in U ----
-#pragma unroll UNR
-            for (int c8 = 0; c8 < nfull; ++c8) {
-                float t[8], hi[8], lo[8];
-#pragma unroll
-                for (int e = 0; e < 8; ++e) t[e] = lx[(c8 * 8 + e) * cstride];
-                if (RAW) {
-                    const float4 m0 = *reinterpret_cast<const float4*>(&s.mean_hi[c8 * 8]);
-                    const float4 m1 = *reinterpret_cast<const float4*>(&s.mean_hi[c8 * 8 + 4]);
-                    const float mh[8] = {m0.x, m0.y, m0.z, m0.w, m1.x, m1.y, m1.z, m1.w};
-#pragma unroll
-                    for (int e = 0; e < 8; ++e) {
-                        float d = t[e] - mh[e];
-                        if (impute) d = (t[e] != t[e]) ? 0.0f : d;
-                        t[e] = d;
-                        lx[(c8 * 8 + e) * cstride] = d;
-                    }
-                }
-#pragma unroll
-                for (int e = 0; e < 8; ++e) split_tf32(t[e], hi[e], lo[e]);
-                const uint32_t off0 = sw128_offset(r, c8 * 8), off1 = sw128_offset(r, c8 * 8 + 4);
-                st4(s.xk_hi, off0, hi[0], hi[1], hi[2], hi[3]);
-                st4(s.xk_hi, off1, hi[4], hi[5], hi[6], hi[7]);
-                st4(s.xk_lo, off0, lo[0], lo[1], lo[2], lo[3]);
-                st4(s.xk_lo, off1, lo[4], lo[5], lo[6], lo[7]);
-            }
-            {   // last group: the remaining features, the ones column at F, zeros
-                const int c0 = nfull * 8;
-                float hi[8], lo[8];
-#pragma unroll
-                for (int e = 0; e < 8; ++e) {
-                    const int c = c0 + e;
-                    float d = 0.0f;
-                    if (c < F) {
-                        const float x = lx[c * cstride];
-                        d = x;
-                        if (RAW) {
-                            d = x - s.mean_hi[c];
-                            if (impute) d = (x != x) ? 0.0f : d;
-                            lx[c * cstride] = d;
-                        }
-                    } else if (c == F) {
-                        d = 1.0f;
-                    }
-                    split_tf32(d, hi[e], lo[e]);
-                }
-                const uint32_t off0 = sw128_offset(r, c0), off1 = sw128_offset(r, c0 + 4);
-                st4(s.xk_hi, off0, hi[0], hi[1], hi[2], hi[3]);
-                st4(s.xk_hi, off1, hi[4], hi[5], hi[6], hi[7]);
-                st4(s.xk_lo, off0, lo[0], lo[1], lo[2], lo[3]);
-                st4(s.xk_lo, off1, lo[4], lo[5], lo[6], lo[7]);
-            }
-            fence_proxy_async();
-            tc_fence_before();                   // this thread's TMEM reads of D1[grp] (two tiles ago) precede GEMM1's write
-            mbar_arrive(&s.xk_ready);
-
-            // ---- dropout words / bits and the label: independent of GEMM1, fetched while it runs ----
+            float* lx = land_x(st) + (RAW ? r : r * F);           // element c of this (already centred) row at lx[c * cstride]
+            // ---- dropout words of this row, made by the helper warps while this group finished its previous tile ----
             uint32_t pw[8];
+            WX_TC_PH(7);
+            if (DROP == DROP_PHILOX) {
+                const int q = i % NPW;
+                if (!mbar_wait(&s.pw_ready[q], uint32_t((i / NPW) & 1))) s.err = 11;
+                const uint4 p0 = *reinterpret_cast<const uint4*>(&s.pw[q][r][0]);
+                const uint4 p1 = *reinterpret_cast<const uint4*>(&s.pw[q][r][4]);
+                pw[0] = p0.x; pw[1] = p0.y; pw[2] = p0.z; pw[3] = p0.w;
+                pw[4] = p1.x; pw[5] = p1.y; pw[6] = p1.z; pw[7] = p1.w;
+                mbar_arrive(&s.pw_free[q]);
+            }
+            WX_TC_PH(0);
+            WX_TC_PH(1);
+            const uint32_t d1 = tm + uint32_t(i % ND1) * 64 + lane_addr;
+            if (!mbar_wait(&s.d1_full[i % ND1], uint32_t((i / ND1) & 1))) s.err = 6;   // GEMM1 done => stage filled and centred
+            tc_fence_after();
+            WX_TC_PH(2);
             uint64_t keep = ~0ull;
-            if (DROP == DROP_PHILOX) wxk::philox_keep_words(uint64_t(tile * TILE + r), key, step_word, pw);
             if (DROP == DROP_MASK) keep = land_m(st)[r];
             const int yv = int(land_y(st)[r]);
             const bool valid = r < tile_rows(tile);
-            // Gate / U of this group are free once GEMM2 of its previous tile has drained (issued a whole tile ago)
-            if (it > 0 && !mbar_wait(&s.a2_free[grp], par ^ 1u)) s.err = 7;
-            if (!mbar_wait(&s.d1_full[grp], par)) s.err = 6;
-            tc_fence_after();
 
-            // ---- phase A: a = relu(z) where kept (dropout scale folded into W2 and the dlogits), logits, Gate tile ----
+            // ---- phase A: a = relu(z) where kept (dropout scale folded into W2 and the dlogits), logits, Gate tile.
+            //      The TMEM load of the next 16 units is in flight while this chunk is processed. ----
             float2 lg = make_float2(0.0f, 0.0f), lgb = make_float2(0.0f, 0.0f);
+            const float2* __restrict__ w2p = s.w2p;              // read-only here: loads may pass the Gate stores
+            float zbuf[2][16];
+            tmem_ld16_nc(d1, zbuf[0]);
 #pragma unroll
             for (int cc = 0; cc < 4; ++cc) {
-                float z[16], gt[16];
-                tmem_ld16(d1 + cc * 16, z);
+                float (&z)[16] = zbuf[cc & 1];
+                tmem_ld_wait_dep(z);
+                if (cc < 3) tmem_ld16_nc(d1 + (cc + 1) * 16, zbuf[(cc + 1) & 1]);
                 uint32_t s0 = 0, s1 = 0;
                 if (DROP == DROP_PHILOX) {
                     s0 = pw[2 * cc];
                     s1 = pw[2 * cc + 1];
                 }
                 const uint32_t kb = uint32_t(keep >> (cc * 16)) & 0xffffu;
-                tmem_ld_wait();
 #pragma unroll
                 for (int q = 0; q < 16; ++q) {
                     bool kp = true;
@@ -421,20 +551,14 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_step_kernel(const GridArgs a
                     if (DROP == DROP_MASK) kp = (kb >> q) & 1u;
                     const bool on = kp && !(z[q] <= 0.0f);                 // relu as torch's threshold: NaN passes
                     const float av = on ? z[q] : 0.0f;
-                    gt[q] = on ? 1.0f : 0.0f;
-                    const float2 w = s.w2p[cc * 16 + q];
+                    const float2 w = w2p[cc * 16 + q];
                     if (q & 1) lgb = __ffma2_rn(make_float2(av, av), w, lgb);
                     else lg = __ffma2_rn(make_float2(av, av), w, lg);
                     z[q] = av;
                 }
-                tmem_st16(d1 + cc * 16, z);                                  // a replaces z in place: phase B reads it back
-#pragma unroll
-                for (int g8 = 0; g8 < 2; ++g8) {
-                    const uint32_t off = mn32_offset(cc * 16 + g8 * 8, r, 512, 1024);
-                    st4(s.gate[grp], off, gt[g8 * 8], gt[g8 * 8 + 1], gt[g8 * 8 + 2], gt[g8 * 8 + 3]);
-                    st4(s.gate[grp], off + 16, gt[g8 * 8 + 4], gt[g8 * 8 + 5], gt[g8 * 8 + 6], gt[g8 * 8 + 7]);
-                }
+                tmem_st16_nc(d1 + cc * 16, z);                               // a replaces z in place: phase B reads it back
             }
+            WX_TC_PH(3);
             const float lg0 = (lg.x + lgb.x) + b2_0;
             const float lg1 = (lg.y + lgb.y) + b2_1;
             // ---- softmax / loss / dlogits, ATen's operation order ----
@@ -450,67 +574,79 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_step_kernel(const GridArgs a
                 gb2_0 += dl0;
                 gb2_1 += dl1;
             }
-            // ---- phase B: dW2 sums, (g0, g1)[j] += a_j * ds * (dl0, dl1), in this thread's TMEM columns ----
+            const float delta = 0.5f * (dl0 - dl1);              // dl1 = -dl0 up to rounding (two classes); ds rides in w2p
+            WX_TC_PH(4);
+            // ---- phase B: dW2[0][j] sum, g[j] += a_j * ds * delta, in this thread's TMEM columns (dW2[1] = -dW2[0]), and the
+            //      Gate tile (a_j != 0 <=> the unit is active).  Gate / U of this group are free once GEMM2 of its previous
+            //      tile has drained: it was issued when that tile ended, a whole phase A ago. ----
             tmem_st_wait();
+            if (it > 0 && !mbar_wait(&s.a2_free[grp], par ^ 1u)) s.err = 7;
             {
-                const float2 dl2 = make_float2(dl0 * ds, dl1 * ds);
-#pragma unroll 1
+                const float dd = ds * delta;
+                float abuf[2][16], gbuf[2][16];
+                tmem_ld16_nc(d1, abuf[0]);
+                tmem_ld16_nc(acc_base, gbuf[0]);
+#pragma unroll
                 for (int cc = 0; cc < 4; ++cc) {
-                    float av[16], g[32];
-                    tmem_ld16(d1 + cc * 16, av);
-                    tmem_ld32(acc_base + cc * 32, g);
-                    tmem_ld_wait();
-#pragma unroll
-                    for (int q = 0; q < 16; ++q) {
-                        const float2 n = __ffma2_rn(make_float2(av[q], av[q]), dl2, make_float2(g[2 * q], g[2 * q + 1]));
-                        g[2 * q] = n.x;
-                        g[2 * q + 1] = n.y;
+                    float (&av)[16] = abuf[cc & 1];
+                    float (&g)[16] = gbuf[cc & 1];
+                    tmem_ld_wait_dep(av);
+                    tmem_dep(g);
+                    if (cc < 3) {
+                        tmem_ld16_nc(d1 + (cc + 1) * 16, abuf[(cc + 1) & 1]);
+                        tmem_ld16_nc(acc_base + (cc + 1) * 16, gbuf[(cc + 1) & 1]);
                     }
-                    float g0[16], g1[16];
 #pragma unroll
-                    for (int q = 0; q < 16; ++q) {
-                        g0[q] = g[q];
-                        g1[q] = g[16 + q];
+                    for (int q = 0; q < 16; ++q) g[q] = fmaf(av[q], dd, g[q]);
+                    tmem_st16_nc(acc_base + cc * 16, g);
+                    float gt[16];
+#pragma unroll
+                    for (int q = 0; q < 16; ++q) gt[q] = (av[q] == 0.0f) ? 0.0f : 1.0f;    // a >= 0 or NaN (NaN counts as active)
+#pragma unroll
+                    for (int g8 = 0; g8 < 2; ++g8) {
+                        const uint32_t off = mn32_offset(cc * 16 + g8 * 8, r, 512, 1024);
+                        st4(s.gate[grp], off, gt[g8 * 8], gt[g8 * 8 + 1], gt[g8 * 8 + 2], gt[g8 * 8 + 3]);
+                        st4(s.gate[grp], off + 16, gt[g8 * 8 + 4], gt[g8 * 8 + 5], gt[g8 * 8 + 6], gt[g8 * 8 + 7]);
                     }
-                    tmem_st16(acc_base + cc * 32, g0);
-                    tmem_st16(acc_base + cc * 32 + 16, g1);
                 }
             }
+            WX_TC_PH(5);
             // ---- U row = delta * D (MN-major, hi at columns [0,K1), lo at [K1, 2 K1)) ----
             {
-                const float delta = 0.5f * (dl0 - dl1);              // the dropout scale rides in w2p (epilogue)
                 unsigned char* ub = reinterpret_cast<unsigned char*>(s.u[grp]);
-#pragma unroll UNR
-                for (int c8 = 0; c8 < nfull; ++c8) {
-                    float hi[8], lo[8];
+                // all loads of the centred row first (a store between two loads of the same shared array serialises them)
+                float dv[32];
 #pragma unroll
-                    for (int e = 0; e < 8; ++e) split_tf32(delta * lx[(c8 * 8 + e) * cstride], hi[e], lo[e]);
-                    const uint32_t oh = mn32_offset(c8 * 8, r, 512, 1024), ol = mn32_offset(K1 + c8 * 8, r, 512, 1024);
-                    st4(ub, oh, hi[0], hi[1], hi[2], hi[3]);
-                    st4(ub, oh + 16, hi[4], hi[5], hi[6], hi[7]);
-                    st4(ub, ol, lo[0], lo[1], lo[2], lo[3]);
-                    st4(ub, ol + 16, lo[4], lo[5], lo[6], lo[7]);
-                }
-                const int c0 = nfull * 8;
-                float hi[8], lo[8];
+                for (int c = 0; c < 32; ++c) dv[c] = (c < K1 && c < F) ? lx[c * cstride] : 0.0f;
 #pragma unroll
-                for (int e = 0; e < 8; ++e) {
-                    const int c = c0 + e;
-                    const float v = c < F ? delta * lx[c * cstride] : (c == F ? delta : 0.0f);
-                    split_tf32(v, hi[e], lo[e]);
+                for (int c8 = 0; c8 < 4; ++c8) {
+                    if (c8 * 8 < K1) {
+                        float hi[8], lo[8];
+#pragma unroll
+                        for (int e = 0; e < 8; ++e) {
+                            const int c = c8 * 8 + e;
+                            const float v = c < F ? delta * dv[c] : (c == F ? delta : 0.0f);
+                            split_tf32(v, hi[e], lo[e]);
+                        }
+                        const uint32_t oh = mn32_offset(c8 * 8, r, 512, 1024), ol = mn32_offset(K1 + c8 * 8, r, 512, 1024);
+                        st4(ub, oh, hi[0], hi[1], hi[2], hi[3]);
+                        st4(ub, oh + 16, hi[4], hi[5], hi[6], hi[7]);
+                        st4(ub, ol, lo[0], lo[1], lo[2], lo[3]);
+                        st4(ub, ol + 16, lo[4], lo[5], lo[6], lo[7]);
+                    }
                 }
-                const uint32_t oh = mn32_offset(c0, r, 512, 1024), ol = mn32_offset(K1 + c0, r, 512, 1024);
-                st4(ub, oh, hi[0], hi[1], hi[2], hi[3]);
-                st4(ub, oh + 16, hi[4], hi[5], hi[6], hi[7]);
-                st4(ub, ol, lo[0], lo[1], lo[2], lo[3]);
-                st4(ub, ol + 16, lo[4], lo[5], lo[6], lo[7]);
             }
             tmem_st_wait();
             fence_proxy_async();
             tc_fence_before();
             mbar_arrive(&s.a2_ready[grp]);
             mbar_arrive(&s.land_empty[st]);
+            st += NGROUPS;
+            if (st >= geo.stages) st -= geo.stages;
+            WX_TC_PH(6);
         }
+        if (r == 0) WX_TC_PH_FLUSH(grp);
+        WX_TC_STAMP(2);
         // ---- all tiles done: wait for this group's last GEMM2, then (after both groups) read T and assemble the slab ----
         if (it > 0 && !mbar_wait(&s.a2_free[grp], uint32_t((it - 1) & 1))) s.err = 8;
         tc_fence_after();
@@ -539,31 +675,35 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_step_kernel(const GridArgs a
                     slab[m * F + c] = wd * s.col_scale[c] * ((trow[c] + trow[K1 + c]) - s.col_shift[c] * tone);
             }
         }
-        // dW2: per-thread sums -> ordered column sums through smem (the Gate tiles are free now), one group at a time.
-        // Row r keeps its 128 values at column (c + 4 r) & 127, so both the row-wise stores and the column-wise reads
-        // are free of bank conflicts.
-        float* red = s.gate[0];                                       // [128 rows][128] floats = 64 KB = both Gate tiles
-        float colsum = 0.0f;
+        // dW2[0][j]: per-thread sums (64 TMEM columns) -> ordered column sums through smem (the Gate tiles are free now).
+        // Both groups store at once: row (grp, r) keeps its 64 values at column (c + 4 r) & 63, so the row-wise stores
+        // and the column-wise reads are free of bank conflicts; thread (h, j) of group 0 then adds the 128 rows of
+        // group h for column j in row order, and the two halves are added in group order.
+        float* red = s.gate[0];                                       // [2][128 rows][64] floats = 64 KB = both Gate tiles
 #pragma unroll 1
-        for (int g = 0; g < NGROUPS; ++g) {
-            if (grp == g) {
-#pragma unroll 1
-                for (int c = 0; c < 8; ++c) {
-                    float v[16];
-                    tmem_ld16(acc_base + c * 16, v);
-                    tmem_ld_wait();
+        for (int c = 0; c < 4; ++c) {
+            float v[16];
+            tmem_ld16(acc_base + c * 16, v);
+            tmem_ld_wait();
 #pragma unroll
-                    for (int q4 = 0; q4 < 4; ++q4)
-                        *reinterpret_cast<float4*>(&red[r * 128 + ((c * 16 + q4 * 4 + 4 * r) & 127)]) =
-                            make_float4(v[q4 * 4], v[q4 * 4 + 1], v[q4 * 4 + 2], v[q4 * 4 + 3]);
-                }
-            }
-            asm volatile("bar.sync 1, 256;" ::: "memory");
-            if (grp == 0)
-                for (int k = 0; k < TILE; ++k) colsum += red[k * 128 + ((r + 4 * k) & 127)];
-            asm volatile("bar.sync 1, 256;" ::: "memory");
+            for (int q4 = 0; q4 < 4; ++q4)
+                *reinterpret_cast<float4*>(&red[(grp * TILE + r) * 64 + ((c * 16 + q4 * 4 + 4 * r) & 63)]) =
+                    make_float4(v[q4 * 4], v[q4 * 4 + 1], v[q4 * 4 + 2], v[q4 * 4 + 3]);
         }
-        if (grp == 0) slab[OFF_W2 + (r & 1) * 64 + (r >> 1)] = colsum;        // TMEM column 2j+c holds dW2[c][j]
+        asm volatile("bar.sync 1, 256;" ::: "memory");
+        if (grp == 0) {
+            const int h = r >> 6, j = r & 63;
+            float colsum = 0.0f;
+            for (int k = 0; k < TILE; ++k) colsum += red[(h * TILE + k) * 64 + ((j + 4 * k) & 63)];
+            s.w_hi[r] = colsum;                                         // W1s is dead: 128 partial column sums
+        }
+        asm volatile("bar.sync 1, 256;" ::: "memory");
+        if (grp == 0 && r < 64) {
+            const float* part = s.w_hi;
+            const float d = part[r] + part[64 + r];
+            slab[OFF_W2 + r] = d;                                       // dW2[0][j]
+            slab[OFF_W2 + 64 + r] = -d;                                 // dW2[1][j] = -dW2[0][j] (two classes)
+        }
         // db2 / loss: warp sums in a fixed order
         const float w0 = warp_sum(gb2_0), w1 = warp_sum(gb2_1), w2 = warp_sum(loss_acc);
         if (lane == 0) {
@@ -581,6 +721,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_step_kernel(const GridArgs a
     // ================= CTA slab -> global; two-level ticket tree sums the slabs in a fixed order =================
     tc_fence_before();
     __syncthreads();
+    WX_TC_STAMP(3);
     if (warp == 0) tmem_dealloc(tm, TMEM_COLS);
     const float* slab = s.u[0];
     const unsigned nparts = gridDim.x;
@@ -598,6 +739,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_step_kernel(const GridArgs a
         s.role = atomicAdd(&tick[TICKET_GROUP0 + mygroup], 1u) == gsize - 1 ? 1 : 0;
     }
     __syncthreads();
+    WX_TC_STAMP(4);
     if (s.role == 0) return;
     __threadfence();
     const int ng4 = slab_stride / 4;
@@ -621,6 +763,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_step_kernel(const GridArgs a
     __syncthreads();
     if (tid == 0) s.role = atomicAdd(&tick[TICKET_TOP], 1u) == ngroups - 1 ? 2 : 1;
     __syncthreads();
+    WX_TC_STAMP(5);
     if (s.role != 2) return;
     __threadfence();
     if (a.tail == wxk::TAIL_ADAM && tid == 0) s.adam = wxk::adam_scalars(a.desc, a.state[0] + 1);
@@ -669,6 +812,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_step_kernel(const GridArgs a
             *a.loss_out = sum;
         }
     }
+    WX_TC_STAMP(6);
     if (tid < 32) {
         for (unsigned g = tid; g < ngroups; g += 32) tick[TICKET_GROUP0 + g] = 0u;
         if (tid == 0) {
@@ -734,7 +878,11 @@ int tc_launch(wx_ctx* ctx, GridArgs& a, cudaStream_t st, const char* who) {
     a.part = reinterpret_cast<float*>(ctx->scratch + WX_SCRATCH_PART_OFF);
     a.ticket = reinterpret_cast<unsigned int*>(ctx->scratch) + 1;
     a.desc = ctx->desc;
+#ifdef WX_TC_TIMERS
+    a.dbg = ctx->debug_times;      // developer build: per-CTA globaltimer stamps [grid][8]
+#else
     a.dbg = nullptr;
+#endif
     if (a.tail == wxk::TAIL_ADAM && ctx->peer.world > 1) {
         a.peer = ctx->peer;
         a.scale = a.scale / float(ctx->peer.world);          // mean over W*B rows (what DDP's averaged gradients give)
