@@ -159,6 +159,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_step_kernel(const GridArgs a
 #define WX_TC_PH_FLUSH(role) do { } while (0)
 #endif
     WX_TC_STAMP(0);
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");   // the next launch may begin its own prologue
     if (tid == 0 && (smem_u32(raw) & 1023u) != 0) atomicExch(err_out, 99);   // dynamic smem base not 1024-aligned
     if (tid == 0) {
         for (int i = 0; i < MAX_STAGES; ++i) {
@@ -179,6 +180,17 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_step_kernel(const GridArgs a
         s.err = 0;
     }
     if (warp == 0) tmem_alloc(&s.tmem_base, TMEM_COLS);
+    // Everything above touches only this CTA's own resources and may overlap the tail of the previous launch in the
+    // stream (programmatic dependent launch); parameters, statistics, step counter and scratch are read below.
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    // parameters and statistics: one coalesced pass into shared memory (U[0] is free until the first tile ends)
+    float* sp = s.u[0];                                           // [P] parameters
+    double* sst = reinterpret_cast<double*>(s.u[0] + ((P + 3) & ~3) + 4);   // [F][4] statistics (8-byte aligned)
+    for (int i = tid; i < P; i += TC_THREADS) sp[i] = a.params[i];
+    if (RAW)
+        for (int i = tid; i < 4 * F; i += TC_THREADS) sst[i] = a.stats[i];
+    if (tid == TC_THREADS - 1 && a.tail == wxk::TAIL_ADAM) s.adam = wxk::adam_scalars(a.desc, a.state[0] + 1);
+    __syncthreads();
     // W1s operand (hi/lo, K-major SW128), one thread per hidden unit; fp64 so that folding 1/std and the mean remainder
     // into the weights costs no accuracy (the products are rounded to fp32 once, like W1 itself)
     if (tid < 64) {
@@ -192,9 +204,9 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_step_kernel(const GridArgs a
                 const int c = c4 * 4 + e;
                 float v = 0.0f;
                 if (c < F) {
-                    double w = double(a.params[n * F + c]);
+                    double w = double(sp[n * F + c]);
                     if (RAW) {
-                        const double mean = a.stats[c * 4 + 1], rs = 1.0 / a.stats[c * 4 + 3];
+                        const double mean = sst[c * 4 + 1], rs = 1.0 / sst[c * 4 + 3];
                         w *= rs;
                         shift += w * (mean - double(float(mean)));
                     }
@@ -207,24 +219,24 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_step_kernel(const GridArgs a
             st4(s.w_lo, off, lo[0], lo[1], lo[2], lo[3]);
         }
         float bh, bl;
-        split_tf32(float(double(a.params[OFF_B1 + n]) - shift), bh, bl);
+        split_tf32(float(double(sp[OFF_B1 + n]) - shift), bh, bl);
         const uint32_t off = sw128_offset(n, F);
         *reinterpret_cast<float*>(reinterpret_cast<unsigned char*>(s.w_hi) + off) = bh;
         *reinterpret_cast<float*>(reinterpret_cast<unsigned char*>(s.w_lo) + off) = bl;
-        s.w2p[n] = make_float2(ds * a.params[OFF_W2 + n], ds * a.params[OFF_W2 + 64 + n]);
+        s.w2p[n] = make_float2(ds * sp[OFF_W2 + n], ds * sp[OFF_W2 + 64 + n]);
     } else if (tid < 96) {
         const int c = tid - 64;
         float mh = 0.0f, sc = 1.0f, sh = 0.0f;
         if (RAW && c < F) {
-            const double mean = a.stats[c * 4 + 1];
+            const double mean = sst[c * 4 + 1];
             mh = float(mean);
-            sc = float(1.0 / a.stats[c * 4 + 3]);
+            sc = float(1.0 / sst[c * 4 + 3]);
             sh = float(mean - double(mh));
         }
         s.mean_hi[c] = mh;
         s.col_scale[c] = sc;
         s.col_shift[c] = sh;
-        if (c < 2) s.b2[c] = a.params[OFF_B2 + c];
+        if (c < 2) s.b2[c] = sp[OFF_B2 + c];
     }
     fence_proxy_async();
     tc_fence_before();
@@ -766,37 +778,64 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_step_kernel(const GridArgs a
     WX_TC_STAMP(5);
     if (s.role != 2) return;
     __threadfence();
-    if (a.tail == wxk::TAIL_ADAM && tid == 0) s.adam = wxk::adam_scalars(a.desc, a.state[0] + 1);
-    // level 2: the group sums in group order -> this rank's [P+1] bucket in shared memory
+    // level 2: the group sums in group order (all of a thread's loads in flight at once), then the update.  Without a
+    // peer exchange every thread updates the four parameters it has just summed -- their p/m/v were requested before the
+    // sums -- and nothing goes through shared memory.
+    constexpr int MAXG = (148 + GROUP_CTAS - 1) / GROUP_CTAS;         // 13 groups at most on a 148-SM part
+    const bool exchange = a.peer.world > 1 && a.tail == wxk::TAIL_ADAM;
+    const bool vec_ok = a.tail == wxk::TAIL_ADAM && !exchange &&
+                        ((reinterpret_cast<uintptr_t>(a.p_rw) | reinterpret_cast<uintptr_t>(a.m) | reinterpret_cast<uintptr_t>(a.v)) & 15) == 0;
     float* bucket = s.u[1];
+    bool apply = true;
     for (int g = tid; g < ng4; g += TC_THREADS) {
+        const bool direct = vec_ok && 4 * g + 3 < P;
+        float4 p4, m4, v4;
+        if (direct) {
+            p4 = reinterpret_cast<const float4*>(a.p_rw)[g];
+            m4 = reinterpret_cast<const float4*>(a.m)[g];
+            v4 = reinterpret_cast<const float4*>(a.v)[g];
+        }
         const float4* src = reinterpret_cast<const float4*>(gpart) + g;
         float4 acc = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
-#pragma unroll 1
-        for (unsigned b = 0; b < ngroups; b += 4) {
-            float4 t[4];
+        if (ngroups <= MAXG) {
+            float4 t[MAXG];
 #pragma unroll
-            for (int u = 0; u < 4; ++u)
-                t[u] = b + u < ngroups ? __ldcg(src + size_t(b + u) * ng4) : make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+            for (int u = 0; u < MAXG; ++u)
+                t[u] = unsigned(u) < ngroups ? __ldcg(src + size_t(u) * ng4) : make_float4(0.0f, 0.0f, 0.0f, 0.0f);
 #pragma unroll
-            for (int u = 0; u < 4; ++u) {
+            for (int u = 0; u < MAXG; ++u) {
                 acc.x += t[u].x; acc.y += t[u].y; acc.z += t[u].z; acc.w += t[u].w;
             }
+        } else {
+            for (unsigned u = 0; u < ngroups; ++u) {
+                const float4 t = __ldcg(src + size_t(u) * ng4);
+                acc.x += t.x; acc.y += t.y; acc.z += t.z; acc.w += t.w;
+            }
         }
-        reinterpret_cast<float4*>(bucket)[g] = acc;
+        if (direct) {
+            wxk::adam_apply(p4.x, acc.x, m4.x, v4.x, s.adam);
+            wxk::adam_apply(p4.y, acc.y, m4.y, v4.y, s.adam);
+            wxk::adam_apply(p4.z, acc.z, m4.z, v4.z, s.adam);
+            wxk::adam_apply(p4.w, acc.w, m4.w, v4.w, s.adam);
+            reinterpret_cast<float4*>(a.p_rw)[g] = p4;
+            reinterpret_cast<float4*>(a.m)[g] = m4;
+            reinterpret_cast<float4*>(a.v)[g] = v4;
+        } else {
+            reinterpret_cast<float4*>(bucket)[g] = acc;               // the group that straddles P, gradients out, or DDP
+        }
     }
     __syncthreads();
     if (tid == 0) bucket[P] *= a.scale;                               // mean loss
     __syncthreads();
-    bool apply = true;
-    if (a.peer.world > 1 && a.tail == wxk::TAIL_ADAM) {
+    if (exchange) {
         // DDP exchange inside the kernel: one-shot all-reduce over NVLink peer memory (csrc/peer.cuh).  If a peer does
         // not show up in time the step is NOT applied on this rank (parameters, moments and step counter stay as they
         // were) and the sticky error code says so -- a visible stall instead of silently diverging replicas.
         apply = wxpeer::allreduce_cta(bucket, P + 1, a.peer, uint64_t(a.state[0]) + 1, tid, TC_THREADS);
         if (!apply && tid == 0) atomicExch(err_out, 20);
     }
-    for (int i = tid; i < P + 1; i += TC_THREADS) {
+    const int first_left = vec_ok ? (P & ~3) : 0;                     // elements not handled above
+    for (int i = first_left + tid; i < P + 1; i += TC_THREADS) {
         const float sum = bucket[i];
         if (a.tail == wxk::TAIL_GRADS) {
             a.out[i] = sum;
@@ -831,7 +870,20 @@ int tc_launch_inst(wx_ctx* ctx, const GridArgs& a, unsigned grid, int smem, cons
         WX_CUDA(cudaFuncSetAttribute(tc_step_kernel<RAW, DROP, FT>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
         if (dev >= 0 && dev < 64) attr_set[dev] = true;
     }
-    tc_step_kernel<RAW, DROP, FT><<<grid, TC_THREADS, smem, st>>>(a, ctx->desc.n_features, geo, err);
+    // programmatic dependent launch: this launch's prologue (barrier init, TMEM allocation) may overlap the tail of the
+    // previous kernel in the stream; the kernel itself waits (griddepcontrol.wait) before it reads anything a
+    // predecessor may have written
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(grid);
+    cfg.blockDim = dim3(TC_THREADS);
+    cfg.dynamicSmemBytes = size_t(smem);
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    WX_CUDA(cudaLaunchKernelEx(&cfg, tc_step_kernel<RAW, DROP, FT>, a, ctx->desc.n_features, geo, err));
     return WX_OK;
 }
 
