@@ -60,23 +60,21 @@ __device__ __forceinline__ bool mbar_try_wait_hint(uint64_t* bar, uint32_t parit
 }
 
 // Bounded wait: returns false if the barrier did not flip within ~2 s (a protocol bug must not hang the GPU).
+// A failed try_wait comes back after a few dozen cycles whatever the hint says; an idle role that kept polling at that
+// rate took a quarter of the SM's issue slots from the roles doing the work, hence the sleep between polls.
+template <unsigned SLEEP_NS = 128>
 __device__ __forceinline__ bool mbar_wait(uint64_t* bar, uint32_t parity) {
     if (mbar_try_wait(bar, parity)) return true;
 #pragma unroll 1
-    for (uint32_t spin = 0; spin < (1u << 21); ++spin) {
-        // idle roles must not steal issue slots from the row workers: park in hardware, ~1 us at a time
-        if (mbar_try_wait_hint(bar, parity, 1000u)) return true;
+    for (uint32_t spin = 0; spin < (1u << 23); ++spin) {
+        __nanosleep(SLEEP_NS);
+        if (mbar_try_wait(bar, parity)) return true;
     }
     return false;
 }
 
-// Latency-critical variant for the MMA issuer: tight polling (try_wait itself blocks for a hardware time slice).
-__device__ __forceinline__ bool mbar_wait_hot(uint64_t* bar, uint32_t parity) {
-#pragma unroll 1
-    for (uint32_t spin = 0; spin < (1u << 28); ++spin)
-        if (mbar_try_wait(bar, parity)) return true;
-    return false;
-}
+// Latency-critical variant for the MMA issuers: short sleeps.
+__device__ __forceinline__ bool mbar_wait_hot(uint64_t* bar, uint32_t parity) { return mbar_wait<32>(bar, parity); }
 
 // generic-proxy writes (st.shared) -> visible to the async proxy (tcgen05.mma / TMA reads of smem)
 __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }

@@ -22,12 +22,12 @@
 // hi*lo + lo*hi + hi*hi (~2^-21 relative); GEMM2's A operand is exact, so hi + lo of U alone gives the same accuracy.
 // dW2 / db2 / loss are row-local sums: dW2 lives in per-thread TMEM columns (packed fp32x2 FMAs), db2 / loss in registers.
 //
-// Roles (448 threads, one CTA per SM, persistent over 128-row tiles; tile i belongs to worker group i & 1):
+// Roles (480 threads, one CTA per SM, persistent over 128-row tiles; tile i belongs to worker group i & 1):
 //   warps 0-3 / 4-7  two row-worker groups: thread r <-> tile row r <-> TMEM lane r (row-local work, no shuffles):
 //                    everything from the GEMM1 accumulator on (ReLU/dropout/logits/softmax/dW2/Gate/U)
 //   warps 8-11       operand builders, every tile: centre + hi/lo split of the landed row (GEMM1 A), Philox words
 //   warp 12          TMA producer (cp.async.bulk of rows or F column segments + labels [+ keep bits], 2-3 stage ring)
-//   warp 13          MMA issuer (whole warp runs the loop, elect.sync picks the issuing lane)
+//   warps 13 / 14    MMA issuers for GEMM1 / GEMM2 (whole warp runs the loop, elect.sync picks the issuing lane)
 // Tail: CTA slabs are summed by a two-level ticket tree (12 CTAs per group, then the groups) in fixed order -- the
 // result is bit-reproducible -- then the cross-rank exchange (csrc/peer.cuh) and Adam run in the last CTA.
 #pragma once
@@ -47,9 +47,9 @@ constexpr int TILE = 128;
 constexpr int NGROUPS = 2;
 constexpr int WORKERS = NGROUPS * TILE;          // 256 row-worker threads
 constexpr int HELPERS = TILE;                    // 128 operand-builder threads (one per tile row)
-constexpr int TC_THREADS = WORKERS + HELPERS + 64;   // + producer warp + MMA warp
+constexpr int TC_THREADS = WORKERS + HELPERS + 96;   // + producer warp + two MMA warps
 constexpr int HELPER_WARP0 = WORKERS / 32;
-constexpr int PRODUCER_WARP = (WORKERS + HELPERS) / 32, MMA_WARP = PRODUCER_WARP + 1;
+constexpr int PRODUCER_WARP = (WORKERS + HELPERS) / 32, MMA1_WARP = PRODUCER_WARP + 1, MMA2_WARP = PRODUCER_WARP + 2;
 constexpr int MAX_STAGES = 6;
 constexpr int MAXF_TC = 31;                      // F feature columns + the ones column fit the 32-column operand tile
 constexpr int TMEM_COLS = 512;                   // D1 x3 [0,192) | T [192,256) | dW2 sums of group g [256+64g, 320+64g) |
@@ -76,7 +76,7 @@ struct TcSmem {
     float red_small[WORKERS / 32][4];            // db2_0, db2_1, loss per worker warp
     __align__(16) uint32_t pw[NPW][TILE][8];     // Philox words of the tiles in flight (helper -> workers), ring by tile
     uint64_t land_full[MAX_STAGES], land_empty[MAX_STAGES];
-    uint64_t xa_ready[2], a2_ready[NGROUPS], a2_free[NGROUPS], d1_full[ND1], pw_ready[NPW], pw_free[NPW];
+    uint64_t xa_ready[2], a2_ready[NGROUPS], a2_free[NGROUPS], d1_full[ND1], d1_free[ND1], pw_ready[NPW], pw_free[NPW];
     uint32_t tmem_base;
     int err;
     int role;                                    // 0 = not last, 1 = last of its group, 2 = last of the grid
@@ -175,7 +175,10 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_step_kernel(const GridArgs a
             mbar_init(&s.pw_ready[g], TILE);
             mbar_init(&s.pw_free[g], TILE);
         }
-        for (int g = 0; g < ND1; ++g) mbar_init(&s.d1_full[g], 1);
+        for (int g = 0; g < ND1; ++g) {
+            mbar_init(&s.d1_full[g], 1);
+            mbar_init(&s.d1_free[g], TILE);
+        }
         fence_mbar_init();
         s.err = 0;
     }
@@ -321,20 +324,23 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_step_kernel(const GridArgs a
             }
         }
         if (lane == 0) WX_TC_PH_FLUSH(4);
-    } else if (warp == MMA_WARP) {
-        // ================= MMA issuer =================
+    } else if (warp == MMA1_WARP) {
+        // ================= MMA issuer 1: GEMM1 of every tile =================
         // The WHOLE warp runs this code and one elected lane issues each MMA: operands stay warp-uniform (uniform
-        // registers) -- 3x faster issue than a lone thread.  One base descriptor per operand; a k-step only adds a
-        // constant to the start-address field.
+        // registers) -- 3x faster issue than a lone thread.  GEMM1 and GEMM2 are issued by different warps so that a
+        // ready GEMM1 (9 MMAs, a row-worker group is waiting for it) is not queued behind the 16 MMAs of a GEMM2.
         const uint32_t id1 = make_idesc_tf32(128, 64, false, false);
-        const uint32_t id2 = make_idesc_tf32(64, N2, true, true);
         const uint64_t wk_d[2] = {make_smem_desc(smem_u32(s.w_hi), 16, 1024), make_smem_desc(smem_u32(s.w_lo), 16, 1024)};
-        // group 1's tiles sit 32 KB after group 0's: + 2048 in the start-address field (16-byte units)
-        const uint64_t gate_d0 = make_smem_desc(smem_u32(s.gate[0]), 512, 1024, LAYOUT_SW128_B32);
-        const uint64_t u_d0 = make_smem_desc(smem_u32(s.u[0]), 512, 1024, LAYOUT_SW128_B32);
-        constexpr uint64_t GROUP_STEP = sizeof(float) * TILE * 64 / 16;
         const int k1steps = K1 / 8;
-        auto gemm1 = [&](uint32_t dst, uint32_t xa) {
+        WX_TC_PH(7);
+        for (int i = 0; i < my_tiles; ++i) {
+            const int q = i % ND1;
+            if (!mbar_wait_hot(&s.xa_ready[i & 1], uint32_t((i >> 1) & 1))) s.err = 3;
+            // D1[q] is free once the row workers of tile i - 3 have read it for the last time
+            if (i >= ND1 && !mbar_wait_hot(&s.d1_free[q], uint32_t((i / ND1 - 1) & 1))) s.err = 13;
+            tc_fence_after();
+            WX_TC_PH(0);
+            const uint32_t dst = tm + uint32_t(q) * 64, xa = tm + TM_XA + uint32_t(i & 1) * 64;
             bool acc = false;                    // small terms first: hi*lo, lo*hi, then hi*hi
 #pragma unroll
             for (int term = 0; term < 3; ++term) {
@@ -346,53 +352,27 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_step_kernel(const GridArgs a
                     acc = true;
                 }
             }
-        };
-        auto gemm2 = [&](int g, bool first) {
-            bool acc = !first;
-            const uint64_t gd = gate_d0 + uint64_t(g) * GROUP_STEP, ud = u_d0 + uint64_t(g) * GROUP_STEP;
-#pragma unroll
-            for (int k = 0; k < TILE / 8; ++k) {
-                umma_tf32_warp(tm + TM_T, gd + uint64_t(k * 128), ud + uint64_t(k * 128), id2, acc);   // +2048 B
-                acc = true;
-            }
-        };
-        // Two in-order queues, served as they become ready with GEMM1 first: the GEMM1 of the next tile (its operand is
-        // built ahead by the helper warps; its accumulator D1[i % 3] is free once the GEMM2 of tile i - 3 has been issued,
-        // because that waited for the rows workers' last reads) and the GEMM2 of the oldest finished tile.  A group that
-        // finishes a tile therefore finds the accumulator of its next tile already computed.
-        WX_TC_PH(7);
-        int i1 = 0, i2 = 0;                      // next GEMM1 tile, next GEMM2 tile
-        uint32_t idle = 0;
-        while (i2 < my_tiles) {
-            bool go1 = false, go2 = false;
-            if (lane == 0) {
-                go1 = i1 < my_tiles && i1 - i2 < ND1 && mbar_test_wait(&s.xa_ready[i1 & 1], uint32_t((i1 >> 1) & 1));
-                go2 = !go1 && i2 < i1 && mbar_test_wait(&s.a2_ready[i2 & 1], uint32_t((i2 >> 1) & 1));
-            }
-            go1 = __shfl_sync(0xffffffffu, go1, 0);
-            go2 = __shfl_sync(0xffffffffu, go2, 0);
-            if (go1) {
-                tc_fence_after();
-                WX_TC_PH(0);
-                gemm1(tm + uint32_t(i1 % ND1) * 64, tm + TM_XA + uint32_t(i1 & 1) * 64);
-                umma_commit_warp(&s.d1_full[i1 % ND1]);
-                WX_TC_PH(1);
-                ++i1;
-                idle = 0;
-            } else if (go2) {
-                tc_fence_after();
-                WX_TC_PH(2);
-                gemm2(i2 & 1, i2 == 0);
-                umma_commit_warp(&s.a2_free[i2 & 1]);
-                WX_TC_PH(3);
-                ++i2;
-                idle = 0;
-            } else if (++idle > (1u << 26)) {
-                s.err = 3;                       // neither queue moved for seconds: protocol bug, do not hang the GPU
-                break;
-            }
+            umma_commit_warp(&s.d1_full[q]);
+            WX_TC_PH(1);
         }
         if (lane == 0) WX_TC_PH_FLUSH(3);
+    } else if (warp == MMA2_WARP) {
+        // ================= MMA issuer 2: GEMM2 of every tile, as its Gate / U tiles become ready =================
+        const uint32_t id2 = make_idesc_tf32(64, N2, true, true);
+        // group 1's tiles sit 32 KB after group 0's: + 2048 in the start-address field (16-byte units)
+        const uint64_t gate_d0 = make_smem_desc(smem_u32(s.gate[0]), 512, 1024, LAYOUT_SW128_B32);
+        const uint64_t u_d0 = make_smem_desc(smem_u32(s.u[0]), 512, 1024, LAYOUT_SW128_B32);
+        constexpr uint64_t GROUP_STEP = sizeof(float) * TILE * 64 / 16;
+        for (int i = 0; i < my_tiles; ++i) {
+            const int g = i & 1;
+            if (!mbar_wait_hot(&s.a2_ready[g], uint32_t((i >> 1) & 1))) s.err = 4;
+            tc_fence_after();
+            const uint64_t gd = gate_d0 + uint64_t(g) * GROUP_STEP, ud = u_d0 + uint64_t(g) * GROUP_STEP;
+#pragma unroll
+            for (int k = 0; k < TILE / 8; ++k)
+                umma_tf32_warp(tm + TM_T, gd + uint64_t(k * 128), ud + uint64_t(k * 128), id2, !(i == 0 && k == 0));   // +2048 B
+            umma_commit_warp(&s.a2_free[g]);
+        }
     } else if (warp >= HELPER_WARP0) {
         // ================= operand builders (4 warps, thread r <-> tile row r, EVERY tile) =================
         // Centre the landed row, split it into the K-major hi/lo operand of GEMM1, and draw the row's dropout words --
@@ -541,7 +521,9 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_step_kernel(const GridArgs a
 
             // ---- phase A: a = relu(z) where kept (dropout scale folded into W2 and the dlogits), logits, Gate tile.
             //      The TMEM load of the next 16 units is in flight while this chunk is processed. ----
-            float2 lg = make_float2(0.0f, 0.0f), lgb = make_float2(0.0f, 0.0f);
+            float2 lgq[4];                                       // four independent accumulation chains
+#pragma unroll
+            for (int k = 0; k < 4; ++k) lgq[k] = make_float2(0.0f, 0.0f);
             const float2* __restrict__ w2p = s.w2p;              // read-only here: loads may pass the Gate stores
             float zbuf[2][16];
             tmem_ld16_nc(d1, zbuf[0]);
@@ -564,15 +546,14 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_step_kernel(const GridArgs a
                     const bool on = kp && !(z[q] <= 0.0f);                 // relu as torch's threshold: NaN passes
                     const float av = on ? z[q] : 0.0f;
                     const float2 w = w2p[cc * 16 + q];
-                    if (q & 1) lgb = __ffma2_rn(make_float2(av, av), w, lgb);
-                    else lg = __ffma2_rn(make_float2(av, av), w, lg);
+                    lgq[q & 3] = __ffma2_rn(make_float2(av, av), w, lgq[q & 3]);
                     z[q] = av;
                 }
                 tmem_st16_nc(d1 + cc * 16, z);                               // a replaces z in place: phase B reads it back
             }
             WX_TC_PH(3);
-            const float lg0 = (lg.x + lgb.x) + b2_0;
-            const float lg1 = (lg.y + lgb.y) + b2_1;
+            const float lg0 = ((lgq[0].x + lgq[1].x) + (lgq[2].x + lgq[3].x)) + b2_0;
+            const float lg1 = ((lgq[0].y + lgq[1].y) + (lgq[2].y + lgq[3].y)) + b2_1;
             // ---- softmax / loss / dlogits, ATen's operation order ----
             const float mx = fmaxf(lg0, lg1);
             const float e0 = lg0 - mx, e1 = lg1 - mx;
@@ -622,6 +603,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_step_kernel(const GridArgs a
                     }
                 }
             }
+            tc_fence_before();
+            mbar_arrive(&s.d1_free[i % ND1]);                     // last read of this tile's accumulator is done
             WX_TC_PH(5);
             // ---- U row = delta * D (MN-major, hi at columns [0,K1), lo at [K1, 2 K1)) ----
             {
