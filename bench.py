@@ -241,8 +241,6 @@ def run_wide(args, rank: int, local_rank: int, world: int) -> int:
 
     import torch
 
-    from wxddp.wide import WideEngine
-
     if args.warmup < 3:
         args.warmup = 3
     if not torch.cuda.is_available():
@@ -253,6 +251,40 @@ def run_wide(args, rank: int, local_rank: int, world: int) -> int:
     if world > 1:
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=device)
+    res = wide_measure(args, torch, dist, world, rank, local_rank, device, steps=args.steps, min_seconds=0.0,
+                       with_e2e=not args.no_e2e)
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return 0
+    line = {"metric": METRIC, "value": res["value"], "unit": UNIT, "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": res["ms_per_step"], "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+            "config": wide_config(args, hidden, B), "roofline": res["roofline"], "clocks": res["clocks"],
+            "gpu_launches": res["gpu_launches"], "final_loss": res["final_loss"], "kernel_status": res["kernel_status"]}
+    if "e2e" in res:
+        line["e2e"] = res["e2e"]
+    if not args.no_cpu_baseline and world == 1:
+        from oracle import wide_ref
+        r = wide_ref.time_cpu_steps(f, hidden, nl, 1024, 4, warmup=1)
+        line["cpu_baseline"] = {"value": r["samples_per_sec"], "unit": UNIT, "cores": r["cores"], "kind": "port",
+                                "sample": f"4 steps x 1024 rows, torch fp32 nn.Sequential + autograd + torch.optim.Adam "
+                                          f"on the host cores ({r['seconds']:.1f} s)"}
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+def wide_measure(args, torch, dist, world, rank, local_rank, device, steps: int, min_seconds: float, with_e2e: bool) -> dict:
+    """BASELINE.json configs[3] on the GPUs of this launch: `steps` optimizer steps per repeat, repeated until at least
+    `min_seconds` of device time have been timed (so that the SUSTAINED tensor peak is the honest denominator); both
+    the sustained and the burst fraction are reported.  Every rank returns; rank 0's dict is the one printed."""
+    from wxddp.wide import WideEngine
+
+    f, hidden, nl, B = args.features, args.wide_hidden, 3, args.wide_rows
+    weights = f * hidden + (nl - 1) * hidden * hidden + 2 * hidden
+    flops_per_row = 6.0 * weights - 2.0 * f * hidden            # SURVEY 8(d): no dX for the first layer
     torch.manual_seed(42)
     eng = WideEngine(f, hidden, nl, max_batch=B, device=device, world=world, rank=rank, process_group=dist,
                      seed=42 + 1000 * rank)
@@ -274,39 +306,28 @@ def run_wide(args, rank: int, local_rank: int, world: int) -> int:
         eng.step(table[w * B:(w + 1) * B], labels[w * B:(w + 1) * B])
         step_no[0] += 1
 
-    for _ in range(args.warmup):
+    for _ in range(max(3, args.warmup)):
         one_step()
     barrier()
     sampler = ClockSampler(local_rank)
     if rank == 0:
         sampler.start()
     l0 = eng.launch_count
-    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    barrier()
-    ev0.record()
-    for _ in range(args.steps):
-        one_step()
-    ev1.record()
-    barrier()
-    ms = ev0.elapsed_time(ev1)
-    launches = eng.launch_count - l0
+    times = timed_repeats(torch, dist, world, device, one_step, steps, 0, barrier, fill_ms=1e3 * min_seconds)
+    launches = (eng.launch_count - l0) // len(times)
     clocks = sampler.stop() if rank == 0 else None
-    t = torch.tensor([ms], dtype=torch.float64, device=device)
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms = float(t.item())
+    ms = median(times)
     final_loss = float(eng.grads[eng.P].item())
     status = eng.status()
-
-    e2e = None
-    if not args.no_e2e:
+    out = {}
+    if with_e2e:
         hx = [table[i * B:(i + 1) * B].cpu().pin_memory() for i in range(4)]
         hy = [labels[i * B:(i + 1) * B].cpu().pin_memory() for i in range(4)]
         for i in range(3):
             eng.step_host(hx[i % 4], hy[i % 4])
         barrier()
         t0 = time.perf_counter()
-        for i in range(args.steps):
+        for i in range(steps):
             last = eng.step_host(hx[i % 4], hy[i % 4])
         barrier()
         dt = time.perf_counter() - t0
@@ -314,40 +335,40 @@ def run_wide(args, rank: int, local_rank: int, world: int) -> int:
         if world > 1:
             dist.all_reduce(tt, op=dist.ReduceOp.MAX)
         dt = float(tt.item())
-        e2e = {"value": args.steps * B * world / dt, "unit": UNIT, "h2d_bytes_per_step": B * (4 * f + 8),
-               "d2h_bytes_per_step": 4, "ms_per_step": 1e3 * dt / args.steps, "last_loss": last,
-               "api": "wxddp.wide.WideEngine.step_host(pinned fp32 features, int64 labels) -> loss"}
-    if rank != 0:
-        if world > 1:
-            dist.destroy_process_group()
-        return 0
+        out["e2e"] = {"value": steps * B * world / dt, "unit": UNIT, "h2d_bytes_per_step": B * (4 * f + 8),
+                      "d2h_bytes_per_step": 4, "ms_per_step": 1e3 * dt / steps, "last_loss": last,
+                      "api": "wxddp.wide.WideEngine.step_host(pinned fp32 features, int64 labels) -> loss"}
     peak, peak_src = read_tensor_peak()
-    step_s = (ms / 1e3) / args.steps
+    burst = read_burst_peak()
+    step_s = (ms / 1e3) / steps
     achieved = B * flops_per_row / step_s / 1e12
-    roof = {"bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak,
-            "traffic": None, "kernel": "wide_gemm2_kernel (tcgen05.mma.cta_group::2 kind::f16, 256x256x64 tiles per SM pair, TMA "
-                                       "128B-swizzle tensor maps, 6-stage ring, TMEM double buffer): 7 of the 8 GEMM launches "
-                                       "per step; bias gradients, all-reduce and Adam run on a side stream under them",
-            "peak_source": peak_src, "algorithmic_flops_per_row": flops_per_row,
-            "note": "achieved = algorithmic FLOPs of the whole step / step time, i.e. it charges the head, bias-gradient, "
-                    "cast and Adam kernels and the DDP exchange to the GEMMs"}
-    line = {"metric": METRIC, "value": args.steps * B * world / (ms / 1e3), "unit": UNIT, "n_gpus": world,
-            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
-            "config": wide_config(args, hidden, B), "roofline": roof, "clocks": clocks, "gpu_launches": int(launches),
-            "final_loss": final_loss, "kernel_status": status}
-    if e2e is not None:
-        line["e2e"] = e2e
-    if not args.no_cpu_baseline and world == 1:
-        from oracle import wide_ref
-        r = wide_ref.time_cpu_steps(f, hidden, nl, 1024, 4, warmup=1)
-        line["cpu_baseline"] = {"value": r["samples_per_sec"], "unit": UNIT, "cores": r["cores"], "kind": "port",
-                                "sample": f"4 steps x 1024 rows, torch fp32 nn.Sequential + autograd + torch.optim.Adam "
-                                          f"on the host cores ({r['seconds']:.1f} s)"}
-    print(json.dumps(line), flush=True)
-    if world > 1:
-        dist.destroy_process_group()
-    return 0
+    out.update({
+        "value": steps * B * world / (ms / 1e3), "ms_per_step": ms / steps, "steps": steps, "repeats": len(times),
+        "timed_seconds": sum(times) / 1e3, "gpu_launches": int(launches), "final_loss": final_loss, "kernel_status": status,
+        "clocks": clocks, "rows_per_step_per_gpu": B,
+        "roofline": {"bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak,
+                     "frac_sustained": achieved / peak, "frac_burst": (achieved / burst) if burst else None,
+                     "peak_burst": burst, "traffic": None,
+                     "kernel": "wide_gemm2_kernel (tcgen05.mma.cta_group::2 kind::f16, 256x256x64 tiles per SM pair, TMA "
+                               "128B-swizzle tensor maps, 6-stage ring, TMEM double buffer): 7 of the 8 GEMM launches "
+                               "per step; bias gradients, all-reduce and Adam run on a side stream under them",
+                     "peak_source": peak_src, "algorithmic_flops_per_row": flops_per_row,
+                     "note": "achieved = algorithmic FLOPs of the whole step / step time, i.e. it charges the head, "
+                             "bias-gradient, cast and Adam kernels and the DDP exchange to the GEMMs; frac = frac_sustained "
+                             "when the timed region is seconds long, frac_burst applies to sub-second regions"}})
+    del eng, table, labels
+    torch.cuda.empty_cache()
+    return out
+
+
+def read_burst_peak():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        with open(path) as fh:
+            d = json.load(fh)
+        if "bf16_tflops" in d:
+            return float(d["bf16_tflops"])
+    return 1590.0
 
 
 def main() -> int:
@@ -367,6 +388,10 @@ def main() -> int:
     ap.add_argument("--kernel", default="auto", choices=["auto", "tc", "ffma"], help="step kernel at N=1")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-extras", action="store_true",
+                    help="skip the configs[2]/[3]/[4] sections (s3_epoch, wide, sweep) of the default line")
+    ap.add_argument("--s3-rows", type=int, default=100_000_000, help="total rows of the configs[2] table (split over the GPUs)")
+    ap.add_argument("--wide-seconds", type=float, default=4.0, help="timed seconds of the wide section of the default line")
     ap.add_argument("--workload", default="weather", choices=["weather", "wide"],
                     help="weather = BASELINE.json configs[1] (default, the headline); wide = configs[3], the 4-layer "
                          "hidden-4096 bf16 tcgen05 MLP")
@@ -424,6 +449,7 @@ def main() -> int:
         feats, _ = ctx.normalize_pack(cols, stats, impute=wxddp.IMPUTE_MEAN)
     n_windows = (T - B) // B + 1
     step_no = [0]
+    bound = ctx.bind_columns(cols)          # pointer array validated once: the per-step call is the C ABI call only
     use_tc = args.kernel != "ffma" and ctx.tc_ok_raw(cols, y, 0) and B % 4 == 0
     step_raw = ctx.tc_train_step_raw if use_tc else ctx.train_step_raw
     kernel_name = ("tc_step_kernel (tcgen05 tf32x3, wx_tc_train_step_raw)" if use_tc
@@ -446,7 +472,7 @@ def main() -> int:
         s = step_no[0]
         row0 = (s % n_windows) * B
         if world == 1 or fused_ddp:
-            step_raw(params, m, v, state, cols, stats, y, loss, row0=row0, batch=B,
+            step_raw(params, m, v, state, bound, stats, y, loss, row0=row0, batch=B,
                      impute=wxddp.IMPUTE_MEAN, dropout=wxddp.DROPOUT_PHILOX, seed=42 + 1000 * rank)
         else:
             # DDP: local sums pre-scaled by 1/(W*B), SUM across ranks (what torch's reducer does, :136),
@@ -474,6 +500,36 @@ def main() -> int:
     launches = (ctx.launch_count - launches0) // len(times)
     clocks = sampler.stop() if rank == 0 else None
     final_loss = float(loss.item()) if (world == 1 or fused_ddp) else float(grads[P].item())
+    tc_status = ctx.tc_status()
+
+    # ---- N > 1: the replicas must be bit-identical, and one fused step (in-kernel NVLink exchange) must agree with the
+    #      same step taken through the NCCL bucket path (wx_tc_mlp_grad -> all_reduce -> wx_adam_step) from the same state
+    ddp_check = None
+    if world > 1 and fused_ddp:
+        gathered = [torch.empty_like(params) for _ in range(world)]
+        dist.all_gather(gathered, params)
+        identical = all(bool(torch.equal(gathered[0], gq)) for gq in gathered[1:])
+        p0, m0, v0, s0 = params.clone(), m.clone(), v.clone(), state.clone()
+        step0 = int(s0[0].item())
+        row0 = 3 * B if T >= 4 * B else 0
+        step_raw(params, m, v, state, bound, stats, y, loss, row0=row0, batch=B, impute=wxddp.IMPUTE_MEAN,
+                 dropout=wxddp.DROPOUT_PHILOX, seed=42 + 1000 * rank)
+        torch.cuda.synchronize()
+        m_fused, loss_fused = m.clone(), float(loss.item())
+        params.copy_(p0); m.copy_(m0); v.copy_(v0); state.copy_(s0)
+        grad_fn(params, feats, y, row0=row0, batch=B, dropout=wxddp.DROPOUT_PHILOX, seed=42 + 1000 * rank, step=step0,
+                scale=1.0 / (world * B), out=grads)
+        dist.all_reduce(grads)
+        ctx.adam_step(params, grads, m, v, step0 + 1, n=P)
+        torch.cuda.synchronize()
+        upd = float((0.1 * grads[:P]).norm().item())               # m_new - 0.9 m_old = 0.1 g
+        rel = float((m_fused - m).norm().item()) / max(upd, 1e-30)
+        ddp_check = {"replicas_identical": bool(identical), "vs_nccl_rel": rel,
+                     "loss_fused": loss_fused, "loss_nccl": float(grads[P].item()), "tc_status": tc_status,
+                     "what": "params all-gathered after the timed loop and compared bit for bit; then one step from the same "
+                             "state through both paths: |m_fused - m_nccl| / |0.1 g| (the fused path standardises raw columns in "
+                             "the kernel, the NCCL path reads the packed table: <= 1 ulp apart per cell)"}
+        params.copy_(p0); m.copy_(m0); v.copy_(v0); state.copy_(s0)
 
     # ---- e2e: public API with HOST buffers; H2D of the step's raw rows + labels and D2H of the loss inside ----
     e2e = None
@@ -493,25 +549,99 @@ def main() -> int:
         for i in range(3):
             eng.submit_host(host_cols[i % n_host], host_y[i % n_host])
         eng.drain()
-        barrier()
-        t0 = time.perf_counter()
-        n_read = 0
-        for i in range(args.steps):
-            # H2D of batch i overlaps the kernel of batch i-1; every step's loss is read back (one call late)
-            r = eng.submit_host(host_cols[i % n_host], host_y[i % n_host])
-            n_read += r is not None
-        last = eng.drain()
-        n_read += 1
-        assert n_read == args.steps
-        barrier()
-        dt = time.perf_counter() - t0
-        tt = torch.tensor([dt], dtype=torch.float64, device=device)
-        if world > 1:
-            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-        dt = float(tt.item())
+        dts = []
+        for _ in range(5):
+            barrier()
+            t0 = time.perf_counter()
+            n_read = 0
+            for i in range(args.steps):
+                # H2D of batch i overlaps the kernel of batch i-1; every step's loss is read back (one call late)
+                r = eng.submit_host(host_cols[i % n_host], host_y[i % n_host])
+                n_read += r is not None
+            last = eng.drain()
+            n_read += 1
+            assert n_read == args.steps
+            barrier()
+            tt = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=device)
+            if world > 1:
+                dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+            dts.append(float(tt.item()))
+        dt = median(dts)
         e2e = {"value": args.steps * B * world / dt, "unit": UNIT, "h2d_bytes_per_step": B * (4 * f + 4),
-               "d2h_bytes_per_step": 4, "ms_per_step": 1e3 * dt / args.steps, "last_loss": last,
+               "d2h_bytes_per_step": 4, "ms_per_step": 1e3 * dt / args.steps, "last_loss": last, "repeats": len(dts),
+               "h2d_gbs_per_gpu": B * (4 * f + 4) * args.steps / dt / 1e9,
                "api": "wxddp.engine.StepEngine.submit_host(pinned raw fp32 columns, int32 labels) -> loss of the previous step; drain() for the last (H2D of batch i overlaps the kernel of batch i-1)"}
+
+    # ---- the other configurations BASELINE.json names, in the same line (rows N2, N3, N1 of the verdict's table) ----
+    extras = {}
+    if not args.no_extras:
+        def timed_once(fn, n):
+            ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            barrier()
+            ev0.record()
+            for i in range(n):
+                fn(i)
+            ev1.record()
+            barrier()
+            t = torch.tensor([ev0.elapsed_time(ev1)], dtype=torch.float64, device=device)
+            if world > 1:
+                dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            return float(t.item())
+
+        def step_at(row0, rows):
+            if world == 1 or fused_ddp:
+                step_raw(params, m, v, state, bound, stats, y, loss, row0=row0, batch=rows, impute=wxddp.IMPUTE_MEAN,
+                         dropout=wxddp.DROPOUT_PHILOX, seed=42 + 1000 * rank)
+            else:
+                grad_fn(params, feats, y, row0=row0, batch=rows, dropout=wxddp.DROPOUT_PHILOX, seed=42 + 1000 * rank,
+                        step=step_no[0], scale=1.0 / (world * rows), out=grads)
+                dist.all_reduce(grads)
+                step_no[0] += 1
+                ctx.adam_step(params, grads, m, v, step_no[0], n=P)
+
+        # configs[4]: batch-size sweep, rows per step and GPU from 256 to 1 Mi (latency-bound -> throughput-bound)
+        sweep = []
+        for rows in (256, 1024, 4096, 16384, 65536, 262144, 1048576):
+            if rows > T // 2:
+                continue
+            nwin = T // rows
+            n = 200 if rows <= 65536 else 50
+            fn = lambda i, rows=rows, nwin=nwin: step_at(((i * 7919) % nwin) * rows, rows)
+            timed_once(fn, 5)
+            ts = [timed_once(fn, n) for _ in range(3)]
+            t_ms = median(ts)
+            sweep.append({"rows_per_step_per_gpu": rows, "rows_per_step": rows * world, "us_per_step": 1e3 * t_ms / n,
+                          "samples_per_s": n * rows * world / (t_ms / 1e3)})
+        extras["sweep"] = sweep
+        # configs[2]: one epoch over a 100 M-row table sharded by rows over the GPUs, 1 Mi rows per step and GPU
+        del raw, cols, bound
+        feats = None
+        torch.cuda.empty_cache()
+        shard = args.s3_rows // world // 4 * 4
+        raw, y = synth_raw_on_device(torch, shard, f, 4321 + rank, device)
+        cols = [raw[j] for j in range(f)]
+        bound = ctx.bind_columns(cols)
+        stats = ctx.col_stats(cols)
+        if world > 1:
+            parts = [torch.empty_like(stats) for _ in range(world)]
+            dist.all_gather(parts, stats)
+            stats = ctx.stats_merge(torch.stack(parts).contiguous())
+        n_steps = (shard + B - 1) // B
+        if world == 1 or fused_ddp:
+            ep = lambda i: step_at(i * B, min(B, shard - i * B) // 4 * 4)
+            timed_once(ep, 3)
+            ep_ms = [timed_once(ep, n_steps) for _ in range(3)]
+            extras["s3_epoch"] = {"rows_total": shard * world, "rows_per_gpu": shard, "steps": n_steps,
+                                  "rows_per_step_per_gpu": B, "ms": median(ep_ms), "ms_runs": ep_ms,
+                                  "samples_per_s": shard * world / (median(ep_ms) / 1e3), "final_loss": float(loss.item()),
+                                  "kernel_status": ctx.tc_status(),
+                                  "table": f"{shard} rows x {f} raw fp32 columns per GPU ({shard * f * 4 / 1e9:.1f} GB) resident in HBM"}
+        del raw, cols, bound
+        torch.cuda.empty_cache()
+        # configs[3]: the wide MLP, timed for seconds so that the sustained tensor peak is the denominator
+        w = wide_measure(args, torch, dist, world, rank, local_rank, device, steps=args.steps,
+                         min_seconds=args.wide_seconds, with_e2e=not args.no_e2e)
+        extras["wide"] = w
 
     if rank != 0:
         if world > 1:
@@ -540,11 +670,14 @@ def main() -> int:
             "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": workload_config(args, B),
             "roofline": roof, "clocks": clocks, "gpu_launches": int(launches), "final_loss": final_loss,
-            "repeats": len(times), "ms_per_step_min": min(times) / args.steps, "ms_per_step_max": max(times) / args.steps,
+            "kernel_status": tc_status, "repeats": len(times), "ms_per_step_min": min(times) / args.steps, "ms_per_step_max": max(times) / args.steps,
             "timing": f"median of {len(times)} repeats of {args.steps} steps each (CUDA events, barrier + synchronize around "
                       f"every repeat, max over ranks); gpu_launches counts one repeat"}
     if e2e is not None:
         line["e2e"] = e2e
+    if ddp_check is not None:
+        line["ddp_check"] = ddp_check
+    line.update(extras)
     if not args.no_cpu_baseline and world == 1:
         rows_cpu = args.cpu_rows_per_step if args.cpu_rows_per_step else B
         r, threads = cpu_baseline(f, max(1, rows_cpu // 2), args.cpu_steps, 2)
