@@ -29,6 +29,7 @@ struct wx_ctx {
     int64_t launches;
     long long* debug_times;   // optional device buffer [grid][4]: smid, t_start, t_loop_end, t_exit (globaltimer ns)
     unsigned char* inbox;     // this rank's peer inbox (wx_peer_export), NULL until exported
+    unsigned int peer_epoch;  // number of wx_peer_connect calls so far (part of every exchange tag)
     wxpeer::PeerArgs peer;    // world <= 1 until wx_peer_connect
     void* peer_mapped[wxpeer::MAXW];   // cudaIpcOpenMemHandle results to close at destroy
     int wide_reserved_sms;    // SMs the wide GEMMs leave free for a concurrent collective (wx_wide_reserve_sms), default 0

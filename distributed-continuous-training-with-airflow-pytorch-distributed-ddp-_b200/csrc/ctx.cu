@@ -48,6 +48,7 @@ int wx_create(int device, const wx_model_desc* desc, wx_ctx** out) {
     c->wide_reserved_sms = 0;
     c->debug_times = nullptr;
     c->inbox = nullptr;
+    c->peer_epoch = 0;
     memset(&c->peer, 0, sizeof(c->peer));
     memset(c->peer_mapped, 0, sizeof(c->peer_mapped));
     cudaError_t e = cudaMalloc(&c->scratch, c->scratch_bytes);
@@ -119,6 +120,8 @@ int wx_peer_connect(wx_ctx* ctx, int rank, int world, const void* handles) {
         ctx->peer_mapped[q] = p;
         pa.inbox[q] = static_cast<unsigned char*>(p);
     }
+    pa.epoch = ++ctx->peer_epoch;            // every rank connects equally often: the epochs agree across ranks
+    if (pa.epoch == 0 || pa.epoch > 255) pa.epoch = ctx->peer_epoch = 1;
     ctx->peer = pa;
     return WX_OK;
 }
