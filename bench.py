@@ -638,6 +638,8 @@ def main() -> int:
                                   "table": f"{shard} rows x {f} raw fp32 columns per GPU ({shard * f * 4 / 1e9:.1f} GB) resident in HBM"}
         del raw, cols, bound
         torch.cuda.empty_cache()
+        if world > 1:
+            extras[f"gpu_reference_config_w{world}"] = reference_config_ddp(torch, dist, device, rank, world)
         # configs[3]: the wide MLP, timed for seconds so that the sustained tensor peak is the denominator
         w = wide_measure(args, torch, dist, world, rank, local_rank, device, steps=args.steps,
                          min_seconds=args.wide_seconds, with_e2e=not args.no_e2e)
@@ -697,6 +699,51 @@ def main() -> int:
     if world > 1:
         dist.destroy_process_group()
     return 0
+
+
+def reference_config_ddp(torch, dist, device, rank: int, world: int) -> dict:
+    """The reference's own DDP regime on GPUs: WORLD_SIZE ranks x 4 rows per step (train_lightning_ddp.py:122,:136,
+    docker-compose.yml:124 has WORLD_SIZE=2), 145,460 x 5 table, sampler-ordered rows, 2048 optimizer steps per launch of
+    the resident kernel with the gradient exchange inside it.  Printed as gpu_reference_config_w<N>."""
+    from wxddp.engine import StepEngine
+
+    f, n, batch = 5, 116_368, 4
+    g = torch.Generator(device=device)
+    g.manual_seed(7)
+    x = torch.randn(n, f, device=device, generator=g)
+    y = (torch.rand(n, device=device, generator=g) < 0.13).to(torch.int64)
+    per_rank = n // world // batch * batch
+    order = torch.randperm(n, device=device, generator=g)[rank * per_rank:(rank + 1) * per_rank].contiguous()
+    torch.manual_seed(42)
+    eng = StepEngine(f, device=device, world=world, rank=rank, process_group=dist)
+    eng.connect_peers()
+    per_launch = 2048
+    n_steps = per_rank // batch
+    buf = torch.empty(per_launch, device=device)
+
+    def epoch():
+        s = 0
+        while s < n_steps:
+            k = min(per_launch, n_steps - s)
+            eng.steps_small(x, y, order[s * batch:(s + k) * batch], k, batch, buf)
+            s += k
+
+    epoch()
+    dist.barrier()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    epoch()
+    e1.record()
+    torch.cuda.synchronize()
+    t = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=device)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t.item())
+    eng.check()
+    return {"value": n_steps * batch * world / (ms / 1e3), "unit": UNIT, "us_per_step": 1e3 * ms / n_steps, "world": world,
+            "sample": f"one epoch: {n_steps} optimizer steps of {batch} rows per rank x {world} ranks (F=5), {per_launch} steps "
+                      f"per launch of wx_train_steps_small, [P+1] bucket exchanged over NVLink inside the kernel every step, "
+                      f"{ms:.1f} ms", "last_loss": float(buf[0].item())}
 
 
 def reference_config_on_gpu(torch, wxddp, device) -> dict:

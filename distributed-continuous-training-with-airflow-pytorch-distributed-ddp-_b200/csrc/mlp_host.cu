@@ -248,6 +248,13 @@ int wx_train_steps_small(wx_ctx* ctx, float* params, float* m, float* v, int64_t
     sa.loss_out = loss_out;
     int smem = 0;
     WX_CUDA(cudaSetDevice(ctx->device));
+    if (ctx->peer.world > 1) {
+        // after wx_peer_connect the steps are DDP steps: every rank launches the same number of steps of the same batch
+        WX_CHECK_ARG(batch <= WARPS * R, "wx_train_steps_small: with connected peers the batch per rank is at most %d rows "
+                     "(got %lld); larger batches take wx_tc_train_step", WARPS * R, (long long)batch);
+        sa.peer = ctx->peer;
+        sa.err = reinterpret_cast<int*>(ctx->scratch) + 8;
+    }
     if (batch > WARPS * R) {
         // more rows than one CTA's eight warps take in a pass: the resident multi-CTA kernel (grid barrier per step)
         small_kernel_t kr = pick_resident_kernel(ctx->desc.n_features, &smem);

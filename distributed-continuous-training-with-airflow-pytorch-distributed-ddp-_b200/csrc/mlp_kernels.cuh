@@ -432,6 +432,7 @@ struct SmallArgs {
     float* part;                    // [2][gridDim.x][slab_stride] CTA partial sums, double-buffered by step parity
     unsigned long long* bar;        // grid barrier counter, zero at launch
     int* err;                       // sticky status word
+    wxpeer::PeerArgs peer;          // world > 1: the [P+1] sums are exchanged over NVLink inside every step (one CTA only)
 };
 
 template <int F>
@@ -455,7 +456,9 @@ __global__ void __launch_bounds__(THREADS, 1) mlp_small_steps_kernel(const Small
     const uint2 key = make_uint2(uint32_t(sa.seed), uint32_t(sa.seed >> 32));
     const int nchunks = int((sa.batch + R - 1) / R);       // <= WARPS
     const bool has_chunk = warp < nchunks;
-    const float scale = 1.0f / float(sa.batch);
+    const bool ddp = sa.peer.world > 1;                    // mean over world * batch rows, as DDP's averaged gradients give
+    const float scale = 1.0f / (float(sa.batch) * float(ddp ? sa.peer.world : 1));
+    int64_t done = sa.n_steps;                             // steps actually taken (fewer if a peer stops arriving)
     float* stg0 = stage_base + warp * 2 * R * D::FS;
 
     // a GridArgs view so load_meta / stage_chunk can be reused; row window moves with the step
@@ -509,6 +512,16 @@ __global__ void __launch_bounds__(THREADS, 1) mlp_small_steps_kernel(const Small
         }
         if (tid == 0) s_adam = adam_scalars(sa.desc, step0 + s + 1);
         __syncthreads();
+        if (ddp) {
+            // DDP's bucket all-reduce + the sync_dist loss (train_lightning_ddp.py:70,:136) without leaving the kernel:
+            // the [P+1] sums cross NVLink once per step (csrc/peer.cuh).  A peer that stops arriving ends the launch here
+            // with the step NOT applied; the status word tells the host.
+            if (!wxpeer::allreduce_cta(slab, D::P + 1, sa.peer, uint64_t(step0 + s + 1), tid, THREADS)) {
+                if (tid == 0 && sa.err != nullptr) atomicExch(sa.err, 20);
+                done = s;
+                break;
+            }
+        }
         for (int i = tid; i < D::P; i += THREADS) adam_apply(s_p[i], slab[i], s_m[i], s_v[i], s_adam);
         if (tid == 0) sa.loss_out[s] = slab[D::P] * scale;
         __syncthreads();
@@ -520,7 +533,7 @@ __global__ void __launch_bounds__(THREADS, 1) mlp_small_steps_kernel(const Small
         sa.m[i] = s_m[i];
         sa.v[i] = s_v[i];
     }
-    if (tid == 0) sa.state[0] = step0 + sa.n_steps;
+    if (tid == 0) sa.state[0] = step0 + done;
 }
 
 

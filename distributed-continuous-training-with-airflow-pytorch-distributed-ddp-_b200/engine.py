@@ -56,7 +56,9 @@ class StepEngine:
 
     def connect_peers(self) -> None:
         """Exchange CUDA IPC handles of the per-rank inboxes so the fused tensor-core steps can all-reduce the [P+1]
-        bucket inside the kernel (NVLink peer stores) instead of mlp_grad -> NCCL -> adam (one launch per step)."""
+        bucket inside the kernel (NVLink peer stores) instead of mlp_grad -> NCCL -> adam (one launch per step).
+        All ranks must be GPUs of one node.  The barrier at the end is part of the protocol: no rank may step before
+        every rank has connected."""
         if self.world == 1:
             return
         mine = self.ctx.peer_export()
@@ -65,6 +67,23 @@ class StepEngine:
         self.ctx.peer_connect(self.rank, self.world, handles)
         self.dist.barrier()
         self.peers = True
+
+    def check(self) -> None:
+        """Raise if a fused step kernel recorded a protocol error since the context was created (20: a peer did not
+        arrive in the in-kernel exchange -- that step was NOT applied on this rank).  Synchronises the device."""
+        st = self.ctx.tc_status()
+        if st != 0:
+            what = "a peer did not arrive in the in-kernel gradient exchange; the step was not applied" if st == 20 \
+                else "a bounded barrier wait inside the step kernel expired"
+            raise WxError(f"step kernel status {st}: {what}")
+
+    def steps_small(self, x, y, rows, n_steps: int, batch: int, losses: torch.Tensor, dropout: int = DROPOUT_PHILOX) -> None:
+        """`n_steps` optimizer steps of `batch` sampler-ordered rows each in ONE launch (the reference's batch-4 regime,
+        train_lightning_ddp.py:122): parameters and Adam moments stay in shared memory between the steps; with connected
+        peers every step's [P+1] sums cross NVLink inside the kernel (DDP, :136)."""
+        self.ctx.train_steps_small(self.params, self.m, self.v, self.state, x, y, losses, n_steps=n_steps, batch=batch,
+                                   row_idx=rows, dropout=dropout, seed=self._dropout_seed())
+        self.steps_done += n_steps
 
     # ---- statistics ------------------------------------------------------------------------------
     def set_stats(self, stats: torch.Tensor) -> None:
@@ -120,6 +139,7 @@ class StepEngine:
         self.dist.all_reduce(self.bucket)                                    # C2 + C3 in one bucket
         self.steps_done += 1
         self.ctx.adam_step(self.params, self.bucket, self.m, self.v, self.steps_done, n=self.P)
+        self.state[:1] += 1               # the device counter drives the fused kernels' Adam / dropout / exchange tags
         return self.bucket[self.P:self.P + 1]
 
     def step_raw(self, cols, y, *, row0: int = 0, batch: int | None = None, impute: int = IMPUTE_MEAN,
@@ -235,4 +255,5 @@ class StepEngine:
         if self.world > 1:
             self.dist.all_reduce(tot)
         tot = tot.cpu()
+        self.check()
         return float(tot[0] / tot[2]), float(tot[1] / tot[2])

@@ -28,6 +28,7 @@ from .surface import MetricLogger, TopOneCheckpoint, build_checkpoint
 
 SEED = 42                      # pl.seed_everything(42), train_lightning_ddp.py:14
 SMALL_BATCH_MAX = 512          # many steps per launch pay off up to here (one CTA to 64 rows, resident multi-CTA above)
+SMALL_BATCH_DDP_MAX = 64       # with the in-kernel DDP exchange: the single-CTA kernel only
 STEPS_PER_LAUNCH = 4096
 
 
@@ -86,6 +87,8 @@ def fit(features: torch.Tensor, labels: torch.Tensor, *, device, rank: int = 0, 
     params0 = init_params_like_reference(f)
     make = engine_factory or StepEngine        # tests inject a CPU double to exercise the N>1 host logic over gloo
     eng = make(f, device=device, world=world, rank=rank, process_group=dist, params=params0, seed=SEED)
+    if world > 1 and not parity and hasattr(eng, "connect_peers"):
+        eng.connect_peers()             # DDP exchange inside the step kernels (all ranks are GPUs of this node)
     dev = eng.device
     x_d = features.to(dev).contiguous()
     y_d = labels.to(dev).contiguous()
@@ -157,19 +160,20 @@ def _run_epoch(eng: StepEngine, x_d, y_d, rows_d, n_rows: int, batch: int, n_ste
     """All optimizer steps of one epoch.  Returns the per-step `train_loss` (rank mean when world > 1)."""
     dev = eng.device
     losses: list[float] = []
-    if world == 1 and batch <= SMALL_BATCH_MAX and not parity:
-        # the reference's regime: thousands of tiny steps -> many steps per launch, one resident CTA
+    small_max = SMALL_BATCH_MAX if world == 1 else SMALL_BATCH_DDP_MAX
+    if (world == 1 or getattr(eng, "peers", False)) and batch <= small_max and not parity:
+        # the reference's regime: thousands of tiny steps -> many steps per launch, one resident CTA (per rank: with
+        # WORLD_SIZE > 1 every step's gradient bucket crosses NVLink inside that kernel)
         s = 0
         n_full = min(n_steps, full_steps)
         buf = torch.empty(min(STEPS_PER_LAUNCH, max(n_full, 1)), device=dev)
         while s < n_full:
             k = min(STEPS_PER_LAUNCH, n_full - s)
-            eng.ctx.train_steps_small(eng.params, eng.m, eng.v, eng.state, x_d, y_d, buf, n_steps=k, batch=batch,
-                                      row_idx=rows_d[s * batch:(s + k) * batch].contiguous(), dropout=DROPOUT_PHILOX,
-                                      seed=eng._dropout_seed())
-            eng.steps_done += k
+            eng.steps_small(x_d, y_d, rows_d[s * batch:(s + k) * batch].contiguous(), k, batch, buf)
             losses += buf[:k].cpu().tolist()
             s += k
+        if world > 1:
+            eng.check()
         if n_steps > full_steps:                            # ragged last batch (drop_last=False)
             l = eng.step(x_d, y_d, row_idx=rows_d[full_steps * batch:n_rows].contiguous())
             losses.append(float(l.item()))
