@@ -53,6 +53,7 @@ SIGNATURES = {
     "wx_col_stats": (_int, [_vp, C.POINTER(_vp), _int, C.POINTER(_vp), _i64, _vp, _vp]),
     "wx_stats_merge": (_int, [_vp, _vp, _int, _vp, _vp]),
     "wx_normalize_pack": (_int, [_vp, C.POINTER(_vp), _int, C.POINTER(_vp), _i64, _vp, _int, _vp, _vp, _vp]),
+    "wx_zscore_f64": (_int, [_vp, C.POINTER(_vp), _int, C.POINTER(_vp), _i64, _vp, C.POINTER(_vp), _vp]),
     "wx_impute_index_list": (_int, [_vp, _vp, _i64, _vp, _i64, _vp, _vp]),
     "wx_mlp_grad": (_int, [_vp, _vp, _vp, _vp, _vp, _i64, _i64, _int, _vp, _u64, _u64, C.c_float, _vp, _vp]),
     "wx_mlp_grad_static": (_int, [_int, _vp, _vp, _vp, _vp, _i64, _i64, _int, _vp, _u64, _u64, C.c_float, _vp, _vp]),

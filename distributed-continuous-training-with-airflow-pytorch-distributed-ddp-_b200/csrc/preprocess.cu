@@ -530,6 +530,55 @@ __global__ void __launch_bounds__(IDX_THREADS) idx_write_kernel(const uint32_t* 
     }
 }
 
+// ---- columnar fp64 z-score: the `*_norm` columns exactly as preprocess.py:38-41 writes them ------------------------
+// out_j[i] = ((double)col_j[i] - mean_j) / std_val_j with IEEE float64 subtraction and DIVISION (not a reciprocal
+// multiply): bit-identical to the float64 expression Spark evaluates.  A clear validity bit gives NaN (SQL null).
+// HBM-bound: 8 (4) bytes in, 8 bytes out per cell; grid.y = column, each thread owns pairs of rows (16-byte stores).
+struct WxOutCols {
+    double* col[WX_MAX_FEATURES];
+};
+
+template <typename T>
+__global__ void __launch_bounds__(256) zscore_f64_kernel(const WxCols in, const WxOutCols out, int64_t n,
+                                                          const double* __restrict__ stats) {
+    const int j = blockIdx.y;
+    const T* __restrict__ x = static_cast<const T*>(in.col[j]);
+    const uint8_t* __restrict__ valid = in.valid[j];
+    double* __restrict__ o = out.col[j];
+    const double mean = stats[j * 4 + 1], sd = stats[j * 4 + 3];
+    const bool vec = ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(o)) & 15) == 0;
+    const int64_t npairs = n >> 1;
+    const int64_t stride = int64_t(gridDim.x) * blockDim.x;
+    if (vec) {
+        for (int64_t pidx = int64_t(blockIdx.x) * blockDim.x + threadIdx.x; pidx < npairs; pidx += stride) {
+            const int64_t i = pidx * 2;
+            double a, b;
+            if (sizeof(T) == 8) {
+                const double2 v = *reinterpret_cast<const double2*>(x + i);
+                a = v.x; b = v.y;
+            } else {
+                const float2 v = *reinterpret_cast<const float2*>(x + i);
+                a = double(v.x); b = double(v.y);
+            }
+            a = (a - mean) / sd;
+            b = (b - mean) / sd;
+            if (valid != nullptr) {
+                const uint8_t bits = valid[i >> 3] >> (i & 7);         // i is even: both bits sit in the same byte
+                if (!(bits & 1)) a = __longlong_as_double(0x7ff8000000000000ll);
+                if (!(bits & 2)) b = __longlong_as_double(0x7ff8000000000000ll);
+            }
+            *reinterpret_cast<double2*>(o + i) = make_double2(a, b);
+        }
+    }
+    // unaligned columns: scalar over everything; aligned: only the odd last row
+    const int64_t first = vec ? (npairs << 1) : 0;
+    for (int64_t i = first + int64_t(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += stride) {
+        double a = (double(x[i]) - mean) / sd;
+        if (valid != nullptr && !((valid[i >> 3] >> (i & 7)) & 1)) a = __longlong_as_double(0x7ff8000000000000ll);
+        o[i] = a;
+    }
+}
+
 int fill_cols(const wx_ctx* ctx, const void* const* cols, const uint8_t* const* validity, int dtype, WxCols* wc,
               const char* who) {
     const int f = ctx->desc.n_features;
@@ -679,6 +728,35 @@ int wx_normalize_pack(wx_ctx* ctx, const void* const* cols, int dtype, const uin
         rc = launch_pack<double>(ctx, f, (cudaStream_t)stream, wc, n, stats, impute_mode, features_out,
                                  nullmask_out);
     if (rc != WX_OK) return rc;
+    WX_LAUNCH_CHECK(ctx);
+    return WX_OK;
+}
+
+int wx_zscore_f64(wx_ctx* ctx, const void* const* cols, int dtype, const uint8_t* const* validity, int64_t n,
+                  const double* stats, double* const* out_cols, void* stream) {
+    WX_CHECK_ARG(ctx != nullptr, "wx_zscore_f64: ctx is NULL");
+    WX_CHECK_ARG(n >= 0, "wx_zscore_f64: n < 0");
+    if (n == 0) return WX_OK;
+    WX_CHECK_ARG(stats && out_cols, "wx_zscore_f64: stats/out_cols is NULL");
+    WxCols wc;
+    int rc = fill_cols(ctx, cols, validity, dtype, &wc, "wx_zscore_f64");
+    if (rc != WX_OK) return rc;
+    const int f = ctx->desc.n_features;
+    WxOutCols oc;
+    for (int j = 0; j < WX_MAX_FEATURES; ++j) oc.col[j] = nullptr;
+    for (int j = 0; j < f; ++j) {
+        WX_CHECK_ARG(out_cols[j] != nullptr && (reinterpret_cast<uintptr_t>(out_cols[j]) & 7) == 0,
+                     "wx_zscore_f64: output column %d is NULL or not 8-byte aligned", j);
+        oc.col[j] = out_cols[j];
+    }
+    WX_CUDA(cudaSetDevice(ctx->device));
+    int64_t gx = ((n >> 1) + 255) / 256;
+    const int64_t cap = (int64_t(ctx->num_sms) * 8 + f - 1) / f;      // ~8 resident CTAs per SM over all columns
+    if (gx > cap) gx = cap;
+    if (gx < 1) gx = 1;
+    dim3 grid((unsigned)gx, (unsigned)f);
+    if (dtype == WX_F32) zscore_f64_kernel<float><<<grid, 256, 0, (cudaStream_t)stream>>>(wc, oc, n, stats);
+    else zscore_f64_kernel<double><<<grid, 256, 0, (cudaStream_t)stream>>>(wc, oc, n, stats);
     WX_LAUNCH_CHECK(ctx);
     return WX_OK;
 }

@@ -166,6 +166,17 @@ class Context:
         check(self.lib.wx_normalize_pack(self._h, cp, dt, vp, n, _p(stats), impute, _p(out), _p(nm), self._stream()))
         return out, nm
 
+    def zscore_f64(self, cols, stats: torch.Tensor, validity=None, out: torch.Tensor | None = None) -> torch.Tensor:
+        """preprocess.py:38-41 as Spark writes it: columnar float64 `(col - mean) / std_val`, [F,N]; nulls -> NaN."""
+        cp, vp, dt, n = self._cols(cols, validity)
+        self._chk(stats, torch.float64, "stats", self.n_features * 4)
+        if out is None:
+            out = torch.empty(self.n_features, n, dtype=torch.float64, device=self.device)
+        self._chk(out, torch.float64, "out", n * self.n_features)
+        op = _lib.ptr_array([out[j].data_ptr() for j in range(self.n_features)])
+        check(self.lib.wx_zscore_f64(self._h, cp, dt, vp, n, _p(stats), op, self._stream()))
+        return out
+
     def impute_index_list(self, nullmask: torch.Tensor, capacity: int | None = None):
         """Ascending flat indices row*F+col of the null cells; returns (idx[:min(count,capacity)], count)."""
         self._chk(nullmask, torch.int32, "nullmask")

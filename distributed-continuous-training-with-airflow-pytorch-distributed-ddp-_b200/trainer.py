@@ -11,7 +11,8 @@ uploaded once per epoch, and steps run as CUDA kernels (`wx_train_steps_small` f
 Extra env (all optional, defaults = the reference's constants): WX_DATA_DIR (/workspace/data/processed),
 WX_MODEL_DIR (/workspace/data/models), WX_BATCH_SIZE (4), WX_MAX_EPOCHS (10), WX_LOG_EVERY (5), WX_PARITY (0: Philox
 dropout; 1: replay torch's CPU dropout stream and loader RNG draws so the loss curve tracks the reference's),
-WX_MAX_STEPS, WX_METRICS_DIR, WX_DISABLE_MLFLOW.
+WX_MAX_STEPS, WX_METRICS_DIR, WX_DISABLE_MLFLOW, WX_INGEST (gpu: parquet -> Arrow buffers -> pinned chunks -> HBM -> cast/pack
+kernel, the default; pandas: the reference's own WeatherDataset on the host).
 """
 from __future__ import annotations
 
@@ -79,8 +80,8 @@ def fit(features: torch.Tensor, labels: torch.Tensor, *, device, rank: int = 0, 
         batch_size: int = 4, max_epochs: int = 10, max_steps: int | None = None, log_every: int = 5,
         parity: bool = False, checkpoint: TopOneCheckpoint | None = None, logger: MetricLogger | None = None,
         sanity_check: bool = True, verbose: bool = True, engine_factory=None) -> dict:
-    """Run the reference's training loop on the GPU.  features fp32 [N,F] / labels int64 [N] are the HOST
-    tensors WeatherDataset produced; they are uploaded once and stay resident."""
+    """Run the reference's training loop on the GPU.  features fp32 [N,F] / labels int64 [N] are what WeatherDataset
+    holds -- host tensors (uploaded once) or tensors already resident on `device` (wxddp.ingest.load_processed)."""
     n, f = features.shape
     torch.manual_seed(SEED)
     tr_idx, va_idx = split_indices(n)                       # consumes the global generator BEFORE model init
@@ -226,14 +227,29 @@ def main() -> int:
                               os.environ.get("WX_METRICS_DIR", os.path.join(os.path.dirname(save_path.rstrip("/")), "mlflow_fallback")),
                               params={}, enabled=os.environ.get("WX_DISABLE_MLFLOW", "0") != "1")
     ckpt = TopOneCheckpoint(save_path) if rank == 0 else None
-    full = WeatherDataset(data_dir)
-    input_dim = full.features.shape[1]
+    if os.environ.get("WX_INGEST", "gpu") == "pandas":
+        full = WeatherDataset(data_dir)                    # the reference's own loader (pandas DataFrame on the host)
+        features, labels = full.features, full.labels
+    else:
+        # same tensors, built on the GPU: Arrow buffers -> pinned chunks -> HBM -> cast + pack kernel (wxddp/ingest.py)
+        from .ingest import load_processed
+        print(f"Loading data from: {os.path.join(data_dir, 'data.parquet')}")
+        try:
+            got = load_processed(data_dir, device=device)
+        except (FileNotFoundError, ValueError):
+            raise
+        except Exception as e:                                                              # :32-33
+            raise RuntimeError(f"Failed to read Parquet file: {e}")
+        features, labels = got["features"], got["labels"]
+        print(f"✓ Loaded {features.shape[0]} rows.")
+        print(f"✓ Training with {len(got['feature_cols'])} features: {got['feature_cols']}")
+    input_dim = features.shape[1]
     if logger is not None and logger.enabled:
         if logger.mlflow is not None:
             logger.mlflow.log_param("input_dim", input_dim)
         else:
             logger._write({"type": "params", "params": {"input_dim": input_dim}})
-    hist = fit(full.features, full.labels, device=device, rank=rank, world=world, dist=dist, batch_size=batch,
+    hist = fit(features, labels, device=device, rank=rank, world=world, dist=dist, batch_size=batch,
                max_epochs=epochs, max_steps=int(max_steps) if max_steps else None, log_every=log_every, parity=parity,
                checkpoint=ckpt, logger=logger)
     if rank == 0:                                                                           # :146-164

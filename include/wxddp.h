@@ -137,6 +137,13 @@ int wx_normalize_pack(wx_ctx* ctx, const void* const* cols, int dtype, const uin
                       int64_t n, const double* stats /* device [F][4] */, int impute_mode,
                       float* features_out, uint32_t* nullmask_out, void* stream);
 
+/* Columnar float64 z-score, the `*_norm` columns as preprocess.py:38-41 writes them to parquet:
+ * out_cols[j][i] = ((double)col_j[i] - mean_j) / std_val_j with IEEE float64 subtraction and division (bit-identical
+ * to the float64 expression Spark evaluates); a clear validity bit gives NaN (SQL null propagates, :38-41).
+ * out_cols: HOST array of F device pointers to double[n]. */
+int wx_zscore_f64(wx_ctx* ctx, const void* const* cols, int dtype, const uint8_t* const* validity,
+                  int64_t n, const double* stats /* device [F][4] */, double* const* out_cols, void* stream);
+
 /* Ascending flat indices (row*F + col) of every null cell recorded in nullmask -- the "imputation
  * indices" of the north star.  idx_out has room for `capacity` entries; *count_out (device) receives
  * the total number of null cells even when it exceeds capacity (then only the first `capacity` are

@@ -155,15 +155,51 @@ def test_etl_front_end_matches_oracle_and_feeds_the_trainer():
     np.testing.assert_array_equal(res["labels32"], want["labels32"])
     np.testing.assert_allclose(res["norm"], want["norm"], rtol=1e-12, atol=1e-12, equal_nan=True)
     np.testing.assert_array_equal(res["nullmask"].cpu().numpy().view(np.uint32), want["nullmask"])
+    # the float64 `*_norm` columns come from wx_zscore_f64: given the SAME statistics they are the oracle's float64
+    # expression (col - mean) / std_val bit for bit (preprocess.py:38-41), nulls included
+    for j in range(5):
+        z = preprocess_ref.zscore(t["raw"][j], res["stats"][j, 1], res["stats"][j, 3])
+        np.testing.assert_array_equal(res["norm"][j].view(np.int64)[~np.isnan(z)], z.view(np.int64)[~np.isnan(z)])
+        np.testing.assert_array_equal(np.isnan(res["norm"][j]), np.isnan(z))
     tmp = tempfile.mkdtemp()
     try:
-        etl.write_parquet_dir(os.path.join(tmp, "data.parquet"), t["names"], res["norm"], res["labels32"])
+        # the Arrow validity bitmaps that came in with the table are the null bitmaps of the written columns
+        etl.write_parquet_dir(os.path.join(tmp, "data.parquet"), t["names"], res["norm"], res["labels32"],
+                              validity=res["validity"])
         ds = WeatherDataset(tmp)
         assert ds.feature_cols == [f"{n}_norm" for n in t["names"]]
         ulp = np.abs(ds.features.numpy().view(np.int32).astype(np.int64) - want["features"].view(np.int32).astype(np.int64))
         ok = ~np.isnan(want["features"])
         assert ulp[ok].max() <= 1 and np.array_equal(np.isnan(ds.features.numpy()), ~ok)
         np.testing.assert_array_equal(ds.labels.numpy(), want["labels"])
+        # the same directory through the GPU ingest path (Arrow buffers -> pinned chunks -> HBM -> cast + pack kernel):
+        # bit-identical to what the reference's pandas/torch casts produce (train_lightning_ddp.py:31,45-46)
+        from wxddp import ingest
+        got = ingest.load_processed(tmp, device=0)
+        assert got["feature_cols"] == ds.feature_cols
+        np.testing.assert_array_equal(got["features"].cpu().numpy().view(np.int32), ds.features.numpy().view(np.int32))
+        np.testing.assert_array_equal(got["labels"].cpu().numpy(), ds.labels.numpy())
+        assert got["info"]["rows"] == 5000 and got["info"]["bytes_h2d"] >= 5000 * (5 * 8 + 4)
+    finally:
+        shutil.rmtree(tmp)
+
+
+def test_ingest_of_a_multi_part_directory_with_unaligned_part_boundaries():
+    """Spark writes several part files; their row counts are not multiples of 8, so the validity bitmaps of consecutive
+    parts do not join on byte boundaries."""
+    from wxddp import ingest
+    from wxddp.module import WeatherDataset
+
+    t = synth.synth_table(5, 10007, 20, null_rate=0.02, const_col=19)
+    pp = preprocess_ref.preprocess_table(t["raw"], t["labels"])
+    tmp = tempfile.mkdtemp()
+    try:
+        preprocess_ref.write_parquet_dir(os.path.join(tmp), t["names"], pp["norm"], pp["labels32"], n_parts=3)
+        ds = WeatherDataset(tmp)
+        got = ingest.load_processed(tmp, device=0)
+        np.testing.assert_array_equal(got["features"].cpu().numpy().view(np.int32), ds.features.numpy().view(np.int32))
+        np.testing.assert_array_equal(got["labels"].cpu().numpy(), ds.labels.numpy())
+        assert got["info"]["files"] == 3
     finally:
         shutil.rmtree(tmp)
 
