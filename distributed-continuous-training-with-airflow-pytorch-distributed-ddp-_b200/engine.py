@@ -197,8 +197,8 @@ class StepEngine:
         """Pipelined form of `step_host`: the H2D copy of THIS batch runs on a copy stream while the previous step's
         kernel runs on the compute stream (two staging slots, event-ordered), and the loss comes back one call late --
         the return value is the loss of the previously submitted step (None on the first call); `drain()` returns the
-        last one.  y_host may be int64 (as WeatherDataset holds it) or int32 (as Spark wrote `label_encoded`,
-        preprocess.py:24): int32 labels cross PCIe as 4 bytes and are widened on the device, which is the cast of
+        last one.  y_host may be int64 (as WeatherDataset holds it), int32 (as Spark wrote `label_encoded`,
+        preprocess.py:24) or uint8 (the same 0/1 codes, one byte per row): narrow labels cross PCIe as they are and are widened on the device, which is the cast of
         train_lightning_ddp.py:46 moved behind the copy.  Same arithmetic and step order as `step_host`; host buffers should be pinned and must stay untouched
         until the next call returns."""
         f, b = cols_host.shape
@@ -208,6 +208,7 @@ class StepEngine:
                 "cols": [torch.empty(f, b, dtype=torch.float32, device=self.device) for _ in range(2)],
                 "y": [torch.empty(b, dtype=torch.int64, device=self.device) for _ in range(2)],
                 "y32": [torch.empty(b, dtype=torch.int32, device=self.device) for _ in range(2)],
+                "y8": [torch.empty(b, dtype=torch.uint8, device=self.device) for _ in range(2)],
                 "ready": [torch.cuda.Event() for _ in range(2)], "free": [torch.cuda.Event() for _ in range(2)],
                 "done": [torch.cuda.Event() for _ in range(2)],
                 "loss": [torch.zeros(1).pin_memory() for _ in range(2)], "pending": None,
@@ -223,6 +224,9 @@ class StepEngine:
             if y_host.dtype == torch.int32:
                 p["y32"][slot].copy_(y_host, non_blocking=True)
                 p["y"][slot].copy_(p["y32"][slot])              # int32 -> int64 on the device (:46)
+            elif y_host.dtype == torch.uint8:                  # the 0/1 codes of preprocess.py:23-25 in one byte each
+                p["y8"][slot].copy_(y_host, non_blocking=True)
+                p["y"][slot].copy_(p["y8"][slot])
             else:
                 p["y"][slot].copy_(y_host, non_blocking=True)
             p["ready"][slot].record(p["copy"])

@@ -242,6 +242,11 @@ def test_host_buffer_steps_sync_and_pipelined_agree():
     got32 = [e32.submit_host(c, l.to(torch.int32).pin_memory()) for c, l in host]
     got32 = [v for v in got32 if v is not None] + [e32.drain()]
     assert got32 == piped
+    e8 = StepEngine(f, device=0, params=p0)                     # one byte per label
+    e8.set_stats(stats)
+    got8 = [e8.submit_host(c, l.to(torch.uint8).pin_memory()) for c, l in host]
+    got8 = [v for v in got8 if v is not None] + [e8.drain()]
+    assert got8 == piped
     assert sync == piped and len(piped) == n_steps
     assert torch.equal(engines[1].params, engines[2].params)
     # device-resident windows of one big table vs per-batch staging buffers: same rows, same kernel
