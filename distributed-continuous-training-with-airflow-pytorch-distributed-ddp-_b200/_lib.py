@@ -46,9 +46,6 @@ SIGNATURES = {
     "wx_launch_count": (_i64, [_vp]),
     "wx_peer_export": (_int, [_vp, _vp]),
     "wx_peer_connect": (_int, [_vp, _int, _int, _vp]),
-    "wx_debug_cta_times": (_int, [_vp, _vp]),
-    "wx_tc_selftest": (_int, [_vp, _vp, _vp, _vp, _int, _vp, _vp, _vp, _vp]),
-    "wx_tc_mma_bench": (_int, [_vp, _int, _int, _int, _vp, _vp]),
     "wx_label_encode": (_int, [_vp, _vp, _vp, _vp, _i64, _vp, _vp, _vp]),
     "wx_col_stats": (_int, [_vp, C.POINTER(_vp), _int, C.POINTER(_vp), _i64, _vp, _vp]),
     "wx_stats_merge": (_int, [_vp, _vp, _int, _vp, _vp]),
@@ -84,6 +81,13 @@ SIGNATURES = {
     "wx_wide_gemm": (_int, [_vp, _int, _int, _vp, _i64, _vp, _i64, _i64, _i64, _i64, _vp, _vp, _vp]),
 }
 
+# developer aids (csrc/wxddp_dev.h): not part of the boundary, bound for scripts/ and the primitives test only
+DEV_SIGNATURES = {
+    "wxdev_cta_times": (_int, [_vp, _vp]),
+    "wxdev_tc_selftest": (_int, [_vp, _vp, _vp, _vp, _int, _vp, _vp, _vp, _vp]),
+    "wxdev_tc_mma_bench": (_int, [_vp, _int, _int, _int, _vp, _vp]),
+}
+
 _lib = None
 
 
@@ -101,7 +105,7 @@ def load() -> C.CDLL:
         raise WxError(f"{path} is missing: build it with `python __graft_entry__.py` (nvcc, sm_100a). "
                       "wxddp has no CPU or PyTorch fallback.")
     lib = C.CDLL(path)
-    for name, (res, args) in SIGNATURES.items():
+    for name, (res, args) in list(SIGNATURES.items()) + list(DEV_SIGNATURES.items()):
         fn = getattr(lib, name)      # AttributeError if the symbol is not exported
         fn.restype = res
         fn.argtypes = args

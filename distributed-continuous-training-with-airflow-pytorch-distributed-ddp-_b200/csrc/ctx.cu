@@ -3,6 +3,7 @@
 #include <string.h>
 
 #include "common.cuh"
+#include "wxddp_dev.h"
 
 static thread_local char g_err[512] = "";
 
@@ -126,7 +127,7 @@ int wx_peer_connect(wx_ctx* ctx, int rank, int world, const void* handles) {
     return WX_OK;
 }
 
-int wx_debug_cta_times(wx_ctx* ctx, long long* device_buf) {
+int wxdev_cta_times(wx_ctx* ctx, long long* device_buf) {
     if (!ctx) return WX_EINVAL;
     ctx->debug_times = device_buf;
     return WX_OK;

@@ -47,7 +47,7 @@ struct GridArgs {
     int64_t* state;
     float* loss_out;
     double* eval_out;       // MODE_EVAL: [2]
-    long long* dbg;         // optional per-CTA timestamps (wx_debug_cta_times)
+    long long* dbg;         // optional per-CTA timestamps (wxdev_cta_times)
     float* probs_out;       // MODE_PREDICT
     wxpeer::PeerArgs peer;  // world > 1: cross-rank sum inside the tail (TAIL_ADAM only)
 };

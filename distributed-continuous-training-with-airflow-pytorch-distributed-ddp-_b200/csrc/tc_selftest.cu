@@ -3,6 +3,7 @@
 //   selftest 1:  Z[128][64]  = Xaug[128][32] * Waug[64][32]^T      (A, B K-major; M=128, N=64, K=32; 3-term tf32 split)
 //   selftest 2:  G[64][32]   = DH[128][64]^T * Xaug[128][32]       (A, B MN-major; M=64, N=32, K=128; 3-term split)
 #include "common.cuh"
+#include "wxddp_dev.h"
 #include "tc_common.cuh"
 
 namespace {
@@ -136,11 +137,11 @@ __global__ void __launch_bounds__(128) tc_selftest_kernel(const float* __restric
 
 }  // namespace
 
-extern "C" int wx_tc_selftest(wx_ctx* ctx, const float* x, const float* w, const float* dh, int terms, float* z, float* g,
+extern "C" int wxdev_tc_selftest(wx_ctx* ctx, const float* x, const float* w, const float* dh, int terms, float* z, float* g,
                               int* status, void* stream) {
-    WX_CHECK_ARG(ctx != nullptr, "wx_tc_selftest: ctx is NULL");
-    WX_CHECK_ARG(x && w && dh && z && g && status, "wx_tc_selftest: NULL pointer");
-    WX_CHECK_ARG((terms >= 1 && terms <= 3) || (terms >= 11 && terms <= 13), "wx_tc_selftest: terms=%d", terms);
+    WX_CHECK_ARG(ctx != nullptr, "wxdev_tc_selftest: ctx is NULL");
+    WX_CHECK_ARG(x && w && dh && z && g && status, "wxdev_tc_selftest: NULL pointer");
+    WX_CHECK_ARG((terms >= 1 && terms <= 3) || (terms >= 11 && terms <= 13), "wxdev_tc_selftest: terms=%d", terms);
     WX_CUDA(cudaSetDevice(ctx->device));
     const int smem = int(sizeof(SelfSmem)) + 1024;
     WX_CUDA(cudaFuncSetAttribute(tc_selftest_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
@@ -245,8 +246,8 @@ __global__ void __launch_bounds__(128) tc_mma_bench_kernel(int variant, int n_di
 }
 }  // namespace
 
-extern "C" int wx_tc_mma_bench(wx_ctx* ctx, int variant, int n_dim, int reps, long long* out, void* stream) {
-    WX_CHECK_ARG(ctx != nullptr && out != nullptr, "wx_tc_mma_bench: NULL argument");
+extern "C" int wxdev_tc_mma_bench(wx_ctx* ctx, int variant, int n_dim, int reps, long long* out, void* stream) {
+    WX_CHECK_ARG(ctx != nullptr && out != nullptr, "wxdev_tc_mma_bench: NULL argument");
     WX_CUDA(cudaSetDevice(ctx->device));
     const int smem = 97 * 1024;
     WX_CUDA(cudaFuncSetAttribute(tc_mma_bench_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));

@@ -11,7 +11,7 @@ st = torch.zeros(2, dtype=torch.int64, device="cuda"); loss = torch.zeros(1, dev
 dbg = torch.zeros(1184 * 4, dtype=torch.int64, device="cuda")
 for i in range(3):
     c.train_step(p, m, v, st, x, y, loss, row0=i * B, batch=B, seed=1)
-c.lib.wx_debug_cta_times(c._h, dbg.data_ptr())
+c.lib.wxdev_cta_times(c._h, dbg.data_ptr())
 c.train_step(p, m, v, st, x, y, loss, row0=3 * B, batch=B, seed=1)
 torch.cuda.synchronize()
 d = dbg.cpu().numpy().reshape(-1, 4)

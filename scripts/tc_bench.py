@@ -18,7 +18,7 @@ print(f"impl={os.environ.get('IMPL','tc')} mode={mode} F={f} B={B}: {ms*1e3:.1f}
 if os.environ.get("CTA_TIMES"):
     import numpy as np
     dbg = torch.zeros(1184 * 4, dtype=torch.int64, device="cuda")
-    c.lib.wx_debug_cta_times(c._h, dbg.data_ptr())
+    c.lib.wxdev_cta_times(c._h, dbg.data_ptr())
     fn(p, m, v, st, x, y, loss, row0=0, batch=B, dropout=mode, seed=3); torch.cuda.synchronize()
     d = dbg.cpu().numpy().reshape(-1, 4); d = d[d[:, 1] > 0]; t0 = d[:, 1].min()
     loop = (d[:, 2] - d[:, 1]) / 1e3; ex = (d[:, 3] - t0) / 1e3
@@ -26,7 +26,7 @@ if os.environ.get("CTA_TIMES"):
           "slowest", [(int(i), int(d[i, 0]), round(float(loop[i]), 1)) for i in np.argsort(loop)[-4:]])
 if os.environ.get("CTA_TIMES"):
     dbg2 = torch.zeros(1184 * 4 + 148 * 2 * 8 + 148 * 8, dtype=torch.int64, device="cuda")
-    c.lib.wx_debug_cta_times(c._h, dbg2.data_ptr())
+    c.lib.wxdev_cta_times(c._h, dbg2.data_ptr())
     fn(p, m, v, st, x, y, loss, row0=0, batch=B, dropout=mode, seed=3); torch.cuda.synchronize()
     ph = dbg2[1184 * 4:1184 * 4 + 148 * 16].cpu().numpy().reshape(148, 2, 8)
     mm = dbg2[1184 * 4 + 148 * 16:].cpu().numpy().reshape(148, 8)

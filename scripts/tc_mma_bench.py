@@ -7,7 +7,7 @@ names = {8: "G1 layout, warp-collective issue (elect.sync)", 9: "G2 layout, warp
 for variant, ns in ((5, (64,)), (8, (64, 32, 128, 256)), (2, (24,)), (9, (24, 8, 64))):
     for n in ns:
         for reps in (64,):
-            c.lib.wx_tc_mma_bench(c._h, variant, n, reps, out.data_ptr(), None); torch.cuda.synchronize()
-            c.lib.wx_tc_mma_bench(c._h, variant, n, reps, out.data_ptr(), None); torch.cuda.synchronize()
+            c.lib.wxdev_tc_mma_bench(c._h, variant, n, reps, out.data_ptr(), None); torch.cuda.synchronize()
+            c.lib.wxdev_tc_mma_bench(c._h, variant, n, reps, out.data_ptr(), None); torch.cuda.synchronize()
             o = out.cpu().tolist()
             print(f"{names[variant]:45s} N={n:3d}: issue {o[0]/(reps*4):7.1f} cyc/MMA, total {o[1]/(reps*4):7.1f} cyc/MMA")

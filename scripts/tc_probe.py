@@ -6,7 +6,7 @@ def run(x, w, dh, terms=1):
     z = torch.full((128, 64), float("nan"), device="cuda"); gg = torch.full((64, 32), float("nan"), device="cuda")
     st = torch.full((1,), -1, dtype=torch.int32, device="cuda")
     xd, wd, dd = x.cuda().contiguous(), w.cuda().contiguous(), dh.cuda().contiguous()
-    rc = c.lib.wx_tc_selftest(c._h, xd.data_ptr(), wd.data_ptr(), dd.data_ptr(), terms, z.data_ptr(), gg.data_ptr(), st.data_ptr(), None)
+    rc = c.lib.wxdev_tc_selftest(c._h, xd.data_ptr(), wd.data_ptr(), dd.data_ptr(), terms, z.data_ptr(), gg.data_ptr(), st.data_ptr(), None)
     torch.cuda.synchronize()
     return z.cpu().numpy(), gg.cpu().numpy(), st.item()
 np.set_printoptions(linewidth=200, precision=3, suppress=True)

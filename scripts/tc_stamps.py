@@ -11,7 +11,7 @@ cols = [cols_t[j] for j in range(f)]; stats = c.col_stats(cols); bound = c.bind_
 p = torch.randn(c.P, device="cuda", generator=g) * 0.2; m = torch.zeros_like(p); v = torch.zeros_like(p)
 st = torch.zeros(2, dtype=torch.int64, device="cuda"); loss = torch.zeros(1, device="cuda")
 dbg = torch.zeros(148 * 8 + 148 * 40, dtype=torch.int64, device="cuda")
-c.lib.wx_debug_cta_times(c._h, dbg.data_ptr())
+c.lib.wxdev_cta_times(c._h, dbg.data_ptr())
 for i in range(6):
     c.tc_train_step_raw(p, m, v, st, bound, stats, y, loss, row0=(i % 2) * B, batch=B, impute=1, dropout=2, seed=3)
 torch.cuda.synchronize()

@@ -144,7 +144,7 @@ def test_tc_selftest_gemms(wx):
     for terms, tol in ((1, 2e-3), (3, 2e-6)):
         z = torch.empty(128, 64, device="cuda"); gg = torch.empty(64, 32, device="cuda")
         st = torch.full((1,), -1, dtype=torch.int32, device="cuda")
-        assert c.lib.wx_tc_selftest(c._h, xd.data_ptr(), wd.data_ptr(), dd.data_ptr(), terms, z.data_ptr(), gg.data_ptr(),
+        assert c.lib.wxdev_tc_selftest(c._h, xd.data_ptr(), wd.data_ptr(), dd.data_ptr(), terms, z.data_ptr(), gg.data_ptr(),
                                     st.data_ptr(), None) == 0
         torch.cuda.synchronize()
         assert st.item() == 0
