@@ -319,3 +319,22 @@ def test_wide_ddp_overlapped_reduce():
     got = torch.from_numpy(r0[2])
     np.testing.assert_allclose(float(got[-1]), float(want[-1]), rtol=1e-4)
     assert float((got[:-1] - want[:-1]).norm() / want[:-1].norm()) < 1e-3 + 1.5 / 512
+
+
+def test_two_contexts_on_two_devices_in_one_process():
+    """The opt-in to large dynamic shared memory is a per-device function attribute: a second context on another GPU of
+    the same process must be able to launch the tensor-core kernels too."""
+    _need(2)
+    import wxddp
+
+    outs = []
+    g = torch.Generator().manual_seed(3)
+    x = torch.randn(4096, 20, generator=g); y = (torch.rand(4096, generator=g) < 0.3).long()
+    p = torch.randn(64 * 20 + 194, generator=g) * 0.2
+    for d in (0, 1):
+        c = wxddp.Context(20, device=d)
+        dev = torch.device("cuda", d)
+        with torch.cuda.device(dev):
+            outs.append(c.tc_mlp_grad(p.to(dev), x.to(dev), y.to(dev), dropout=wxddp.DROPOUT_PHILOX, seed=5, step=1).cpu())
+            assert c.tc_status() == 0
+    np.testing.assert_array_equal(outs[0].numpy(), outs[1].numpy())
