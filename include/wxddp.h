@@ -53,7 +53,8 @@ extern "C" {
 /* dropout source in the training step (train_lightning_ddp.py:60) */
 #define WX_DROPOUT_OFF 0    /* eval semantics */
 #define WX_DROPOUT_MASK 1   /* caller supplies keep bits: uint64 per row, bit j = keep hidden unit j */
-#define WX_DROPOUT_PHILOX 2 /* in-kernel Philox4x32-10 keyed by (seed, step, row); 16-bit thresholds, p_keep = 52429/65536 */
+#define WX_DROPOUT_PHILOX 2 /* in-kernel Philox4x32-10 keyed by (seed, step, row): two calls per row, eight base-5 digits per
+                             * word, keep <=> digit != 0 (p_keep = 0.8); the stream is specified in oracle/philox_ref.py */
 
 typedef struct wx_ctx wx_ctx;
 
@@ -82,12 +83,13 @@ int wx_num_sms(const wx_ctx* ctx);
 int64_t wx_launch_count(const wx_ctx* ctx);
 
 /* ---- multi-GPU: gradient exchange inside the step kernel ------------------------------------------------ */
-/* Replaces DDP's bucket all-reduce and the sync_dist loss reduce (train_lightning_ddp.py:70,:136) for the fused
- * tensor-core steps: after wx_peer_connect, wx_tc_train_step / wx_tc_train_step_raw sum the [P+1] bucket over all
- * ranks INSIDE the kernel's tail (stores into every rank's inbox over NVLink peer memory, flag per rank, ordered sum)
- * and scale by 1/(world*batch).  One process per GPU on one node; every rank must launch the same step.
+/* Replaces DDP's bucket all-reduce and the sync_dist loss reduce (train_lightning_ddp.py:70,:136) for the fused steps:
+ * after wx_peer_connect, wx_tc_train_step / wx_tc_train_step_raw / wx_train_steps_small sum the [P+1] bucket over all
+ * ranks INSIDE the kernel (8-byte {value, tag} words stored into every rank's inbox over NVLink peer memory, ordered sum)
+ * and scale by 1/(world*batch).  One process per GPU on one node; every rank must launch the same steps.
  *   wx_peer_export : allocates this rank's inbox (cudaMalloc, once) and writes its 64-byte CUDA IPC handle to handle_out (host).
- *   wx_peer_connect: handles = host [world][64] bytes gathered from all ranks (any transport, e.g. torch.distributed). */
+ *   wx_peer_connect: handles = host [world][64] bytes gathered from all ranks (any transport, e.g. torch.distributed).
+ * Protocol: export on every rank, gather, connect on every rank, then a BARRIER across the ranks before the first step. */
 int wx_peer_export(wx_ctx* ctx, void* handle_out);
 int wx_peer_connect(wx_ctx* ctx, int rank, int world, const void* handles);
 
@@ -158,7 +160,8 @@ int wx_mlp_grad(wx_ctx* ctx, const float* params, const float* x, const int64_t*
  * loops that cannot take cudaMalloc's implicit synchronisation, or under a no-allocation-after-start policy.
  * The partial-sum scratch is a fixed 1.5 MiB array inside the library image (each GPU that loads the library
  * holds it until the process exits).  Limits: n_features <= 32 and batch <= 16,777,216 rows per call; larger
- * requests are rejected with WX_EINVAL and a message (split the batch and add the outputs -- they are sums).
+ * requests are rejected with WX_EINVAL and a message (split the batch and add the outputs -- they are sums).  The
+ * launch never uses more thread blocks than the array holds partial-sum slabs for, so every in-limit request runs.
  * The first call on a device looks the array's device address up and queries the device; make that first call
  * before starting any stream capture.  The call itself performs no cudaMalloc / cudaFree / allocating library
  * call.  All calls share the one array: two calls whose kernels can overlap on the GPU (different streams,
@@ -168,11 +171,13 @@ int wx_mlp_grad_static(int n_features, const float* params, const float* x, cons
                        const uint64_t* keep_mask, uint64_t seed, uint64_t step, float scale,
                        float* out /* device [P+1] */, void* stream);
 
-/* Tensor-core (tcgen05, kind::tf32 with a 3-term hi/lo split -> fp32-level accuracy) versions of wx_mlp_grad and
- * wx_train_step: same arithmetic contract and outputs (train_lightning_ddp.py:57-71,:88), the two F x 64 contractions
- * run on the 5th-generation tensor cores, rows arrive by TMA bulk copies.  Restrictions: n_features <= 29, contiguous
- * rows only (no row_idx), x + row0*F*4 and y + row0*8 16-byte aligned.  wx_tc_last_status reads a sticky protocol
- * error code (0 = none) that the kernel sets if one of its bounded barrier waits expired. */
+/* Tensor-core (tcgen05, kind::tf32 with hi/lo operand splits -> fp32-level accuracy) versions of wx_mlp_grad and
+ * wx_train_step: same outputs and the same 1e-5 contract (train_lightning_ddp.py:57-71,:88); the two F x 64 contractions
+ * run on the 5th-generation tensor cores with operands and accumulators in tensor memory (csrc/tc_step_kernel.cuh).
+ * Restrictions: n_features <= 31, contiguous rows only (no row_idx), x + row0*F*4 (or every column + row0*4) and
+ * y + row0*8 16-byte aligned.  After wx_peer_connect the train-step forms sum the [P+1] bucket over all ranks inside
+ * the kernel.  wx_tc_last_status reads a sticky protocol error code (0 = none): a bounded barrier wait that expired, or
+ * 20 = a peer did not arrive in the exchange (that step was not applied on this rank). */
 int wx_tc_mlp_grad(wx_ctx* ctx, const float* params, const float* x, const int64_t* y, int64_t row0, int64_t batch,
                    int dropout_mode, const uint64_t* keep_mask, uint64_t seed, uint64_t step, float scale,
                    float* out /* device [P+1] */, void* stream);
@@ -216,7 +221,10 @@ int wx_train_step_raw(wx_ctx* ctx, float* params, float* m, float* v, int64_t* s
  * their own copy of params/m/v in shared memory, exchange per-CTA gradient sums through global memory and cross one grid
  * barrier per step (the latency-bound end of the batch sweep: the per-step launch, parameter reload and last-CTA tail of
  * wx_train_step are gone).  Same arithmetic and dropout stream as wx_train_step.  Measured at F = 20: 5 / 9.5 / 16.6 us per
- * step at batch 8 / 64 / 256 against ~20 us for one launch per step; from ~1024 rows on a launch per step is faster. */
+ * step at batch 8 / 64 / 256 against ~20 us for one launch per step; from ~1024 rows on a launch per step is faster.
+ * After wx_peer_connect (batch <= 64 per rank) every step is a DDP step (:136): the [P+1] sums cross NVLink inside the
+ * step loop, every rank must launch the same n_steps and batch; if a peer stops arriving the launch ends early with
+ * state[0] counting the steps actually applied and status 20 (wx_tc_last_status). */
 #define WX_RESIDENT_MAX_BATCH 16384
 int wx_train_steps_small(wx_ctx* ctx, float* params, float* m, float* v, int64_t* state,
                          const float* x, const int64_t* y, const int64_t* row_idx, int64_t row0,
