@@ -60,16 +60,24 @@ __device__ __forceinline__ bool allreduce_cta(float* vec, int n, const PeerArgs&
     const uint64_t* base = reinterpret_cast<const uint64_t*>(pa.inbox[pa.rank]) + size_t(par) * MAXW * SLOT_FLOATS;
     bool ok = true;
     for (int i = tid; i < n; i += nthreads) {
+        // all W words of this element are requested at once (each load is a ~1 us round trip: one after the other they
+        // cost 17 us at 8 ranks); a word whose tag is not there yet is then polled on its own
+        uint64_t word[MAXW];
+#pragma unroll
+        for (int q = 0; q < MAXW; ++q) word[q] = q < w ? ld_relaxed_sys_u64(base + size_t(q) * SLOT_FLOATS + i) : 0ull;
         float s = 0.0f;
-        for (int q = 0; q < w; ++q) {
-            const uint64_t* src = base + size_t(q) * SLOT_FLOATS + i;
-            uint64_t word = ld_relaxed_sys_u64(src);
-            for (long long spin = 0; uint32_t(word >> 32) != tag && spin < (1ll << 22); ++spin) {
-                __nanosleep(64);
-                word = ld_relaxed_sys_u64(src);
+#pragma unroll
+        for (int q = 0; q < MAXW; ++q) {
+            if (q < w) {
+                const uint64_t* src = base + size_t(q) * SLOT_FLOATS + i;
+                uint64_t wd = word[q];
+                for (long long spin = 0; uint32_t(wd >> 32) != tag && spin < (1ll << 22); ++spin) {
+                    __nanosleep(64);
+                    wd = ld_relaxed_sys_u64(src);
+                }
+                if (uint32_t(wd >> 32) != tag) ok = false;
+                s += __uint_as_float(uint32_t(wd));
             }
-            if (uint32_t(word >> 32) != tag) ok = false;
-            s += __uint_as_float(uint32_t(word));
         }
         vec[i] = s;
     }
