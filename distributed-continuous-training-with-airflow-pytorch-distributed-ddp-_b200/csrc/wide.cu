@@ -44,7 +44,7 @@ struct Layout {
     int64_t P;                    // number of fp32 parameters
     int64_t off_w[8], off_b[8];   // parameter offsets of hidden layer l = 1..L (index l), head at index L+1
     size_t wb[8];                 // workspace byte offsets: bf16 weights of hidden layer l
-    size_t x0, h[8], dz[2], dlog, part, part2, dw1tmp, dwtmp[8], total;
+    size_t x0, h[8], dz[2], dlog, part, part2, dw1tmp, dwtmp[8], cpart[8], total;
 };
 
 size_t align_up(size_t v) { return (v + 1023) & ~size_t(1023); }
@@ -91,6 +91,10 @@ int make_layout(const wx_wide_desc* d, int64_t batch, Layout* L) {
     for (int l = 2; l <= nl; ++l) {   // second split-K slab of dW_l (wave quantisation: see wx_wide_backward_layer)
         L->dwtmp[l] = w;
         w = align_up(w + size_t(H) * H * 4);
+    }
+    for (int l = 1; l < nl; ++l) {    // 32-row column sums of dZ_l written by the dZ product of layer l+1 (bias gradient of l)
+        L->cpart[l] = w;
+        w = align_up(w + size_t((batch + 31) / 32) * H * 4);
     }
     L->total = w;
     return 0;
@@ -741,7 +745,7 @@ int wx_wide_backward_layer(wx_ctx* ctx, const wx_wide_desc* desc, void* ws, int6
                  (long long)batch);
     const int nl = desc->n_hidden;
     WX_CHECK_ARG(layer >= 1 && layer <= nl, "wx_wide_backward_layer: layer=%d outside 1..%d", layer, nl);
-    WX_CHECK_ARG(parts >= 1 && parts <= 31, "wx_wide_backward_layer: parts=%d (bit 0 dW, bit 1 db, bit 2 dZ below, bit 3 fold, bit 4 head dW)", parts);
+    WX_CHECK_ARG(parts >= 1 && parts <= 63, "wx_wide_backward_layer: parts=%d (bit 0 dW, bit 1 db, bit 2 dZ below, bit 3 fold, bit 4 head dW, bit 5 db from the fused partials)", parts);
     WX_CUDA(cudaSetDevice(ctx->device));
     Layout L;
     make_layout(desc, batch, &L);
@@ -812,6 +816,14 @@ int wx_wide_backward_layer(wx_ctx* ctx, const wx_wide_desc* desc, void* ws, int6
         wide_reduce_kernel<<<int((H + 255) / 256), 256, 0, st>>>(part, slabs, H, H, grads + L.off_b[layer]);
         WX_LAUNCH_CHECK(ctx);
     }
+    // db from the 32-row partial column sums that the dZ product of the layer above left behind (no pass over dZ)
+    if (parts & WX_WIDE_DB_FUSED) {
+        WX_CHECK_ARG(layer < nl, "wx_wide_backward_layer: WX_WIDE_DB_FUSED needs a layer below the top hidden layer "
+                     "(its dZ comes from the head kernel, not from a dZ product); use WX_WIDE_DB there");
+        wide_reduce_kernel<<<int((H + 255) / 256), 256, 0, st>>>(reinterpret_cast<const float*>(w + L.cpart[layer]),
+                                                                int((batch + 31) / 32), H, H, grads + L.off_b[layer]);
+        WX_LAUNCH_CHECK(ctx);
+    }
     // dZ_below = (dZ W) * gate(H_below): A = dZ [batch, H] K-major, B = W stored [H(out), H(in)] = [K, N]
     if (layer > 1 && (parts & WX_WIDE_DZ)) {
         GemmArgs g = {};
@@ -820,6 +832,7 @@ int wx_wide_backward_layer(wx_ctx* ctx, const wx_wide_desc* desc, void* ws, int6
         g.gate = reinterpret_cast<const __nv_bfloat16*>(h_below); g.ldg = H;
         g.inv_keep = drop ? 1.0f / (1.0f - desc->dropout_p) : 1.0f;
         g.keep_thresh16 = 65536u;
+        g.colsum_part = reinterpret_cast<float*>(w + L.cpart[layer - 1]);   // db of the layer below, as 32-row partials
         rc = launch_gemm(ctx, true, false, EPI_DX, dz, H, w + L.wb[layer], H, g, st);
         if (rc != WX_OK) return rc;
     }

@@ -50,6 +50,8 @@ struct GemmArgs {
     uint32_t keep_thresh16;   // keep <=> 16 random bits < this; 65536 when dropout is off
     uint32_t seed_lo, seed_hi, step, layer;
     int* err;
+    float* colsum_part;       // EPI_DX only, may be NULL: [ceil(M/32)][N] column sums of each 32-row block of the bf16 OUTPUT
+                              // (the bias gradient of the layer below falls out of the dZ product that writes its dZ)
 };
 
 // ---- Philox4x32-10, 16 bits per element: the wide path's dropout contract (oracle/wide_ref.py: keep_mask) -------------
@@ -145,6 +147,51 @@ __device__ __forceinline__ void epilogue_chunk(float (&v)[16], const GemmArgs& g
                 const bool on = (bits & 0x7FFFu) != 0 && !(bits & 0x8000u);   // gate > 0
                 v[i] = on ? v[i] * g.inv_keep : 0.0f;
             }
+        } else {
+#pragma unroll
+            for (int i = 0; i < 16; ++i) v[i] = 0.0f;
+        }
+        if (g.colsum_part != nullptr) {
+            // column sums over this warp's 32 rows of the values AS STORED (bf16-rounded): one transposing butterfly
+            // (8 + 4 + 2 + 1 + 1 shuffles), after which lanes 2k and 2k+1 hold the total of column k
+            float r[16];
+#pragma unroll
+            for (int i = 0; i < 16; ++i) r[i] = __bfloat162float(__float2bfloat16_rn(v[i]));
+            const int lane = threadIdx.x & 31;
+            float u8[8], u4[4], u2[2];
+            {
+                const bool hi = lane & 16;
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    const float send = hi ? r[i] : r[i + 8];
+                    const float keep = hi ? r[i + 8] : r[i];
+                    u8[i] = keep + __shfl_xor_sync(0xffffffffu, send, 16);
+                }
+            }
+            {
+                const bool hi = lane & 8;
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    const float send = hi ? u8[i] : u8[i + 4];
+                    const float keep = hi ? u8[i + 4] : u8[i];
+                    u4[i] = keep + __shfl_xor_sync(0xffffffffu, send, 8);
+                }
+            }
+            {
+                const bool hi = lane & 4;
+#pragma unroll
+                for (int i = 0; i < 2; ++i) {
+                    const float send = hi ? u4[i] : u4[i + 2];
+                    const float keep = hi ? u4[i + 2] : u4[i];
+                    u2[i] = keep + __shfl_xor_sync(0xffffffffu, send, 4);
+                }
+            }
+            const bool hi2 = lane & 2;
+            float t = (hi2 ? u2[1] : u2[0]) + __shfl_xor_sync(0xffffffffu, hi2 ? u2[0] : u2[1], 2);
+            t += __shfl_xor_sync(0xffffffffu, t, 1);
+            // lane bits 4,3,2,1 selected the upper half at each step: column = 8*b4 + 4*b3 + 2*b2 + b1
+            const int col = ((lane >> 4) & 1) * 8 + ((lane >> 3) & 1) * 4 + ((lane >> 2) & 1) * 2 + ((lane >> 1) & 1);
+            if ((lane & 1) == 0) g.colsum_part[(row >> 5) * g.N + col0 + col] = t;
         }
     } else if (EPI == EPI_PLAIN) {
         if (g.bias) {

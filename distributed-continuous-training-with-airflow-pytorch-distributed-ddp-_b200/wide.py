@@ -158,7 +158,8 @@ class WideEngine:
         db_done = {}
         for layer in range(self.L, 0, -1):
             # side: bias gradient of this layer (dZ_layer is ready: the side stream already waited for its producer)
-            check(lib.wx_wide_backward_layer(h, d, ws, b, layer, dropout, 2, g, sst))
+            # (below the top hidden layer it is a sum of the 32-row partials the dZ product above wrote beside dZ_layer)
+            check(lib.wx_wide_backward_layer(h, d, ws, b, layer, dropout, 2 if layer == self.L else 32, g, sst))
             db_done[layer] = torch.cuda.Event()
             db_done[layer].record(side)
             check(lib.wx_wide_backward_layer(h, d, ws, b, layer, dropout, 1, g, mst))          # dW
