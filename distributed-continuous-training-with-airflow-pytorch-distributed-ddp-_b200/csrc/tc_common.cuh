@@ -73,7 +73,16 @@ __device__ __forceinline__ bool mbar_wait(uint64_t* bar, uint32_t parity) {
     return false;
 }
 
-// Latency-critical variant for the MMA issuers: short sleeps.
+// Tight polling (try_wait itself blocks for a hardware time slice): for roles that own their scheduler slot, e.g. the
+// producer and MMA warps of the wide GEMM.
+__device__ __forceinline__ bool mbar_wait_spin(uint64_t* bar, uint32_t parity) {
+#pragma unroll 1
+    for (uint32_t spin = 0; spin < (1u << 28); ++spin)
+        if (mbar_try_wait(bar, parity)) return true;
+    return false;
+}
+
+// Latency-critical variant for the MMA issuers of the step kernel: short sleeps.
 __device__ __forceinline__ bool mbar_wait_hot(uint64_t* bar, uint32_t parity) { return mbar_wait<32>(bar, parity); }
 
 // generic-proxy writes (st.shared) -> visible to the async proxy (tcgen05.mma / TMA reads of smem)

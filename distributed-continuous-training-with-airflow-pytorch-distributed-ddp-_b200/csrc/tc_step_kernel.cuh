@@ -70,6 +70,7 @@ struct TcSmem {
     float gate[NGROUPS][TILE * 64];              // Gate [k=row][m=64]  MN-major SW128_B32 (GEMM2 A); reused by the final reductions
     float u[NGROUPS][TILE * 64];                 // U    [k=row][n: hi | lo] MN-major SW128_B32 (GEMM2 B); u[0]/u[1] hold the slab / bucket at the end
     float2 w2p[64];                              // ds * (W2[0][j], W2[1][j])
+    __align__(16) float wdl[64];                 // ds * (W2[1][j] - W2[0][j]): the logit DIFFERENCE is all a 2-class softmax needs
     float b2[2];
     __align__(16) float mean_hi[32];             // raw loader: float(mean_c)
     float col_scale[32], col_shift[32];          // epilogue: 1/std_c and (mean_c - float(mean_c)) as floats
@@ -227,6 +228,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_step_kernel(const GridArgs a
         *reinterpret_cast<float*>(reinterpret_cast<unsigned char*>(s.w_hi) + off) = bh;
         *reinterpret_cast<float*>(reinterpret_cast<unsigned char*>(s.w_lo) + off) = bl;
         s.w2p[n] = make_float2(ds * sp[OFF_W2 + n], ds * sp[OFF_W2 + 64 + n]);
+        s.wdl[n] = ds * (sp[OFF_W2 + 64 + n] - sp[OFF_W2 + n]);
     } else if (tid < 96) {
         const int c = tid - 64;
         float mh = 0.0f, sc = 1.0f, sh = 0.0f;
@@ -521,17 +523,27 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_step_kernel(const GridArgs a
 
             // ---- phase A: a = relu(z) where kept (dropout scale folded into W2 and the dlogits), logits, Gate tile.
             //      The TMEM load of the next 16 units is in flight while this chunk is processed. ----
-            float2 lgq[4];                                       // four independent accumulation chains
-#pragma unroll
-            for (int k = 0; k < 4; ++k) lgq[k] = make_float2(0.0f, 0.0f);
-            const float2* __restrict__ w2p = s.w2p;              // read-only here: loads may pass the Gate stores
+            // Only lg1 - lg0 enters a two-class log-softmax, so one FMA per unit against ds (W2[1][j] - W2[0][j]) replaces the
+            // two logit FMAs; the 16 weights of the next chunk are requested before this chunk is processed.
+            float dq[4] = {0.0f, 0.0f, 0.0f, 0.0f};              // four independent accumulation chains
+            const float4* __restrict__ wdl4 = reinterpret_cast<const float4*>(s.wdl);   // read-only here
             float zbuf[2][16];
+            float4 wbuf[2][4];
             tmem_ld16_nc(d1, zbuf[0]);
+#pragma unroll
+            for (int k = 0; k < 4; ++k) wbuf[0][k] = wdl4[k];
 #pragma unroll
             for (int cc = 0; cc < 4; ++cc) {
                 float (&z)[16] = zbuf[cc & 1];
                 tmem_ld_wait_dep(z);
-                if (cc < 3) tmem_ld16_nc(d1 + (cc + 1) * 16, zbuf[(cc + 1) & 1]);
+                if (cc < 3) {
+                    tmem_ld16_nc(d1 + (cc + 1) * 16, zbuf[(cc + 1) & 1]);
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) wbuf[(cc + 1) & 1][k] = wdl4[(cc + 1) * 4 + k];
+                }
+                const float4 (&w4)[4] = wbuf[cc & 1];
+                const float wv[16] = {w4[0].x, w4[0].y, w4[0].z, w4[0].w, w4[1].x, w4[1].y, w4[1].z, w4[1].w,
+                                      w4[2].x, w4[2].y, w4[2].z, w4[2].w, w4[3].x, w4[3].y, w4[3].z, w4[3].w};
                 uint32_t s0 = 0, s1 = 0;
                 if (DROP == DROP_PHILOX) {
                     s0 = pw[2 * cc];
@@ -545,15 +557,14 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_step_kernel(const GridArgs a
                     if (DROP == DROP_MASK) kp = (kb >> q) & 1u;
                     const bool on = kp && !(z[q] <= 0.0f);                 // relu as torch's threshold: NaN passes
                     const float av = on ? z[q] : 0.0f;
-                    const float2 w = w2p[cc * 16 + q];
-                    lgq[q & 3] = __ffma2_rn(make_float2(av, av), w, lgq[q & 3]);
+                    dq[q & 3] = fmaf(av, wv[q], dq[q & 3]);
                     z[q] = av;
                 }
                 tmem_st16_nc(d1 + cc * 16, z);                               // a replaces z in place: phase B reads it back
             }
             WX_TC_PH(3);
-            const float lg0 = ((lgq[0].x + lgq[1].x) + (lgq[2].x + lgq[3].x)) + b2_0;
-            const float lg1 = ((lgq[0].y + lgq[1].y) + (lgq[2].y + lgq[3].y)) + b2_1;
+            const float lg0 = 0.0f;                               // log-softmax is shift-invariant: (0, lg1 - lg0)
+            const float lg1 = ((dq[0] + dq[1]) + (dq[2] + dq[3])) + (b2_1 - b2_0);
             // ---- softmax / loss / dlogits, ATen's operation order ----
             const float mx = fmaxf(lg0, lg1);
             const float e0 = lg0 - mx, e1 = lg1 - mx;

@@ -266,7 +266,7 @@ wide_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                 const int kb0 = split * kb_per, kb1 = (kb0 + kb_per < kb_total) ? kb0 + kb_per : kb_total;
                 for (int kb = kb0; kb < kb1; ++kb, ++it) {
                     const int s = it % STAGES;
-                    if (it >= STAGES && !wxtc::mbar_wait_hot(&empty[s], ((it / STAGES) - 1) & 1)) { ok = false; break; }
+                    if (it >= STAGES && !wxtc::mbar_wait_spin(&empty[s], ((it / STAGES) - 1) & 1)) { ok = false; break; }
                     if (is_a) {
                         wxtc::mbar_arrive_expect_tx(&full[s], A_STAGE_BYTES);
                         unsigned char* a = sA + size_t(s) * A_STAGE_BYTES;
@@ -289,14 +289,14 @@ wide_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             uint32_t it = 0, local = 0;
             for (int64_t tile = blockIdx.x; tile < n_tiles && ok; tile += gridDim.x, ++local) {
                 const uint32_t acc = local & 1;
-                if (local >= 2 && !wxtc::mbar_wait_hot(&tmem_empty[acc], ((local >> 1) - 1) & 1)) { ok = false; break; }
+                if (local >= 2 && !wxtc::mbar_wait_spin(&tmem_empty[acc], ((local >> 1) - 1) & 1)) { ok = false; break; }
                 wxtc::tc_fence_after();
                 const uint32_t d_tmem = tmem_base + acc * BN;
                 const int split = int(tile / mn_tiles);
                 const int kb0 = split * kb_per, kb1 = (kb0 + kb_per < kb_total) ? kb0 + kb_per : kb_total;
                 for (int kb = kb0; kb < kb1; ++kb, ++it) {
                     const int s = it % STAGES;
-                    if (!wxtc::mbar_wait_hot(&full[s], (it / STAGES) & 1)) { ok = false; break; }
+                    if (!wxtc::mbar_wait_spin(&full[s], (it / STAGES) & 1)) { ok = false; break; }
                     wxtc::tc_fence_after();
                     const uint32_t a_addr = wxtc::smem_u32(sA + size_t(s) * A_STAGE_BYTES);
                     const uint32_t b_addr = wxtc::smem_u32(sB + size_t(s) * B_STAGE_BYTES);
