@@ -16,8 +16,10 @@ MAX_FEATURES = 32
 class ModelDesc(C.Structure):
     _fields_ = [("n_features", C.c_int32), ("hidden", C.c_int32), ("classes", C.c_int32),
                 ("dropout_p", C.c_float), ("lr", C.c_double), ("beta1", C.c_double),
-                ("beta2", C.c_double), ("eps", C.c_double)]
+                ("beta2", C.c_double), ("eps", C.c_double), ("optimizer", C.c_int32)]
 
+
+OPT_ADAM, OPT_SGD = 0, 1
 
 class WideDesc(C.Structure):
     _fields_ = [("n_features", C.c_int32), ("hidden", C.c_int32), ("n_hidden", C.c_int32), ("classes", C.c_int32),

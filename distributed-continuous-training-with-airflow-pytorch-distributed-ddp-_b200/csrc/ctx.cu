@@ -31,6 +31,8 @@ int wx_create(int device, const wx_model_desc* desc, wx_ctx** out) {
                  desc->classes, WX_CLASSES);
     WX_CHECK_ARG(desc->dropout_p == 0.0f || desc->dropout_p == 0.2f,
                  "wx_create: dropout_p=%g, only 0.2 (train_lightning_ddp.py:60) and 0 are built", desc->dropout_p);
+    WX_CHECK_ARG(desc->optimizer == WX_OPT_ADAM || desc->optimizer == WX_OPT_SGD, "wx_create: optimizer=%d is neither WX_OPT_ADAM "
+                 "nor WX_OPT_SGD", desc->optimizer);
     WX_CUDA(cudaSetDevice(device));
     cudaDeviceProp prop;
     WX_CUDA(cudaGetDeviceProperties(&prop, device));

@@ -125,7 +125,8 @@ int wx_adam_step(wx_ctx* ctx, float* params, const float* grads, float* m, float
     WX_CUDA(cudaSetDevice(ctx->device));
     const wx_model_desc& d = ctx->desc;
     AdamScalars a;
-    const double bc1 = 1.0 - pow(d.beta1, double(step));
+    a.sgd = d.optimizer == WX_OPT_SGD;
+    const double bc1 = a.sgd ? 1.0 : 1.0 - pow(d.beta1, double(step));
     const double bc2 = 1.0 - pow(d.beta2, double(step));
     a.w_lerp = float(1.0 - d.beta1);
     a.beta2 = float(d.beta2);

@@ -371,12 +371,19 @@ struct AdamScalars {
     float neg_step;     // float(-(lr / bias_correction1))
     float bc2_sqrt;     // float(sqrt(bias_correction2))
     float eps;
+    int sgd;            // WX_OPT_SGD: p += neg_step * g with neg_step = -lr, moments untouched
 };
 
 __device__ __forceinline__ AdamScalars adam_scalars(const wx_model_desc& d, int64_t step /*1-based*/) {
     // torch computes the bias corrections and step size in Python doubles and hands fp32 scalars to
     // the element-wise kernels; same here.
     AdamScalars a;
+    a.sgd = d.optimizer == WX_OPT_SGD;
+    if (a.sgd) {
+        a.w_lerp = a.beta2 = a.one_m_beta2 = a.bc2_sqrt = a.eps = 0.0f;
+        a.neg_step = float(-d.lr);
+        return a;
+    }
     const double b1 = d.beta1, b2 = d.beta2;
     const double bc1 = 1.0 - pow(b1, double(step));
     const double bc2 = 1.0 - pow(b2, double(step));
@@ -390,6 +397,10 @@ __device__ __forceinline__ AdamScalars adam_scalars(const wx_model_desc& d, int6
 }
 
 __device__ __forceinline__ void adam_apply(float& p, float g, float& m, float& v, const AdamScalars& a) {
+    if (a.sgd) {
+        p = fmaf(a.neg_step, g, p);                            // param.add_(grad, alpha=-lr), one rounding like ATen's fused add
+        return;
+    }
     m = fmaf(a.w_lerp, g - m, m);                              // exp_avg.lerp_(grad, 1-beta1)
     v = v * a.beta2;                                           // exp_avg_sq.mul_(beta2)
     v = v + (a.one_m_beta2 * g) * g;                           //   .addcmul_(grad, grad, value=1-beta2)

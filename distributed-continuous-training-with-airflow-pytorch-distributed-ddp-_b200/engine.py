@@ -27,8 +27,8 @@ def init_params_like_reference(n_features: int) -> torch.Tensor:
 class StepEngine:
     def __init__(self, n_features: int, device=0, world: int = 1, rank: int = 0, process_group=None,
                  params: torch.Tensor | None = None, seed: int = 42, lr: float = 0.01, dropout_p: float = 0.2,
-                 use_tc: bool = True):
-        self.ctx = Context(n_features, device=device, dropout_p=dropout_p, lr=lr)
+                 use_tc: bool = True, optimizer: str = "adam"):
+        self.ctx = Context(n_features, device=device, dropout_p=dropout_p, lr=lr, optimizer=optimizer)
         self.device = self.ctx.device
         self.F = n_features
         self.P = n_params(n_features)

@@ -42,7 +42,7 @@ class Context:
     """One per process / GPU (wx_ctx).  Owns scratch only; all tensors stay caller-owned."""
 
     def __init__(self, n_features: int, device: int | torch.device = 0, dropout_p: float = 0.2,
-                 lr: float = 0.01, beta1: float = 0.9, beta2: float = 0.999, eps: float = 1e-8):
+                 lr: float = 0.01, beta1: float = 0.9, beta2: float = 0.999, eps: float = 1e-8, optimizer: str = "adam"):
         self.lib = _lib.load()
         if not torch.cuda.is_available():
             raise WxError("wxddp needs a CUDA device (sm_100a); there is no CPU path")
@@ -53,7 +53,9 @@ class Context:
         torch.cuda.init()
         with torch.cuda.device(dev):
             torch.cuda.current_stream()      # make sure torch's primary context exists before ours attaches
-        desc = ModelDesc(self.n_features, HIDDEN, CLASSES, dropout_p, lr, beta1, beta2, eps)
+        if optimizer not in ("adam", "sgd"):
+            raise WxError(f"optimizer={optimizer!r}: 'adam' (the reference's, train_lightning_ddp.py:88) or 'sgd'")
+        desc = ModelDesc(self.n_features, HIDDEN, CLASSES, dropout_p, lr, beta1, beta2, eps, _lib.OPT_SGD if optimizer == "sgd" else _lib.OPT_ADAM)
         h = C.c_void_p()
         check(self.lib.wx_create(dev.index or 0, C.byref(desc), C.byref(h)))
         self._h = h

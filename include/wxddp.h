@@ -67,7 +67,13 @@ typedef struct wx_model_desc {
     double beta1;       /* 0.9   torch.optim.Adam default used by :88 */
     double beta2;       /* 0.999 */
     double eps;         /* 1e-8 */
+    int32_t optimizer;  /* WX_OPT_ADAM (:88, the reference's) or WX_OPT_SGD */
 } wx_model_desc;
+
+/* update rule applied by wx_adam_step and by the tails of the fused step kernels */
+#define WX_OPT_ADAM 0 /* torch.optim.Adam(lr), single-tensor op order (train_lightning_ddp.py:88) */
+#define WX_OPT_SGD 1  /* p -= lr * g (torch.optim.SGD without momentum); no counterpart in the reference, which only uses Adam --
+                       * the m / v buffers are left untouched, the step counter still advances */
 
 /* ---- library / context --------------------------------------------------------------------- */
 int wx_version(void);               /* 10000*major + 100*minor + patch */

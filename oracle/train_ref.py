@@ -127,6 +127,12 @@ def adam_update(p: torch.Tensor, g: torch.Tensor, m: torch.Tensor, v: torch.Tens
     p.addcdiv_(m, denom, value=-(lr / bc1))
 
 
+def sgd_update(p: torch.Tensor, g: torch.Tensor, lr: float = LR) -> None:
+    """In-place `torch.optim.SGD(lr)` step without momentum: p.add_(g, alpha=-lr).  The reference only uses Adam (:88);
+    this is the oracle of the WX_OPT_SGD extension."""
+    p.add_(g, alpha=-lr)
+
+
 def seeded_setup(n_rows: int, f: int, seed: int = SEED):
     """The RNG-order-sensitive prologue of main(): seed (:14) -> random_split (:117-119) -> model init (:126).
 

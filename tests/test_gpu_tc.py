@@ -267,3 +267,29 @@ def test_tc_raw_steps_track_the_oracle_over_several_steps(wx):
     # +-0.01 (hard part 4), so the parameters are compared as a distribution, not entry by entry
     d = np.abs(p.cpu().numpy() - p_ref.numpy())
     assert np.quantile(d, 0.99) <= 1e-3 and d.max() <= 0.11
+
+
+def test_sgd_update_rule_in_the_fused_steps(wx):
+    """WX_OPT_SGD (no counterpart in the reference, which only uses Adam, :88): p -= lr * g in the tails of both fused
+    step kernels and in wx_adam_step, against the oracle's gradient and torch's SGD arithmetic."""
+    f, n = 20, 8192
+    g = torch.Generator().manual_seed(12)
+    x = torch.randn(n, f, generator=g); y = (torch.rand(n, generator=g) < 0.3).long()
+    c = wx.Context(f, device=0, optimizer="sgd", lr=0.05)
+    p0 = torch.randn(c.P, generator=g) * 0.2
+    _, grad = train_ref.loss_and_grads(p0, f, x, y, None)
+    want = p0.clone()
+    train_ref.sgd_update(want, grad, lr=0.05)
+    xd, yd = x.cuda(), y.cuda()
+    for name, fn in (("tc", c.tc_train_step), ("ffma", c.train_step)):
+        p = p0.cuda(); m = torch.full_like(p, 7.0); v = torch.full_like(p, 9.0)
+        st = torch.zeros(2, dtype=torch.int64, device="cuda"); loss = torch.zeros(1, device="cuda")
+        fn(p, m, v, st, xd, yd, loss, dropout=wx.DROPOUT_OFF)
+        torch.cuda.synchronize()
+        np.testing.assert_allclose(p.cpu().numpy(), want.numpy(), rtol=1e-6, atol=1e-7, err_msg=name)
+        assert st.cpu().tolist() == [1, 0] and bool((m == 7.0).all()) and bool((v == 9.0).all()), name
+    p = p0.cuda()
+    c.adam_step(p, grad.cuda(), torch.zeros_like(p), torch.zeros_like(p), 1, n=c.P)
+    np.testing.assert_allclose(p.cpu().numpy(), want.numpy(), rtol=1e-6, atol=1e-8)
+    assert c.tc_status() == 0
+    c.close()
