@@ -525,10 +525,14 @@ def main() -> int:
         upd = float((0.1 * grads[:P]).norm().item())               # m_new - 0.9 m_old = 0.1 g
         rel = float((m_fused - m).norm().item()) / max(upd, 1e-30)
         ddp_check = {"replicas_identical": bool(identical), "vs_nccl_rel": rel,
+                     "vs_nccl_max_abs": float((m_fused - m).abs().max().item()), "grad_l2": upd / 0.1,
+                     "grad_max_abs": float(grads[:P].abs().max().item()),
                      "loss_fused": loss_fused, "loss_nccl": float(grads[P].item()), "tc_status": tc_status,
                      "what": "params all-gathered after the timed loop and compared bit for bit; then one step from the same "
                              "state through both paths: |m_fused - m_nccl| / |0.1 g| (the fused path standardises raw columns in "
-                             "the kernel, the NCCL path reads the packed table: <= 1 ulp apart per cell)"}
+                             "the kernel, the NCCL path reads the packed table: <= 1 ulp apart per cell; after thousands of "
+                             "steps the mean gradient is a small difference of large per-row terms, so the relative figure is "
+                             "read next to vs_nccl_max_abs and the gradient's own size)"}
         params.copy_(p0); m.copy_(m0); v.copy_(v0); state.copy_(s0)
 
     # ---- e2e: public API with HOST buffers; H2D of the step's raw rows + labels and D2H of the loss inside ----
