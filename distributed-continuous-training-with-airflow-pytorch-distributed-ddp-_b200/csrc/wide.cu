@@ -39,6 +39,7 @@ constexpr int KPAD = 64;          // the first layer's contraction length, zero 
 constexpr int COLSUM_SLABS = 128;
 constexpr int HEAD_SLABS = 128;
 constexpr int MAX_SPLIT_K = 8;
+constexpr int MAX_TAIL_SPLIT = 4;
 
 struct Layout {
     int64_t P;                    // number of fp32 parameters
@@ -88,9 +89,9 @@ int make_layout(const wx_wide_desc* d, int64_t batch, Layout* L) {
     w = align_up(w + size_t(HEAD_SLABS) * 2 * H * 4);
     L->dw1tmp = w;
     w = align_up(w + size_t(MAX_SPLIT_K) * H * KPAD * 4);
-    for (int l = 2; l <= nl; ++l) {   // second split-K slab of dW_l (wave quantisation: see wx_wide_backward_layer)
+    for (int l = 2; l <= nl; ++l) {   // K-range slabs 1..3 of dW_l's tail tiles (wave quantisation: see plan_dw)
         L->dwtmp[l] = w;
-        w = align_up(w + size_t(H) * H * 4);
+        w = align_up(w + size_t(MAX_TAIL_SPLIT - 1) * H * H * 4);
     }
     for (int l = 1; l < nl; ++l) {    // 32-row column sums of dZ_l written by the dZ product of layer l+1 (bias gradient of l)
         L->cpart[l] = w;
@@ -313,13 +314,22 @@ __global__ void __launch_bounds__(256) wide_colsum_kernel(const __nv_bfloat16* _
     for (int i = 0; i < 8; ++i) p[c8 * 8 + i] = a[i];
 }
 
-// dst[i] += src[i] (second split-K slab of a weight gradient)
-__global__ void __launch_bounds__(256) wide_add_kernel(float* __restrict__ dst, const float* __restrict__ src, int64_t n4) {
-    for (int64_t i = int64_t(blockIdx.x) * blockDim.x + threadIdx.x; i < n4; i += int64_t(gridDim.x) * blockDim.x) {
-        float4 a = reinterpret_cast<float4*>(dst)[i];
-        const float4 b = __ldg(reinterpret_cast<const float4*>(src) + i);
-        a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w;
-        reinterpret_cast<float4*>(dst)[i] = a;
+// Tail tiles of a weight gradient (GemmArgs::tail_*): out += slab_1 + ... + slab_{n-1}, in that order, over the tiles
+// [tail_first, tail_first + gridDim.y) only.  grid (tile_rows * tile_cols / 4 / 256 / 4, tail tiles), 4 float4 per thread.
+__global__ void __launch_bounds__(256) wide_tail_fold_kernel(float* __restrict__ out, int64_t ldo, const float* __restrict__ slabs,
+                                                            int64_t slab_stride, int n_slabs, int64_t tail_first, int tiles_n,
+                                                            int tile_rows, int tile_cols) {
+    const int64_t mn = tail_first + blockIdx.y;
+    const int64_t m0 = (mn / tiles_n) * tile_rows, n0 = (mn % tiles_n) * tile_cols;
+    const int c4 = tile_cols / 4;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < tile_rows * c4; i += gridDim.x * blockDim.x) {
+        const int64_t off = (m0 + i / c4) * ldo + n0 + (i % c4) * 4;
+        float4 a = *reinterpret_cast<const float4*>(out + off);
+        for (int s = 0; s < n_slabs; ++s) {
+            const float4 b = __ldg(reinterpret_cast<const float4*>(slabs + s * slab_stride + off));
+            a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w;
+        }
+        *reinterpret_cast<float4*>(out + off) = a;
     }
 }
 
@@ -476,16 +486,18 @@ int launch_gemm_t(wx_ctx* ctx, const CUtensorMap& ta, const CUtensorMap& tb, con
     return WX_OK;
 }
 
-// two-SM kernel: clusters of 2 CTAs, 256 x 256 tiles (wide_gemm2.cuh)
-template <bool A_K, bool B_K, int EPI>
-int launch_gemm2_t(wx_ctx* ctx, const CUtensorMap& ta, const CUtensorMap& tb, const GemmArgs& g, cudaStream_t st) {
+// two-SM kernel: clusters of 2 CTAs, 256 x 256 (NB = 1) or 256 x 512 (NB = 2) tiles (wide_gemm2.cuh)
+template <bool A_K, bool B_K, int EPI, int NB>
+int launch_gemm2_nb(wx_ctx* ctx, const CUtensorMap& ta, const CUtensorMap& tb, const GemmArgs& g, cudaStream_t st) {
     static bool attr_set[64] = {};
+    constexpr size_t GEMM2_SMEM = gemm2_smem(NB);
     if (!attr_set[ctx->device & 63]) {
-        WX_CUDA(cudaFuncSetAttribute(wide_gemm2_kernel<A_K, B_K, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        WX_CUDA(cudaFuncSetAttribute(wide_gemm2_kernel<A_K, B_K, EPI, NB>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                      int(GEMM2_SMEM)));
         attr_set[ctx->device & 63] = true;
     }
-    const int64_t tiles = (g.M / (2 * BM)) * (g.N / BN) * g.split_k;
+    const int64_t mn_tiles = (g.M / (2 * BM)) * (g.N / (NB * BN));
+    const int64_t tiles = g.tail_split > 1 ? g.tail_first + (mn_tiles - g.tail_first) * g.tail_split : mn_tiles * g.split_k;
     const int64_t pairs = (ctx->num_sms - ctx->wide_reserved_sms) / 2;
     const int64_t clusters = tiles < pairs ? tiles : pairs;
     cudaLaunchConfig_t cfg = {};
@@ -500,9 +512,37 @@ int launch_gemm2_t(wx_ctx* ctx, const CUtensorMap& ta, const CUtensorMap& tb, co
     attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    WX_CUDA(cudaLaunchKernelEx(&cfg, wide_gemm2_kernel<A_K, B_K, EPI>, ta, tb, g));
+    WX_CUDA(cudaLaunchKernelEx(&cfg, wide_gemm2_kernel<A_K, B_K, EPI, NB>, ta, tb, g));
     WX_LAUNCH_CHECK(ctx);
     return WX_OK;
+}
+
+int forced_tile_nb() {
+    static int forced = -1;
+    if (forced < 0) {
+        const char* e = getenv("WX_WIDE_NB");         // developer switch for A/B timing of the two tile widths
+        forced = (e != nullptr && (e[0] == '1' || e[0] == '2')) ? e[0] - '0' : 0;
+    }
+    return forced;
+}
+
+// Tile width of the two-SM kernel.  The 256 x 512 tile moves a quarter less data per FLOP through L2 and shared memory
+// (the narrow tile asks the L2 for more than it delivers at the tensor pipe's full rate), but its accumulator takes all of
+// TMEM, so a tile's epilogue is not hidden behind the next tile's MMAs -- which is why the epilogue warps do everything
+// that does not need the accumulator (dropout bits, gate bits) while the MMAs run.  Wide when there are at least two
+// wide tiles per SM pair.
+int wide_tile_nb(const wx_ctx* ctx, const GemmArgs& g, int epi) {
+    const bool fits = g.N % (2 * BN) == 0;
+    if (g.nb) return (g.nb == 2 && fits) ? 2 : 1;
+    if (forced_tile_nb()) return (forced_tile_nb() == 2 && fits) ? 2 : 1;
+    const int64_t tiles2 = (g.M / (2 * BM)) * (g.N / (2 * BN)) * g.split_k, pairs = ctx->num_sms / 2;
+    return (fits && tiles2 >= 2 * pairs) ? 2 : 1;
+}
+
+template <bool A_K, bool B_K, int EPI>
+int launch_gemm2_t(wx_ctx* ctx, const CUtensorMap& ta, const CUtensorMap& tb, const GemmArgs& g, cudaStream_t st) {
+    if (wide_tile_nb(ctx, g, EPI) == 2) return launch_gemm2_nb<A_K, B_K, EPI, 2>(ctx, ta, tb, g, st);
+    return launch_gemm2_nb<A_K, B_K, EPI, 1>(ctx, ta, tb, g, st);
 }
 
 bool two_sm_enabled() {
@@ -562,16 +602,44 @@ int launch_gemm(wx_ctx* ctx, bool a_k, bool b_k, int epi, const void* A, int64_t
     return WX_EINVAL;
 }
 
-// Number of split-K slabs of dW_layer.  (H/256)^2 tile pairs rarely fill the SM pairs evenly (256 tiles on 74 pairs = 3.46
-// rounds at H = 4096): when the last round would be less than ~80 % full the batch is cut in two -- slab 0 is the gradient
-// itself, slab 1 a workspace buffer that WX_WIDE_DW_FOLD adds in (a separate piece so it can run off the GEMM stream).
-int dw_splits(const wx_ctx* ctx, const wx_wide_desc* d, int64_t batch, int layer) {
-    if (layer <= 1 || !two_sm_enabled()) return 1;
-    const int64_t H = d->hidden;
-    const int64_t tiles = (H / (2 * BM)) * (H / BN), pairs = ctx->num_sms / 2;   // NOT the reserved count: DW and FOLD calls must agree
-    if (pairs < 1 || tiles < pairs || batch < 1024) return 1;
-    const double rounds = double(tiles) / double(pairs);
-    return (ceil(rounds) - rounds) > 0.2 ? 2 : 1;
+// How the weight-gradient product dW_layer = dZ^T H_below (hidden x hidden, K = batch) is cut into work units.
+// (H/256)^2 tile pairs rarely fill the SM pairs evenly (256 tiles on 74 pairs = 3.46 rounds at H = 4096; 128 tiles of
+// 256 x 512 = 1.73).  The whole rounds run as whole tiles; the tiles of the last, partly filled round are cut into 2 or 4
+// ranges of the batch, range 0 accumulating into the gradient itself and ranges 1.. into workspace slabs that
+// WX_WIDE_DW_FOLD adds in (a separate piece so it can run off the GEMM stream): 54 tiles x 4 ranges = 216 units = 2.92 short
+// rounds instead of one long one.  Depends on the device's SM count only (NOT the reserved count: the DW and FOLD calls
+// must agree).
+struct DwPlan {
+    int nb;               // tile width (1: 256 x 256, 2: 256 x 512); 0 = not the two-SM kernel's business
+    int tail_split;       // 1 = no split
+    int64_t tail_first;   // first split tile
+    int64_t tail_tiles;   // number of split tiles
+};
+
+DwPlan plan_dw(const wx_ctx* ctx, const wx_wide_desc* d, int64_t batch, int layer) {
+    DwPlan p = {0, 1, 0, 0};
+    if (layer <= 1 || !two_sm_enabled()) return p;
+    const int64_t H = d->hidden, pairs = ctx->num_sms / 2;
+    p.nb = (H % (2 * BN) == 0 && forced_tile_nb() != 1) ? 2 : 1;
+    if (forced_tile_nb() == 0 && (H / (2 * BM)) * (H / (2 * BN)) * 2 < pairs) p.nb = 1;
+    const int64_t tiles = (H / (2 * BM)) * (H / (p.nb * BN));
+    if (pairs < 1 || batch < 1024) return p;
+    const int64_t rest = tiles % pairs;
+    if (rest == 0) return p;
+    double best = 1.0;
+    for (int ts = 2; ts <= MAX_TAIL_SPLIT; ts *= 2) {
+        if (batch / BK / ts < 8) break;                       // at least 8 K blocks per range
+        const double rounds = double((rest * ts + pairs - 1) / pairs) / ts;
+        if (rounds < best - 1e-9) {
+            best = rounds;
+            p.tail_split = ts;
+        }
+    }
+    if (p.tail_split > 1) {
+        p.tail_first = tiles - rest;
+        p.tail_tiles = rest;
+    }
+    return p;
 }
 
 AdamS adam_consts(const wx_wide_desc* d, int64_t step) {
@@ -784,13 +852,13 @@ int wx_wide_backward_layer(wx_ctx* ctx, const wx_wide_desc* desc, void* ws, int6
             g.out = w + L.dw1tmp; g.ldo = KPAD;
         } else {
             g.out = grads + L.off_w[layer]; g.ldo = H;
-            // (H/256)^2 tile pairs rarely fill the 74 SM pairs evenly (256 tiles = 3.46 rounds at H = 4096): when the last
-            // round would be less than ~80 % full, cut the batch in two -- slab 0 is the gradient itself, slab 1 a workspace
-            // buffer that WX_WIDE_DW_FOLD adds in (kept separate so the caller can run it off the GEMM stream)
-            splits = dw_splits(ctx, desc, batch, layer);
-            if (splits == 2) {
-                g.split_k = 2;
-                g.split_stride = (reinterpret_cast<float*>(w + L.dwtmp[layer]) - (grads + L.off_w[layer]));
+            const DwPlan pl = plan_dw(ctx, desc, batch, layer);
+            g.nb = pl.nb;
+            if (pl.tail_split > 1) {
+                g.tail_split = pl.tail_split;
+                g.tail_first = pl.tail_first;
+                g.tail_off = reinterpret_cast<float*>(w + L.dwtmp[layer]) - (grads + L.off_w[layer]);
+                g.tail_stride = H * H;
             }
         }
         rc = launch_gemm(ctx, false, false, EPI_DW, dz, H, h_below, in, g, st);
@@ -801,10 +869,16 @@ int wx_wide_backward_layer(wx_ctx* ctx, const wx_wide_desc* desc, void* ws, int6
             WX_LAUNCH_CHECK(ctx);
         }
     }
-    if ((parts & WX_WIDE_DW_FOLD) && dw_splits(ctx, desc, batch, layer) == 2) {
-        wide_add_kernel<<<grid_for(ctx, H * H, 4), 256, 0, st>>>(grads + L.off_w[layer],
-                                                                reinterpret_cast<const float*>(w + L.dwtmp[layer]), H * H / 4);
-        WX_LAUNCH_CHECK(ctx);
+    if (parts & WX_WIDE_DW_FOLD) {
+        const DwPlan pl = plan_dw(ctx, desc, batch, layer);
+        if (pl.tail_split > 1) {
+            const int tile_cols = pl.nb * BN;
+            dim3 fg(unsigned(2 * BM * tile_cols / 4 / 256 / 4), unsigned(pl.tail_tiles));
+            wide_tail_fold_kernel<<<fg, 256, 0, st>>>(grads + L.off_w[layer], H, reinterpret_cast<const float*>(w + L.dwtmp[layer]),
+                                                     H * H, pl.tail_split - 1, pl.tail_first, int(H / tile_cols), 2 * BM,
+                                                     tile_cols);
+            WX_LAUNCH_CHECK(ctx);
+        }
     }
     // db = column sums of dZ
     if (parts & WX_WIDE_DB) {

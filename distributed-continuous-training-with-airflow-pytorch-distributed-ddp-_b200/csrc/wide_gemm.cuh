@@ -50,6 +50,12 @@ struct GemmArgs {
     uint32_t keep_thresh16;   // keep <=> 16 random bits < this; 65536 when dropout is off
     uint32_t seed_lo, seed_hi, step, layer;
     int* err;
+    int nb;                   // two-SM kernel: 0 = pick the tile width, 1 = 256 x 256, 2 = 256 x 512
+    // Tail split (two-SM kernel, split_k == 1, fp32 output): output tiles [0, tail_first) are whole work units, every later
+    // tile is cut into tail_split ranges of K -- range 0 goes to `out`, range s >= 1 to out + tail_off + (s-1) * tail_stride
+    // -- so that the last, partly filled round of tiles is spread over all SM pairs.  tail_split <= 1: off.
+    int tail_split;
+    int64_t tail_first, tail_off, tail_stride;
     float* colsum_part;       // EPI_DX only, may be NULL: [ceil(M/32)][N] column sums of each 32-row block of the bf16 OUTPUT
                               // (the bias gradient of the layer below falls out of the dZ product that writes its dZ)
 };
@@ -111,10 +117,11 @@ __device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
     return *reinterpret_cast<uint32_t*>(&v);
 }
 
-// Fused pointwise work + store of one 16-column chunk of an accumulator row (shared by the 1-CTA and 2-CTA kernels).
+// Fused pointwise work on one 16-column chunk of an accumulator row (shared by the 1-CTA and 2-CTA kernels).  gw: the 16
+// bf16 gate values of this row and chunk (EPI_DX only).
 template <int EPI>
-__device__ __forceinline__ void epilogue_chunk(float (&v)[16], const GemmArgs& g, int64_t row, bool row_ok, int64_t col0,
-                                               int64_t out_off) {
+__device__ __forceinline__ void epilogue_math(float (&v)[16], const GemmArgs& g, int64_t row, bool row_ok, int64_t col0,
+                                              const uint32_t (&gw)[8]) {
     if (EPI == EPI_FWD) {
         uint32_t keep = 0xFFFFu;
         if (g.keep_thresh16 < 65536u) {
@@ -138,9 +145,6 @@ __device__ __forceinline__ void epilogue_chunk(float (&v)[16], const GemmArgs& g
         }
     } else if (EPI == EPI_DX) {
         if (row_ok) {
-            const uint4* gp = reinterpret_cast<const uint4*>(g.gate + row * g.ldg + col0);
-            const uint4 g0 = __ldg(gp), g1 = __ldg(gp + 1);
-            const uint32_t gw[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
 #pragma unroll
             for (int i = 0; i < 16; ++i) {
                 const uint32_t bits = (gw[i >> 1] >> (16 * (i & 1))) & 0xFFFFu;
@@ -199,6 +203,20 @@ __device__ __forceinline__ void epilogue_chunk(float (&v)[16], const GemmArgs& g
             for (int i = 0; i < 16; ++i) v[i] += __ldg(g.bias + col0 + i);
         }
     }
+}
+
+// epilogue_math + the store, straight from registers: every lane writes 32 or 64 bytes of its own row (the 1-CTA kernel)
+template <int EPI>
+__device__ __forceinline__ void epilogue_chunk(float (&v)[16], const GemmArgs& g, int64_t row, bool row_ok, int64_t col0,
+                                               int64_t out_off) {
+    uint32_t gw[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    if (EPI == EPI_DX && row_ok) {
+        const uint4* gp = reinterpret_cast<const uint4*>(g.gate + row * g.ldg + col0);
+        const uint4 g0 = __ldg(gp), g1 = __ldg(gp + 1);
+        gw[0] = g0.x; gw[1] = g0.y; gw[2] = g0.z; gw[3] = g0.w;
+        gw[4] = g1.x; gw[5] = g1.y; gw[6] = g1.z; gw[7] = g1.w;
+    }
+    epilogue_math<EPI>(v, g, row, row_ok, col0, gw);
     if (row_ok) {
         if (EPI == EPI_FWD || EPI == EPI_DX) {
             __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(g.out) + row * g.ldo + col0;

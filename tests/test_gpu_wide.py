@@ -26,10 +26,12 @@ def eng():
 
 
 @pytest.mark.parametrize("m,n,k", [(128, 256, 64), (256, 512, 128), (384, 256, 320), (128, 768, 512), (4096, 64, 384),
-                                   (200, 48, 64), (512, 512, 256), (256, 768, 1024), (1024, 256, 64)])
+                                   (200, 48, 64), (512, 512, 256), (256, 768, 1024), (1024, 256, 64),
+                                   (4096, 5120, 192), (2560, 9728, 64)])
 def test_gemm_three_operand_layouts(eng, m, n, k):
-    """M % 256 == 0 and N % 256 == 0 take the two-SM kernel (cta_group::2, 256 x 256 tiles per CTA pair), everything
-    else the one-CTA kernel; both must agree with a float32 matmul of the same bf16 operands."""
+    """M % 256 == 0 and N % 256 == 0 take the two-SM kernel (cta_group::2, 256 x 256 tiles per CTA pair; 256 x 512 when
+    N % 512 == 0 and there are at least two such tiles per SM pair -- the last two shapes), everything else the one-CTA
+    kernel; all must agree with a float32 matmul of the same bf16 operands."""
     torch.manual_seed(m + n + k)
     a = torch.randn(m, k, device="cuda").bfloat16()
     b = torch.randn(n, k, device="cuda").bfloat16()
@@ -79,11 +81,12 @@ def test_step_gradients_match_oracle(eng, dropout, batch):
 
 
 def test_split_k_weight_gradient_at_large_hidden():
-    """hidden 2560 -> 100 tile pairs on 74 SM pairs: the dW products are cut in two along the batch and folded on the side
-    stream; the result must still match the oracle (and be reproducible bit for bit)."""
+    """hidden 2560 -> 50 tiles of 256 x 512 on 74 SM pairs: the dW product's tiles are cut into four ranges of the batch
+    (200 units = 2.7 short rounds), ranges 1..3 land in workspace slabs and are folded in on the side stream; the result
+    must still match the oracle (and be reproducible bit for bit)."""
     from wxddp.wide import WideEngine
 
-    f, h, nl, b = 20, 2560, 2, 1024
+    f, h, nl, b = 20, 2560, 2, 2048
     torch.manual_seed(11)
     e = WideEngine(f, h, nl, max_batch=b, device=0)
     x = torch.randn(b, f)
@@ -92,6 +95,26 @@ def test_split_k_weight_gradient_at_large_hidden():
     again = e.loss_and_grads(x.cuda(), y.cuda(), dropout=2, step=2).clone()
     assert torch.equal(got, again) and e.status() == 0
     want = wide_ref.loss_and_grads(e.params.cpu(), x, y, f, h, nl, dropout=True, seed=e.seed, step=2)
+    got = got.cpu()
+    np.testing.assert_allclose(float(got[-1]), float(want[-1]), rtol=1e-4)
+    for lo, hi in e.slices + [(e.head_slice[0], e.P)]:
+        assert rel(got[lo:hi], want[lo:hi]) < 1e-3 + 1.5 / b, (lo, hi)
+
+
+def test_step_through_the_512_wide_tiles():
+    """batch 18,944 x hidden 1024: the forward and dZ products have 148 tiles of 256 x 512 (two per SM pair) and take the
+    wide-tile kernel with its fused epilogues (bias + ReLU + dropout; gate + 32-row column sums); same bars as above."""
+    from wxddp.wide import WideEngine
+
+    f, h, nl, b = 20, 1024, 3, 18944
+    torch.manual_seed(5)
+    e = WideEngine(f, h, nl, max_batch=b, device=0)
+    x = torch.randn(b, f)
+    y = (torch.rand(b) < 0.3).long()
+    got = e.loss_and_grads(x.cuda(), y.cuda(), dropout=2, step=3).clone()
+    again = e.loss_and_grads(x.cuda(), y.cuda(), dropout=2, step=3).clone()
+    assert torch.equal(got, again) and e.status() == 0
+    want = wide_ref.loss_and_grads(e.params.cpu(), x, y, f, h, nl, dropout=True, seed=e.seed, step=3)
     got = got.cpu()
     np.testing.assert_allclose(float(got[-1]), float(want[-1]), rtol=1e-4)
     for lo, hi in e.slices + [(e.head_slice[0], e.P)]:
