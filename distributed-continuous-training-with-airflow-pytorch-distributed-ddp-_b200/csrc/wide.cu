@@ -487,12 +487,12 @@ int launch_gemm_t(wx_ctx* ctx, const CUtensorMap& ta, const CUtensorMap& tb, con
 }
 
 // two-SM kernel: clusters of 2 CTAs, 256 x 256 (NB = 1) or 256 x 512 (NB = 2) tiles (wide_gemm2.cuh)
-template <bool A_K, bool B_K, int EPI, int NB>
+template <bool A_K, bool B_K, int EPI, int NB, int EW = 8>
 int launch_gemm2_nb(wx_ctx* ctx, const CUtensorMap& ta, const CUtensorMap& tb, const GemmArgs& g, cudaStream_t st) {
     static bool attr_set[64] = {};
-    constexpr size_t GEMM2_SMEM = gemm2_smem(NB);
+    constexpr size_t GEMM2_SMEM = gemm2_smem(NB, EW);
     if (!attr_set[ctx->device & 63]) {
-        WX_CUDA(cudaFuncSetAttribute(wide_gemm2_kernel<A_K, B_K, EPI, NB>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        WX_CUDA(cudaFuncSetAttribute(wide_gemm2_kernel<A_K, B_K, EPI, NB, EW>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                      int(GEMM2_SMEM)));
         attr_set[ctx->device & 63] = true;
     }
@@ -502,7 +502,7 @@ int launch_gemm2_nb(wx_ctx* ctx, const CUtensorMap& ta, const CUtensorMap& tb, c
     const int64_t clusters = tiles < pairs ? tiles : pairs;
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(unsigned(clusters * 2));
-    cfg.blockDim = dim3(GEMM_THREADS);
+    cfg.blockDim = dim3(gemm2_threads(EW));
     cfg.dynamicSmemBytes = GEMM2_SMEM;
     cfg.stream = st;
     cudaLaunchAttribute attr[1];
@@ -512,9 +512,18 @@ int launch_gemm2_nb(wx_ctx* ctx, const CUtensorMap& ta, const CUtensorMap& tb, c
     attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    WX_CUDA(cudaLaunchKernelEx(&cfg, wide_gemm2_kernel<A_K, B_K, EPI, NB>, ta, tb, g));
+    WX_CUDA(cudaLaunchKernelEx(&cfg, wide_gemm2_kernel<A_K, B_K, EPI, NB, EW>, ta, tb, g));
     WX_LAUNCH_CHECK(ctx);
     return WX_OK;
+}
+
+bool short_k_wide_epilogue() {
+    static int v = -1;
+    if (v < 0) {
+        const char* e = getenv("WX_WIDE_EW8");        // developer switch: keep 8 epilogue warps for the short-K product
+        v = (e != nullptr && e[0] == '1') ? 0 : 1;
+    }
+    return v == 1;
 }
 
 int forced_tile_nb() {
@@ -541,6 +550,10 @@ int wide_tile_nb(const wx_ctx* ctx, const GemmArgs& g, int epi) {
 
 template <bool A_K, bool B_K, int EPI>
 int launch_gemm2_t(wx_ctx* ctx, const CUtensorMap& ta, const CUtensorMap& tb, const GemmArgs& g, cudaStream_t st) {
+    // the first layer's forward product (K = one 64-deep block) is all epilogue: twice the epilogue warps
+    if constexpr (EPI == EPI_FWD && A_K && B_K) {
+        if (g.K <= 2 * BK && short_k_wide_epilogue()) return launch_gemm2_nb<true, true, EPI_FWD, 1, 16>(ctx, ta, tb, g, st);
+    }
     if (wide_tile_nb(ctx, g, EPI) == 2) return launch_gemm2_nb<A_K, B_K, EPI, 2>(ctx, ta, tb, g, st);
     return launch_gemm2_nb<A_K, B_K, EPI, 1>(ctx, ta, tb, g, st);
 }

@@ -24,11 +24,14 @@
 namespace wxwide {
 
 constexpr int B2_STAGE_BYTES = (BN / 2) * BK * 2;   // 16 KiB: this CTA's half of one 256-column B block
-__host__ __device__ constexpr int gemm2_stages(int nb) { return nb == 1 ? 6 : 4; }
 constexpr int EPI_STAGE_BYTES = 32 * 128;            // per epilogue warp: 32 rows x 128 bytes of output, 16-byte units XOR-swizzled
-__host__ __device__ constexpr size_t gemm2_smem(int nb) {
-    return size_t(gemm2_stages(nb)) * (A_STAGE_BYTES + nb * B2_STAGE_BYTES) + size_t(EPI_WARPS) * EPI_STAGE_BYTES + 1024;
+// EW = epilogue warps per CTA: 8 for the long products; 16 (and a shallower ring) for products whose contraction is a
+// K block or two, where the kernel is bound by the epilogue's instructions, not by the MMAs.
+__host__ __device__ constexpr int gemm2_stages(int nb, int ew) { return ew > 8 ? 4 : (nb == 1 ? 6 : 4); }
+__host__ __device__ constexpr size_t gemm2_smem(int nb, int ew) {
+    return size_t(gemm2_stages(nb, ew)) * (A_STAGE_BYTES + nb * B2_STAGE_BYTES) + size_t(ew) * EPI_STAGE_BYTES + 1024;
 }
+__host__ __device__ constexpr int gemm2_threads(int ew) { return (3 + ew) * 32; }
 __device__ __forceinline__ uint32_t epi_unit_addr(uint32_t base, int row, int unit) {
     return base + uint32_t(row) * 128u + (uint32_t(unit ^ (row & 7)) << 4);
 }
@@ -93,12 +96,12 @@ __device__ __forceinline__ void tmem2_dealloc(uint32_t taddr, uint32_t ncols) {
     asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
 }
 
-template <bool A_K, bool B_K, int EPI, int NB>
-__global__ void __launch_bounds__(GEMM_THREADS, 1)
+template <bool A_K, bool B_K, int EPI, int NB, int EW>
+__global__ void __launch_bounds__(gemm2_threads(EW), 1)
 wide_gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const GemmArgs g) {
     extern __shared__ unsigned char wide_smem_raw[];
     unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(wide_smem_raw) + 1023) & ~uintptr_t(1023));
-    constexpr int STAGES2 = gemm2_stages(NB);
+    constexpr int STAGES2 = gemm2_stages(NB, EW);
     constexpr int BNT = NB * BN;                              // tile width
     constexpr int BT_STAGE_BYTES = NB * B2_STAGE_BYTES;
     constexpr uint32_t NACC = 2 / NB;                         // accumulator buffers that fit in 512 TMEM columns
@@ -148,7 +151,7 @@ wide_gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
         }
         for (int a = 0; a < 2; ++a) {
             wxtc::mbar_init(&tmem_full[a], 1);
-            wxtc::mbar_init(&tmem_empty[a], 2 * EPI_WARPS);
+            wxtc::mbar_init(&tmem_empty[a], 2 * EW);
         }
         wxtc::fence_mbar_init();
     }
@@ -241,7 +244,7 @@ wide_gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
         constexpr bool OUT_BF16 = (EPI == EPI_FWD || EPI == EPI_DX);
         constexpr int SPAN_COLS = OUT_BF16 ? 64 : 32;            // 128 bytes of an output row
         constexpr int SPAN_CHUNKS = SPAN_COLS / 16;
-        constexpr int WARP_COLS = BNT / 2;
+        constexpr int WARP_COLS = BNT / (EW / 4);               // EW / 4 warps share a 32-lane quarter of the accumulator
         const int q = warp & 3;
         const int half = (warp - 3) >> 2;
         const uint32_t stg = wxtc::smem_u32(sEpi + size_t(warp - 3) * EPI_STAGE_BYTES);
