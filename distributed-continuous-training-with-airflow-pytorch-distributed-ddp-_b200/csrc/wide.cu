@@ -230,6 +230,155 @@ __global__ void __launch_bounds__(256) wide_head_kernel(const __nv_bfloat16* __r
     }
 }
 
+// The same head pass for hidden <= 4096, eight rows at a time per CTA: warp w owns the 8-column units k*256 + w*32 + lane of
+// every row, so the two head weight rows sit in registers for the whole kernel (the warp-per-row kernel above re-reads
+// them from L1 for every row: four weight loads per activation load) and the eight rows' activations stay in registers
+// between the logit pass and the dZ pass.  Partial logits: per warp one transposing butterfly over the 16 (row, class)
+// sums, then warp r adds the eight warps' parts of row r in warp order.  Same outputs as wide_head_kernel.
+template <int K8>
+__global__ void __launch_bounds__(256) wide_head_rows_kernel(const __nv_bfloat16* __restrict__ h, int64_t batch, int H,
+                                                            const float* __restrict__ w_o, const float* __restrict__ b_o,
+                                                            const int64_t* __restrict__ y, float scale,
+                                                            float* __restrict__ dlog, float* __restrict__ part,
+                                                            float inv_keep, __nv_bfloat16* __restrict__ dz) {
+    constexpr int R = 8;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    __shared__ float red[8][2 * R];
+    __shared__ float dl[R][2];
+    float w0[K8][8], w1[K8][8];
+    bool on[K8];
+#pragma unroll
+    for (int k = 0; k < K8; ++k) {
+        const int u = k * 256 + warp * 32 + lane;
+        on[k] = u * 8 < H;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            w0[k][i] = on[k] ? __ldg(w_o + u * 8 + i) : 0.0f;
+            w1[k][i] = on[k] ? __ldg(w_o + H + u * 8 + i) : 0.0f;
+        }
+    }
+    const float bo0 = b_o[0], bo1 = b_o[1];
+    float acc_loss = 0.0f, acc0 = 0.0f, acc1 = 0.0f, acc_ok = 0.0f;      // lane 0 of warp r: row r of every block
+    for (int64_t r0 = int64_t(blockIdx.x) * R; r0 < batch; r0 += int64_t(gridDim.x) * R) {
+        uint4 hv[R][K8];
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+#pragma unroll
+            for (int k = 0; k < K8; ++k) {
+                hv[r][k] = make_uint4(0, 0, 0, 0);
+                if (on[k] && r0 + r < batch)
+                    hv[r][k] = __ldg(reinterpret_cast<const uint4*>(h + (r0 + r) * H) + k * 256 + warp * 32 + lane);
+            }
+        }
+        float ps[2 * R];
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            float s0 = 0.0f, s1 = 0.0f;
+#pragma unroll
+            for (int k = 0; k < K8; ++k) {
+                float f[8];
+                unpack8(hv[r][k], f);
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    s0 = fmaf(f[i], w0[k][i], s0);
+                    s1 = fmaf(f[i], w1[k][i], s1);
+                }
+            }
+            ps[2 * r] = s0;
+            ps[2 * r + 1] = s1;
+        }
+        int col;
+        const float t = warp_transpose_sum16(ps, lane, col);
+        if ((lane & 1) == 0) red[warp][col] = t;
+        __syncthreads();
+        {
+            const int r = warp;                                          // R == number of warps
+            float s0 = 0.0f, s1 = 0.0f;
+#pragma unroll
+            for (int w = 0; w < 8; ++w) {
+                s0 += red[w][2 * r];
+                s1 += red[w][2 * r + 1];
+            }
+            s0 += bo0;
+            s1 += bo1;
+            if (lane == 0 && r0 + r < batch) {
+                const float mx = fmaxf(s0, s1);
+                const float e0 = expf(s0 - mx), e1 = expf(s1 - mx);
+                const float lse = mx + logf(e0 + e1);
+                const int64_t lab = y[r0 + r];
+                const float inv = 1.0f / (e0 + e1);
+                const float d0 = (e0 * inv - (lab == 0 ? 1.0f : 0.0f)) * scale;
+                const float d1 = (e1 * inv - (lab == 1 ? 1.0f : 0.0f)) * scale;
+                dl[r][0] = d0;
+                dl[r][1] = d1;
+                if (dlog != nullptr) {
+                    dlog[(r0 + r) * 2] = d0;
+                    dlog[(r0 + r) * 2 + 1] = d1;
+                }
+                acc_loss += (lse - (lab == 0 ? s0 : s1)) * scale;
+                acc_ok += (int64_t(s1 > s0) == lab) ? 1.0f : 0.0f;      // argmax, first index on ties (torch.argmax)
+                acc0 += d0;
+                acc1 += d1;
+            }
+        }
+        __syncthreads();
+        if (dz != nullptr) {
+#pragma unroll
+            for (int r = 0; r < R; ++r) {
+                if (r0 + r >= batch) break;
+                const float d0 = dl[r][0], d1 = dl[r][1];
+#pragma unroll
+                for (int k = 0; k < K8; ++k) {
+                    if (!on[k]) continue;
+                    float f[8], o[8];
+                    unpack8(hv[r][k], f);
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) {
+                        const float dh = fmaf(d0, w0[k][i], d1 * w1[k][i]);
+                        o[i] = f[i] > 0.0f ? dh * inv_keep : 0.0f;
+                    }
+                    uint4 ov;
+                    ov.x = pack_bf16(o[0], o[1]);
+                    ov.y = pack_bf16(o[2], o[3]);
+                    ov.z = pack_bf16(o[4], o[5]);
+                    ov.w = pack_bf16(o[6], o[7]);
+                    reinterpret_cast<uint4*>(dz + (r0 + r) * H)[k * 256 + warp * 32 + lane] = ov;
+                }
+            }
+        }
+    }
+    __shared__ float sh[8][4];
+    if (lane == 0) {
+        sh[warp][0] = acc_loss;
+        sh[warp][1] = acc0;
+        sh[warp][2] = acc1;
+        sh[warp][3] = acc_ok;
+    }
+    __syncthreads();
+    if (threadIdx.x < 4) {
+        float t = 0.0f;
+        for (int w = 0; w < 8; ++w) t += sh[w][threadIdx.x];
+        part[blockIdx.x * 4 + threadIdx.x] = t;
+    }
+}
+
+// launches the head pass; returns the number of per-CTA partials written to `part`
+int launch_head(wx_ctx* ctx, const __nv_bfloat16* h, int64_t batch, int H, const float* w_o, const float* b_o, const int64_t* y,
+                float scale, float* dlog, float* part, float inv_keep, __nv_bfloat16* dz, cudaStream_t st) {
+    if (H <= 4096) {
+        int64_t blocks = (batch + 7) / 8;
+        const int64_t cap = int64_t(ctx->num_sms) * 4;
+        const int grid = int(blocks < cap ? blocks : cap);
+        if (H <= 2048) wide_head_rows_kernel<1><<<grid, 256, 0, st>>>(h, batch, H, w_o, b_o, y, scale, dlog, part, inv_keep, dz);
+        else wide_head_rows_kernel<2><<<grid, 256, 0, st>>>(h, batch, H, w_o, b_o, y, scale, dlog, part, inv_keep, dz);
+        return grid;
+    }
+    int hgrid = int((batch + 7) / 8);
+    if (hgrid > 4096) hgrid = 4096;
+    wide_head_kernel<<<hgrid, 256, 0, st>>>(h, batch, H, w_o, b_o, y, scale, dlog, part, inv_keep, dz);
+    return hgrid;
+}
+
 // head backward: dZ_L[r][c] = (dl0[r] W_o[0][c] + dl1[r] W_o[1][c]) * gate(H_L[r][c]) as bf16, and per-slab partial sums
 // of dW_o[k][c] = sum_r dl_k[r] H_L[r][c].  Thread = 8 columns, CTA = 2048 columns, grid.y = row slabs.
 __global__ void __launch_bounds__(256) wide_head_bwd_kernel(const __nv_bfloat16* __restrict__ h, int64_t batch, int H,
@@ -801,13 +950,11 @@ int wx_wide_forward(wx_ctx* ctx, const wx_wide_desc* desc, const float* params, 
     float* dlog = reinterpret_cast<float*>(w + L.dlog);
     float* part = reinterpret_cast<float*>(w + L.part);
     float* head_part = part + size_t(HEAD_SLABS) * 2 * H;       // [grid][4]
-    int hgrid = int((batch + 7) / 8);
-    if (hgrid > 4096) hgrid = 4096;
     // logits, loss, dlogits AND dZ_L in one pass over H_L; dW_o (the other reader of H_L) is WX_WIDE_HEAD_DW of
     // wx_wide_backward_layer(layer = n_hidden), so the caller can keep it off the stream the GEMMs are waiting on
-    wide_head_kernel<<<hgrid, 256, 0, st>>>(hl, batch, int(H), params + L.off_w[nl + 1], params + L.off_b[nl + 1], y,
-                                           grad_scale, dlog, head_part, drop ? 1.0f / keep_p : 1.0f,
-                                           reinterpret_cast<__nv_bfloat16*>(w + L.dz[0]));
+    const int hgrid = launch_head(ctx, hl, batch, int(H), params + L.off_w[nl + 1], params + L.off_b[nl + 1], y, grad_scale,
+                                  dlog, head_part, drop ? 1.0f / keep_p : 1.0f, reinterpret_cast<__nv_bfloat16*>(w + L.dz[0]),
+                                  st);
     WX_LAUNCH_CHECK(ctx);
     wide_head_finish_kernel<<<1, 256, 0, st>>>(head_part, hgrid, grads + L.off_b[nl + 1], grads + L.P, nullptr);
     WX_LAUNCH_CHECK(ctx);
@@ -989,11 +1136,9 @@ int wx_wide_eval(wx_ctx* ctx, const wx_wide_desc* desc, const float* params, voi
     if (rc != WX_OK) return rc;
     float* part = reinterpret_cast<float*>(w + L.part);
     float* head_part = part + size_t(HEAD_SLABS) * 2 * desc->hidden;
-    int hgrid = int((batch + 7) / 8);
-    if (hgrid > 4096) hgrid = 4096;
-    wide_head_kernel<<<hgrid, 256, 0, st>>>(reinterpret_cast<const __nv_bfloat16*>(w + L.h[nl]), batch, desc->hidden,
-                                           params + L.off_w[nl + 1], params + L.off_b[nl + 1], y, 1.0f, nullptr, head_part,
-                                           1.0f, nullptr);
+    const int hgrid = launch_head(ctx, reinterpret_cast<const __nv_bfloat16*>(w + L.h[nl]), batch, desc->hidden,
+                                  params + L.off_w[nl + 1], params + L.off_b[nl + 1], y, 1.0f, nullptr, head_part, 1.0f,
+                                  nullptr, st);
     WX_LAUNCH_CHECK(ctx);
     wide_head_finish_kernel<<<1, 256, 0, st>>>(head_part, hgrid, nullptr, out, out + 1);
     WX_LAUNCH_CHECK(ctx);

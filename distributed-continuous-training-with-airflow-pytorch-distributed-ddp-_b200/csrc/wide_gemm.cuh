@@ -117,6 +117,45 @@ __device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
     return *reinterpret_cast<uint32_t*>(&v);
 }
 
+// Sums of 16 per-lane values over the 32 lanes of a warp with one transposing butterfly (8 + 4 + 2 + 1 + 1 shuffles):
+// afterwards lanes 2k and 2k+1 both hold the total of value `col` (returned per lane: col = 8 b4 + 4 b3 + 2 b2 + b1 of the
+// lane index).  Fixed order, so the result is reproducible.
+__device__ __forceinline__ float warp_transpose_sum16(const float (&r)[16], int lane, int& col) {
+    float u8[8], u4[4], u2[2];
+    {
+        const bool hi = lane & 16;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const float send = hi ? r[i] : r[i + 8];
+            const float keep = hi ? r[i + 8] : r[i];
+            u8[i] = keep + __shfl_xor_sync(0xffffffffu, send, 16);
+        }
+    }
+    {
+        const bool hi = lane & 8;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const float send = hi ? u8[i] : u8[i + 4];
+            const float keep = hi ? u8[i + 4] : u8[i];
+            u4[i] = keep + __shfl_xor_sync(0xffffffffu, send, 8);
+        }
+    }
+    {
+        const bool hi = lane & 4;
+#pragma unroll
+        for (int i = 0; i < 2; ++i) {
+            const float send = hi ? u4[i] : u4[i + 2];
+            const float keep = hi ? u4[i + 2] : u4[i];
+            u2[i] = keep + __shfl_xor_sync(0xffffffffu, send, 4);
+        }
+    }
+    const bool hi2 = lane & 2;
+    float t = (hi2 ? u2[1] : u2[0]) + __shfl_xor_sync(0xffffffffu, hi2 ? u2[0] : u2[1], 2);
+    t += __shfl_xor_sync(0xffffffffu, t, 1);
+    col = ((lane >> 4) & 1) * 8 + ((lane >> 3) & 1) * 4 + ((lane >> 2) & 1) * 2 + ((lane >> 1) & 1);
+    return t;
+}
+
 // Fused pointwise work on one 16-column chunk of an accumulator row (shared by the 1-CTA and 2-CTA kernels).  gw: the 16
 // bf16 gate values of this row and chunk (EPI_DX only).
 template <int EPI>
@@ -161,40 +200,9 @@ __device__ __forceinline__ void epilogue_math(float (&v)[16], const GemmArgs& g,
             float r[16];
 #pragma unroll
             for (int i = 0; i < 16; ++i) r[i] = __bfloat162float(__float2bfloat16_rn(v[i]));
+            int col;
+            const float t = warp_transpose_sum16(r, threadIdx.x & 31, col);
             const int lane = threadIdx.x & 31;
-            float u8[8], u4[4], u2[2];
-            {
-                const bool hi = lane & 16;
-#pragma unroll
-                for (int i = 0; i < 8; ++i) {
-                    const float send = hi ? r[i] : r[i + 8];
-                    const float keep = hi ? r[i + 8] : r[i];
-                    u8[i] = keep + __shfl_xor_sync(0xffffffffu, send, 16);
-                }
-            }
-            {
-                const bool hi = lane & 8;
-#pragma unroll
-                for (int i = 0; i < 4; ++i) {
-                    const float send = hi ? u8[i] : u8[i + 4];
-                    const float keep = hi ? u8[i + 4] : u8[i];
-                    u4[i] = keep + __shfl_xor_sync(0xffffffffu, send, 8);
-                }
-            }
-            {
-                const bool hi = lane & 4;
-#pragma unroll
-                for (int i = 0; i < 2; ++i) {
-                    const float send = hi ? u4[i] : u4[i + 2];
-                    const float keep = hi ? u4[i + 2] : u4[i];
-                    u2[i] = keep + __shfl_xor_sync(0xffffffffu, send, 4);
-                }
-            }
-            const bool hi2 = lane & 2;
-            float t = (hi2 ? u2[1] : u2[0]) + __shfl_xor_sync(0xffffffffu, hi2 ? u2[0] : u2[1], 2);
-            t += __shfl_xor_sync(0xffffffffu, t, 1);
-            // lane bits 4,3,2,1 selected the upper half at each step: column = 8*b4 + 4*b3 + 2*b2 + b1
-            const int col = ((lane >> 4) & 1) * 8 + ((lane >> 3) & 1) * 4 + ((lane >> 2) & 1) * 2 + ((lane >> 1) & 1);
             if ((lane & 1) == 0) g.colsum_part[(row >> 5) * g.N + col0 + col] = t;
         }
     } else if (EPI == EPI_PLAIN) {
