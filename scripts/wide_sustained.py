@@ -5,7 +5,7 @@ import torch
 from wxddp.wide import WideEngine
 dev = torch.device("cuda", 0)
 H = int(os.environ.get("H", 4096)); B = int(os.environ.get("B", 16384)); F = 20; SECS = float(os.environ.get("SECS", 4))
-eng = WideEngine(F, H, 3, max_batch=B, device=dev)
+eng = WideEngine(F, H, 3, max_batch=B, device=dev, dropout_p=float(os.environ.get('DROP', 0.2)))
 x = torch.randn(8 * B, F, device=dev); y = (torch.rand(8 * B, device=dev) < 0.3).long()
 n = [0]
 def step():
