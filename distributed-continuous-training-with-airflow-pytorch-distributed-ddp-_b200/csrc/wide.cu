@@ -485,11 +485,22 @@ __global__ void __launch_bounds__(256) wide_tail_fold_kernel(float* __restrict__
 // out[i] = sum over parts (in order) of part[p * stride + i]
 __global__ void __launch_bounds__(256) wide_reduce_kernel(const float* __restrict__ part, int n_parts, int64_t stride,
                                                          int64_t n, float* __restrict__ out) {
-    const int64_t i = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
-    if (i >= n) return;
+    // CTA = 32 columns x 8 part groups: group g adds parts g, g + 8, ... in order, then the 8 group sums are added in group
+    // order (fixed order; with 512 parts per column a thread per column was a 512-deep dependent chain on 16 CTAs)
+    __shared__ float sh[8][32];
+    const int lane = threadIdx.x & 31, grp = threadIdx.x >> 5;
+    const int64_t i = int64_t(blockIdx.x) * 32 + lane;
     float t = 0.0f;
-    for (int p = 0; p < n_parts; ++p) t += part[size_t(p) * stride + i];
-    out[i] = t;
+    if (i < n)
+        for (int p = grp; p < n_parts; p += 8) t += part[size_t(p) * stride + i];
+    sh[grp][lane] = t;
+    __syncthreads();
+    if (grp == 0 && i < n) {
+        float a = 0.0f;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) a += sh[k][lane];
+        out[i] = a;
+    }
 }
 
 // head partials [n_parts][4] = (loss, db0, db1, -) -> grads[off_b_out .. +2] and grads[P]
@@ -994,7 +1005,7 @@ int wx_wide_backward_layer(wx_ctx* ctx, const wx_wide_desc* desc, void* ws, int6
                                                 nullptr, reinterpret_cast<const float*>(w + L.dlog), 1.0f,
                                                 nullptr, part);
         WX_LAUNCH_CHECK(ctx);
-        wide_reduce_kernel<<<int((2 * H + 255) / 256), 256, 0, st>>>(part, slabs, 2 * H, 2 * H, grads + L.off_w[nl + 1]);
+        wide_reduce_kernel<<<int((2 * H + 31) / 32), 256, 0, st>>>(part, slabs, 2 * H, 2 * H, grads + L.off_w[nl + 1]);
         WX_LAUNCH_CHECK(ctx);
     }
     // dW = dZ^T H_below : A = dZ stored [batch, H] = [K, M], B = H_below stored [batch, in] = [K, N]
@@ -1047,14 +1058,14 @@ int wx_wide_backward_layer(wx_ctx* ctx, const wx_wide_desc* desc, void* ws, int6
         dim3 cg((unsigned)((H / 8 + 255) / 256), (unsigned)slabs);
         wide_colsum_kernel<<<cg, 256, 0, st>>>(reinterpret_cast<const __nv_bfloat16*>(dz), batch, int(H), part);
         WX_LAUNCH_CHECK(ctx);
-        wide_reduce_kernel<<<int((H + 255) / 256), 256, 0, st>>>(part, slabs, H, H, grads + L.off_b[layer]);
+        wide_reduce_kernel<<<int((H + 31) / 32), 256, 0, st>>>(part, slabs, H, H, grads + L.off_b[layer]);
         WX_LAUNCH_CHECK(ctx);
     }
     // db from the 32-row partial column sums that the dZ product of the layer above left behind (no pass over dZ)
     if (parts & WX_WIDE_DB_FUSED) {
         WX_CHECK_ARG(layer < nl, "wx_wide_backward_layer: WX_WIDE_DB_FUSED needs a layer below the top hidden layer "
                      "(its dZ comes from the head kernel, not from a dZ product); use WX_WIDE_DB there");
-        wide_reduce_kernel<<<int((H + 255) / 256), 256, 0, st>>>(reinterpret_cast<const float*>(w + L.cpart[layer]),
+        wide_reduce_kernel<<<int((H + 31) / 32), 256, 0, st>>>(reinterpret_cast<const float*>(w + L.cpart[layer]),
                                                                 int((batch + 31) / 32), H, H, grads + L.off_b[layer]);
         WX_LAUNCH_CHECK(ctx);
     }
