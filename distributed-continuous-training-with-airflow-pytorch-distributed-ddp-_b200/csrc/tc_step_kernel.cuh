@@ -699,9 +699,10 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_step_kernel(const GridArgs a
         asm volatile("bar.sync 1, 256;" ::: "memory");
         if (grp == 0) {
             const int h = r >> 6, j = r & 63;
-            float colsum = 0.0f;
-            for (int k = 0; k < TILE; ++k) colsum += red[(h * TILE + k) * 64 + ((j + 4 * k) & 63)];
-            s.w_hi[r] = colsum;                                         // W1s is dead: 128 partial column sums
+            float cs[4] = {0.0f, 0.0f, 0.0f, 0.0f};                     // four chains (rows k = q mod 4), added in a fixed order
+#pragma unroll 8
+            for (int k = 0; k < TILE; ++k) cs[k & 3] += red[(h * TILE + k) * 64 + ((j + 4 * k) & 63)];
+            s.w_hi[r] = (cs[0] + cs[1]) + (cs[2] + cs[3]);              // W1s is dead: 128 partial column sums
         }
         asm volatile("bar.sync 1, 256;" ::: "memory");
         if (grp == 0 && r < 64) {
