@@ -289,7 +289,7 @@ int wx_wide_forward(wx_ctx* ctx, const wx_wide_desc* desc, const float* params, 
 #define WX_WIDE_DW 1 /* weight gradient of the layer */
 #define WX_WIDE_DB 2 /* bias gradient (column sums of dZ) */
 #define WX_WIDE_DZ 4 /* dZ of the layer below (skipped for layer 1) */
-#define WX_WIDE_DW_FOLD 8 /* add the second split-K slab of dW into the gradient (no-op when dW was not split); must follow DW */
+#define WX_WIDE_DW_FOLD 8 /* add the workspace slabs of dW's split tail tiles into the gradient (no-op when dW was not split); must follow DW */
 #define WX_WIDE_HEAD_DW 16 /* with layer == n_hidden only: the head's weight gradient dW_o (wx_wide_forward leaves it to this piece) */
 #define WX_WIDE_DB_FUSED 32 /* layer < n_hidden only: the bias gradient from the 32-row column sums that the WX_WIDE_DZ piece of
                              * layer + 1 wrote beside dZ_layer (no pass over dZ); use instead of WX_WIDE_DB, after that piece */
