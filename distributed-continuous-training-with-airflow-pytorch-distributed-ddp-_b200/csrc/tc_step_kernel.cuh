@@ -783,12 +783,25 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_step_kernel(const GridArgs a
     float* bucket = s.u[1];
     bool apply = true;
     for (int g = tid; g < ng4; g += TC_THREADS) {
-        const bool direct = vec_ok && 4 * g + 3 < P;
-        float4 p4, m4, v4;
-        if (direct) {
-            p4 = reinterpret_cast<const float4*>(a.p_rw)[g];
-            m4 = reinterpret_cast<const float4*>(a.m)[g];
-            v4 = reinterpret_cast<const float4*>(a.v)[g];
+        // vec_ok: every thread updates the (up to) four parameters it sums, in this same pass -- the group that straddles P
+        // element by element, with the mean loss in the element after the last parameter
+        const bool direct = vec_ok && 4 * g < P + 1;
+        const bool full = 4 * g + 3 < P;
+        float pq[4] = {0.0f, 0.0f, 0.0f, 0.0f}, mq[4] = {0.0f, 0.0f, 0.0f, 0.0f}, vq[4] = {0.0f, 0.0f, 0.0f, 0.0f};
+        if (direct && full) {
+            const float4 p4 = reinterpret_cast<const float4*>(a.p_rw)[g], m4 = reinterpret_cast<const float4*>(a.m)[g],
+                         v4 = reinterpret_cast<const float4*>(a.v)[g];
+            pq[0] = p4.x; pq[1] = p4.y; pq[2] = p4.z; pq[3] = p4.w;
+            mq[0] = m4.x; mq[1] = m4.y; mq[2] = m4.z; mq[3] = m4.w;
+            vq[0] = v4.x; vq[1] = v4.y; vq[2] = v4.z; vq[3] = v4.w;
+        } else if (direct) {
+#pragma unroll
+            for (int e = 0; e < 4; ++e)
+                if (4 * g + e < P) {
+                    pq[e] = a.p_rw[4 * g + e];
+                    mq[e] = a.m[4 * g + e];
+                    vq[e] = a.v[4 * g + e];
+                }
         }
         const float4* src = reinterpret_cast<const float4*>(gpart) + g;
         float4 acc = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
@@ -808,42 +821,57 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_step_kernel(const GridArgs a
             }
         }
         if (direct) {
-            wxk::adam_apply(p4.x, acc.x, m4.x, v4.x, s.adam);
-            wxk::adam_apply(p4.y, acc.y, m4.y, v4.y, s.adam);
-            wxk::adam_apply(p4.z, acc.z, m4.z, v4.z, s.adam);
-            wxk::adam_apply(p4.w, acc.w, m4.w, v4.w, s.adam);
-            reinterpret_cast<float4*>(a.p_rw)[g] = p4;
-            reinterpret_cast<float4*>(a.m)[g] = m4;
-            reinterpret_cast<float4*>(a.v)[g] = v4;
+            const float gq[4] = {acc.x, acc.y, acc.z, acc.w};
+#pragma unroll
+            for (int e = 0; e < 4; ++e)
+                if (full || 4 * g + e < P) wxk::adam_apply(pq[e], gq[e], mq[e], vq[e], s.adam);
+            if (full) {
+                reinterpret_cast<float4*>(a.p_rw)[g] = make_float4(pq[0], pq[1], pq[2], pq[3]);
+                reinterpret_cast<float4*>(a.m)[g] = make_float4(mq[0], mq[1], mq[2], mq[3]);
+                reinterpret_cast<float4*>(a.v)[g] = make_float4(vq[0], vq[1], vq[2], vq[3]);
+            } else {
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                    const int i = 4 * g + e;
+                    if (i < P) {
+                        a.p_rw[i] = pq[e];
+                        a.m[i] = mq[e];
+                        a.v[i] = vq[e];
+                    } else if (i == P) {
+                        *a.loss_out = gq[e] * a.scale;                // mean loss
+                    }
+                }
+            }
         } else {
-            reinterpret_cast<float4*>(bucket)[g] = acc;               // the group that straddles P, gradients out, or DDP
+            reinterpret_cast<float4*>(bucket)[g] = acc;               // gradients out, or DDP: through the bucket
         }
     }
-    __syncthreads();
-    if (tid == 0) bucket[P] *= a.scale;                               // mean loss
-    __syncthreads();
-    if (exchange) {
-        // DDP exchange inside the kernel: one-shot all-reduce over NVLink peer memory (csrc/peer.cuh).  If a peer does
-        // not show up in time the step is NOT applied on this rank (parameters, moments and step counter stay as they
-        // were) and the sticky error code says so -- a visible stall instead of silently diverging replicas.
-        apply = wxpeer::allreduce_cta(bucket, P + 1, a.peer, uint64_t(a.state[0]) + 1, tid, TC_THREADS);
-        if (!apply && tid == 0) atomicExch(err_out, 20);
-    }
-    const int first_left = vec_ok ? (P & ~3) : 0;                     // elements not handled above
-    for (int i = first_left + tid; i < P + 1; i += TC_THREADS) {
-        const float sum = bucket[i];
-        if (a.tail == wxk::TAIL_GRADS) {
-            a.out[i] = sum;
-        } else if (!apply) {
-            continue;
-        } else if (i < P) {
-            float p = a.p_rw[i], m = a.m[i], v = a.v[i];
-            wxk::adam_apply(p, sum, m, v, s.adam);
-            a.p_rw[i] = p;
-            a.m[i] = m;
-            a.v[i] = v;
-        } else {
-            *a.loss_out = sum;
+    if (!vec_ok) {
+        __syncthreads();
+        if (tid == 0) bucket[P] *= a.scale;                           // mean loss
+        __syncthreads();
+        if (exchange) {
+            // DDP exchange inside the kernel: one-shot all-reduce over NVLink peer memory (csrc/peer.cuh).  If a peer does
+            // not show up in time the step is NOT applied on this rank (parameters, moments and step counter stay as they
+            // were) and the sticky error code says so -- a visible stall instead of silently diverging replicas.
+            apply = wxpeer::allreduce_cta(bucket, P + 1, a.peer, uint64_t(a.state[0]) + 1, tid, TC_THREADS);
+            if (!apply && tid == 0) atomicExch(err_out, 20);
+        }
+        for (int i = tid; i < P + 1; i += TC_THREADS) {
+            const float sum = bucket[i];
+            if (a.tail == wxk::TAIL_GRADS) {
+                a.out[i] = sum;
+            } else if (!apply) {
+                continue;
+            } else if (i < P) {
+                float p = a.p_rw[i], m = a.m[i], v = a.v[i];
+                wxk::adam_apply(p, sum, m, v, s.adam);
+                a.p_rw[i] = p;
+                a.m[i] = m;
+                a.v[i] = v;
+            } else {
+                *a.loss_out = sum;
+            }
         }
     }
     WX_TC_STAMP(6);
@@ -851,7 +879,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_step_kernel(const GridArgs a
         for (unsigned g = tid; g < ngroups; g += 32) tick[TICKET_GROUP0 + g] = 0u;
         if (tid == 0) {
             tick[TICKET_TOP] = 0u;
-            if (a.tail == wxk::TAIL_ADAM && apply) a.state[0] += 1;
+            if (a.tail == wxk::TAIL_ADAM && apply) a.state[0] = int64_t(step_word) + 1;   // read at kernel start: a store, no round trip
         }
     }
 }
