@@ -18,6 +18,18 @@ import sys
 import threading
 import time
 
+# Rank 0 prints ONE JSON line on stdout.  Libraries write there too (NCCL's version banner, its INFO lines when the
+# environment asks for them): main() keeps a private copy of the real stdout for that line and points file descriptor 1 at
+# stderr for everything else.
+_RESULT_OUT = None
+
+
+def emit(line: dict) -> None:
+    out = _RESULT_OUT if _RESULT_OUT is not None else sys.stdout
+    out.write(json.dumps(line) + "\n")
+    out.flush()
+
+
 ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
@@ -182,7 +194,7 @@ def run_reference(args, rank: int):
         "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
     return 0
 
 
@@ -236,7 +248,7 @@ def run_wide(args, rank: int, local_rank: int, world: int) -> int:
                                            f"autograd + torch.optim.Adam on the host cores ({r['seconds']:.1f} s)"},
                 "e2e": {"value": r["samples_per_sec"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
                 "gpu_launches": 0}
-        print(json.dumps(line), flush=True)
+        emit(line)
         return 0
 
     import torch
@@ -270,7 +282,7 @@ def run_wide(args, rank: int, local_rank: int, world: int) -> int:
         line["cpu_baseline"] = {"value": r["samples_per_sec"], "unit": UNIT, "cores": r["cores"], "kind": "port",
                                 "sample": f"4 steps x 1024 rows, torch fp32 nn.Sequential + autograd + torch.optim.Adam "
                                           f"on the host cores ({r['seconds']:.1f} s)"}
-    print(json.dumps(line), flush=True)
+    emit(line)
     if world > 1:
         dist.destroy_process_group()
     return 0
@@ -372,6 +384,10 @@ def read_burst_peak():
 
 
 def main() -> int:
+    global _RESULT_OUT
+    sys.stdout.flush()
+    _RESULT_OUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=50)
@@ -714,7 +730,7 @@ def main() -> int:
                                                   "__getitem__+collate (train_lightning_ddp.py:49,122)"}
     if world == 1 and not args.no_cpu_baseline:
         line["gpu_reference_config"] = reference_config_on_gpu(torch, wxddp, device)
-    print(json.dumps(line), flush=True)
+    emit(line)
     if world > 1:
         dist.destroy_process_group()
     return 0
