@@ -184,17 +184,23 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_step_kernel(const GridArgs a
         s.err = 0;
     }
     if (warp == 0) tmem_alloc(&s.tmem_base, TMEM_COLS);
+    __syncthreads();                                              // the barriers exist for every role from here on
     // Everything above touches only this CTA's own resources and may overlap the tail of the previous launch in the
-    // stream (programmatic dependent launch); parameters, statistics, step counter and scratch are read below.
+    // stream (programmatic dependent launch); inputs, parameters, statistics, step counter and scratch are read below.
     asm volatile("griddepcontrol.wait;" ::: "memory");
-    // parameters and statistics: one coalesced pass into shared memory (U[0] is free until the first tile ends)
+    // The producer warp goes straight to its loop: the first tiles are on their way from HBM while the other 14 warps
+    // stage the parameters and build the W1s operand (they meet on named barrier 2; everyone meets again at the tail).
+    constexpr int NSTAGE_THREADS = TC_THREADS - 32;
+    const int stid = tid < PRODUCER_WARP * 32 ? tid : tid - 32;   // index among the staging threads
     float* sp = s.u[0];                                           // [P] parameters
     double* sst = reinterpret_cast<double*>(s.u[0] + ((P + 3) & ~3) + 4);   // [F][4] statistics (8-byte aligned)
-    for (int i = tid; i < P; i += TC_THREADS) sp[i] = a.params[i];
+    if (warp != PRODUCER_WARP) {
+    // parameters and statistics: one coalesced pass into shared memory (U[0] is free until the first tile ends)
+    for (int i = stid; i < P; i += NSTAGE_THREADS) sp[i] = a.params[i];
     if (RAW)
-        for (int i = tid; i < 4 * F; i += TC_THREADS) sst[i] = a.stats[i];
+        for (int i = stid; i < 4 * F; i += NSTAGE_THREADS) sst[i] = a.stats[i];
     if (tid == TC_THREADS - 1 && a.tail == wxk::TAIL_ADAM) s.adam = wxk::adam_scalars(a.desc, a.state[0] + 1);
-    __syncthreads();
+    asm volatile("bar.sync 2, %0;" ::"n"(NSTAGE_THREADS) : "memory");
     // W1s operand (hi/lo, K-major SW128), one thread per hidden unit; fp64 so that folding 1/std and the mean remainder
     // into the weights costs no accuracy (the products are rounded to fp32 once, like W1 itself)
     if (tid < 64) {
@@ -245,8 +251,9 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_step_kernel(const GridArgs a
     }
     fence_proxy_async();
     tc_fence_before();
-    __syncthreads();
+    asm volatile("bar.sync 2, %0;" ::"n"(NSTAGE_THREADS) : "memory");
     tc_fence_after();
+    }
     WX_TC_STAMP(1);
     const uint32_t tm = s.tmem_base;
     const uint64_t step_word = (a.state != nullptr) ? uint64_t(a.state[0]) : a.step;
@@ -310,7 +317,9 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_step_kernel(const GridArgs a
                 } else {
                     for (int c = 0; c < F; ++c)
                         for (int e = lane; e < TILE; e += 32)
-                            lx[c * TILE + e] = e < nr ? static_cast<const float*>(a.cols.col[c])[row + e] : s.mean_hi[c];
+                            lx[c * TILE + e] = e < nr ? static_cast<const float*>(a.cols.col[c])[row + e]
+                                                      : float(a.stats[c * 4 + 1]);   // centres to exactly zero (= s.mean_hi[c], which
+                                                                                     // the staging warps may not have written yet)
                 }
                 for (int e = lane; e < TILE; e += 32) {
                     land_y(st)[e] = e < nr ? a.y[row + e] : 0;
