@@ -6,10 +6,12 @@
 // Data flow of one step (all device pointers caller-owned; `ws` is one caller-allocated workspace):
 //   x fp32 [B,F] --cast/pad--> X0 bf16 [B,64]
 //   H_l = drop(relu(H_{l-1} W_l^T + b_l))            GEMM, EPI_FWD      l = 1..L   (bf16 activations, fp32 accumulate)
-//   logits = H_L W_o^T + b_o ; loss ; dlogits         wide_head_kernel   (fp32, warp per row)
-//   dZ_L = (dlogits W_o) * gate(H_L) ; dW_o partials  wide_head_bwd_kernel
+//   logits = H_L W_o^T + b_o ; loss ; dlogits ; dZ_L = (dlogits W_o) * gate(H_L)
+//                                                      wide_head_rows_kernel (hidden <= 4096; else wide_head_kernel)
+//   dW_o partials                                      wide_head_bwd_kernel
 //   for l = L..1:  dW_l = dZ_l^T H_{l-1}              GEMM, EPI_DW (both operands read MN-major, fp32 out)
-//                  db_l = colsum(dZ_l)                 wide_colsum_kernel + wide_reduce_kernel
+//                  db_l = colsum(dZ_l)                 top layer: wide_colsum_kernel + wide_reduce_kernel; below: 32-row
+//                                                      partials from the EPI_DX epilogue + wide_reduce_kernel
 //                  dZ_{l-1} = (dZ_l W_l) * gate(H_{l-1})   GEMM, EPI_DX (W read MN-major)
 //   Adam on the fp32 master parameters, re-emitting the bf16 copies of the hidden weights in the same pass.
 #include "wide_gemm2.cuh"

@@ -1,22 +1,25 @@
-// Two-SM variant of the wide bf16 GEMM (wide_gemm.cuh): clusters of 2 CTAs on one TPC compute a 256 x 256 output tile with
-// tcgen05.mma.cta_group::2.  Each CTA stages ITS 128 rows of A and ITS 128-column half of B (32 KiB per stage instead of
-// 48), the leader CTA's MMA warp issues one M256 N256 K16 instruction that reads both CTAs' shared memory, and each CTA
-// keeps the accumulator of its own 128 rows (all 256 columns) in its own TMEM.  Per FLOP the pair reads a third less
-// shared memory than two independent 128 x 256 tiles, and the ring is 6 stages deep.
+// Two-SM variant of the wide bf16 GEMM (wide_gemm.cuh): clusters of 2 CTAs on one TPC compute a 256 x 256 (NB = 1) or
+// 256 x 512 (NB = 2) output tile with tcgen05.mma.cta_group::2.  Each CTA stages ITS 128 rows of A and ITS 128-column half
+// of every 256-column block of B, the leader CTA's MMA warp issues M256 N256 K16 instructions that read both CTAs' shared
+// memory, and each CTA keeps the accumulator of its own 128 rows in its own TMEM.
 //
 // Barrier protocol (per stage / accumulator buffer):
 //   full[s]        lives in the LEADER: both CTAs' TMA loads complete_tx on it (barrier address with the peer bit cleared);
 //                  only the leader's producers arrive.expect_tx (for both CTAs' bytes)
 //   empty[s]       one per CTA: the leader's tcgen05.commit multicasts the arrive to both
 //   tmem_full[a]   one per CTA, multicast commit as well
-//   tmem_empty[a]  in the leader, 2 x 8 arrivals: the peer's epilogue warps arrive remotely (mapa + mbarrier.arrive.cluster)
+//   tmem_empty[a]  in the leader, 2 x EW arrivals: the peer's epilogue warps arrive remotely (mapa + mbarrier.arrive.cluster)
 // Used for the big products of the wide MLP (M % 256 == 0, N % 256 == 0); everything else takes the 1-CTA kernel.
 //
-// NB = 2 widens the pair's tile to 256 x 512 (two N = 256 MMAs per K step against the same A rows).  A 256 x 256 tile pulls
-// 64 KiB per 64-deep K block and pair, i.e. 64 B per clock and SM at the tensor pipe's full rate -- 9.5 KB per clock for
-// the chip, more than the L2 delivers -- so the narrow tile is L2-bound at roughly 2/3 of the tensor rate.  The wide tile
-// needs 48 B per clock and SM.  It costs the second accumulator (512 TMEM columns hold one 128 x 512 fp32 tile), so the
-// epilogue of a tile is no longer hidden behind the next tile's MMAs; the loads of the next tile still run ahead.
+// NB = 2 (two N = 256 MMAs per K step against the same A rows; 4 stages of 48 KiB).  A 256 x 256 tile pulls 64 KiB per
+// 64-deep K block and pair, i.e. 64 B per clock and SM at the tensor pipe's full rate -- 9.5 KB per clock for the chip, more
+// than the L2 delivers -- so the narrow tile (6 stages of 32 KiB, two accumulators) is L2-bound at roughly 2/3 of the
+// tensor rate.  The wide tile needs 48 B per clock and SM.  It costs the second accumulator (512 TMEM columns hold one
+// 128 x 512 fp32 tile), so the epilogue of a tile is no longer hidden behind the next tile's MMAs; the loads of the next
+// tile still run ahead, and the epilogue warps do everything that does not need the accumulator before they wait for it.
+//
+// Work units: output tiles, optionally cut along K (GemmArgs::split_k: every tile; GemmArgs::tail_*: only the tiles of the
+// last, partly filled round -- see decode() below).
 #pragma once
 
 #include "wide_gemm.cuh"
