@@ -16,8 +16,10 @@ def _free_port() -> int:
 
 
 def _line(stdout: str) -> dict:
-    rows = [ln for ln in stdout.splitlines() if ln.startswith("{")]
-    assert len(rows) == 1, stdout
+    # ONE JSON line and nothing else on stdout: bench.py keeps a private copy of the real stdout for its line and points
+    # file descriptor 1 at stderr, so that what libraries print (NCCL's banner on the GPU boxes) cannot land in front of it
+    rows = [ln for ln in stdout.splitlines() if ln.strip()]
+    assert len(rows) == 1 and rows[0].startswith("{"), stdout
     return json.loads(rows[0])
 
 
