@@ -20,7 +20,8 @@
 //
 // fp32 accuracy on tf32 tensor cores: x = hi + lo (hi = x rounded to 11 significant bits, lo exact); GEMM1 sums
 // hi*lo + lo*hi + hi*hi (~2^-21 relative); GEMM2's A operand is exact, so hi + lo of U alone gives the same accuracy.
-// dW2 / db2 / loss are row-local sums: dW2 lives in per-thread TMEM columns (packed fp32x2 FMAs), db2 / loss in registers.
+// dW2 / db2 / loss are row-local sums: dW2 lives in per-thread TMEM columns (packed fp32x2 FMAs, two units each), db2 / loss
+// in registers.
 //
 // Roles (480 threads, one CTA per SM, persistent over 128-row tiles; tile i belongs to worker group i & 1):
 //   warps 0-3 / 4-7  two row-worker groups: thread r <-> tile row r <-> TMEM lane r (row-local work, no shuffles):
@@ -534,7 +535,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_step_kernel(const GridArgs a
             //      The TMEM load of the next 16 units is in flight while this chunk is processed. ----
             // Only lg1 - lg0 enters a two-class log-softmax, so one FMA per unit against ds (W2[1][j] - W2[0][j]) replaces the
             // two logit FMAs; the 16 weights of the next chunk are requested before this chunk is processed.
-            float dq[4] = {0.0f, 0.0f, 0.0f, 0.0f};              // four independent accumulation chains
+            // four independent accumulation chains (units = 0..3 mod 4), two per packed fp32x2 FMA
+            float2 dq2[2] = {make_float2(0.0f, 0.0f), make_float2(0.0f, 0.0f)};
             const float4* __restrict__ wdl4 = reinterpret_cast<const float4*>(s.wdl);   // read-only here
             float zbuf[2][16];
             float4 wbuf[2][4];
@@ -565,15 +567,15 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_step_kernel(const GridArgs a
                     if (DROP == DROP_PHILOX) kp = wxk::keep_digit(q < 8 ? s0 : s1);
                     if (DROP == DROP_MASK) kp = (kb >> q) & 1u;
                     const bool on = kp && !(z[q] <= 0.0f);                 // relu as torch's threshold: NaN passes
-                    const float av = on ? z[q] : 0.0f;
-                    dq[q & 3] = fmaf(av, wv[q], dq[q & 3]);
-                    z[q] = av;
+                    z[q] = on ? z[q] : 0.0f;
+                    if (q & 1)
+                        dq2[(q >> 1) & 1] = __ffma2_rn(make_float2(z[q - 1], z[q]), make_float2(wv[q - 1], wv[q]), dq2[(q >> 1) & 1]);
                 }
                 tmem_st16_nc(d1 + cc * 16, z);                               // a replaces z in place: phase B reads it back
             }
             WX_TC_PH(3);
             const float lg0 = 0.0f;                               // log-softmax is shift-invariant: (0, lg1 - lg0)
-            const float lg1 = ((dq[0] + dq[1]) + (dq[2] + dq[3])) + (b2_1 - b2_0);
+            const float lg1 = ((dq2[0].x + dq2[0].y) + (dq2[1].x + dq2[1].y)) + (b2_1 - b2_0);
             // ---- softmax / loss / dlogits, ATen's operation order ----
             const float mx = fmaxf(lg0, lg1);
             const float e0 = lg0 - mx, e1 = lg1 - mx;
@@ -610,7 +612,11 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_step_kernel(const GridArgs a
                         tmem_ld16_nc(acc_base + (cc + 1) * 16, gbuf[(cc + 1) & 1]);
                     }
 #pragma unroll
-                    for (int q = 0; q < 16; ++q) g[q] = fmaf(av[q], dd, g[q]);
+                    for (int q = 0; q < 16; q += 2) {
+                        const float2 t = __ffma2_rn(make_float2(av[q], av[q + 1]), make_float2(dd, dd), make_float2(g[q], g[q + 1]));
+                        g[q] = t.x;
+                        g[q + 1] = t.y;
+                    }
                     tmem_st16_nc(acc_base + cc * 16, g);
                     float gt[16];
 #pragma unroll
