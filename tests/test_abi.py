@@ -64,3 +64,29 @@ def test_context_without_gpu_fails_loudly(wx):
         pytest.skip("GPU present")
     with pytest.raises(wx.WxError):
         wx.Context(5)
+
+
+def _sass_of(lib_path: str, mangled: str) -> str:
+    r = subprocess.run(["cuobjdump", "-sass", "-fun", mangled, lib_path], capture_output=True, text=True, timeout=120)
+    return "\n".join(ln for ln in r.stdout.splitlines() if re.match(r"\s+/\*[0-9a-f]+\*/", ln))
+
+
+@pytest.mark.skipif(subprocess.run(["which", "cuobjdump"], capture_output=True).returncode != 0, reason="no cuobjdump")
+def test_the_dominant_kernels_are_tcgen05_code(wx):
+    """What the bench lines name as the dominant kernels must be Blackwell tensor-core code in the built library: UTC*MMA
+    (tcgen05.mma), LDTM / STTM (tcgen05.ld / st) and, for the wide GEMM, UTMALDG (TMA tensor loads) -- and no legacy
+    HMMA (mma.sync) anywhere in them.  (SASS mnemonics: /opt/skills/guides/B200_PROFILING.md; the whole library is
+    listed in profiles/r2_sass_mnemonics.txt.)"""
+    lib = wx.lib_path() if hasattr(wx, "lib_path") else None
+    if lib is None:
+        from wxddp import _lib
+        lib = _lib.lib_path()
+    step = _sass_of(lib, "_ZN8wxtcstep14tc_step_kernelILb1ELi2ELi20EEEvN3wxk8GridArgsEiNS_6TcGeomEPi")
+    assert len(step.splitlines()) > 1000, "tc_step_kernel<true, PHILOX, 20> not found in the library"
+    assert len(re.findall(r"\bUTC[A-Z]*MMA\b", step)) >= 25          # 9 GEMM1 + 16 GEMM2 MMAs per tile
+    assert "LDTM" in step and "STTM" in step and "LDGSTS" in step    # TMEM operands / accumulators, cp.async producer
+    assert "FFMA2" in step and not re.search(r"\bHMMA\b", step)
+    gemm = _sass_of(lib, "_ZN6wxwide17wide_gemm2_kernelILb1ELb1ELi0ELi2ELi8EEEv14CUtensorMap_stS1_NS_8GemmArgsE")
+    assert len(gemm.splitlines()) > 500, "wide_gemm2_kernel<K, K, FWD, 256x512, 8> not found in the library"
+    assert re.search(r"\bUTC[A-Z]*MMA\b", gemm) and "UTMALDG" in gemm and "LDTM" in gemm
+    assert not re.search(r"\bHMMA\b", gemm)
